@@ -1,0 +1,330 @@
+#!/usr/bin/env python
+"""bench.py -- captions/sec of the attention-LSTM decoder training step (fwd+bwd, T=16), BASELINE.json's metric.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config cfg2]
+
+* ours: DecoderTrainStep.forward_train (alexcap_attn_train_fused through the C ABI).  `value` = whole-job captions/s
+  with inputs resident in HBM; `e2e` = same through the public API from PINNED HOST buffers (H2D of features+captions
+  and D2H of the loss inside the timed region).  N>1 (torchrun): one rank per GPU, per-rank batch fixed (weak scaling),
+  gradients all-reduced with NCCL inside the timed step.
+* reference: the reference's CPU execution path (oracle/ref_port.py: the reference modules' per-step structure, stock
+  torch CPU ops + autograd; the reference itself is Python under /root/reference and cannot travel to the GPU box)
+  with all host threads, on bounded samples of the same workload.  Rank 0 only.
+One JSON line on stdout (rank 0).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+CONFIGS = {
+    # BASELINE.json configs[1]: the configuration the metric is quoted on at N=1
+    'cfg2': dict(model='LSTMwAttentionModel', B=128, L=196, D=512, H=512, E=512, V=10000, T=16, dtype='f32'),
+    'cfg1': dict(model='LSTMModel', B=16, L=1, D=512, H=512, E=512, V=10000, T=16, dtype='f32'),
+    'cfg3_f32': dict(model='LSTMwAttentionModel', B=512, L=49, D=2048, H=1024, E=1024, V=10000, T=16, dtype='f32'),
+}
+METRIC = 'captions/sec (attn-LSTM fwd+bwd, T=16)'
+
+
+def peaks():
+    p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(p):
+        j = json.load(open(p))
+        return dict(hbm=j['hbm_gbs'], bf16=j['bf16_tflops'], bf16_sus=j['bf16_tflops_sustained'], src='measured')
+    return dict(hbm=6650.0, bf16=1590.0, bf16_sus=1400.0, src='fallback')
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    def __init__(self, gpu_index=0):
+        self.rows, self.proc, self.gpu = [], None, gpu_index
+
+    def __enter__(self):
+        q = ('clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,'
+             'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,'
+             'clocks_event_reasons.sw_power_cap')
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', f'--query-gpu={q}', '--format=csv,noheader,nounits', '-lms', '100',
+                                          '-i', str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(',')])
+
+    def __exit__(self, *a):
+        if self.proc:
+            time.sleep(0.15)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self):
+        sm, mx, reasons = [], 0.0, set()
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx = max(mx, float(r[1]))
+            except Exception:
+                continue
+            for n, v in zip(names, r[3:7]):
+                if v.lower().startswith('active'):
+                    reasons.add(n)
+        sm.sort()
+        return dict(sm_mhz=(sm[len(sm) // 2] if sm else None), sm_max_mhz=mx or None, reasons=sorted(reasons),
+                    samples=len(sm))
+
+
+def algorithmic_work(c):
+    """GEMM FLOPs and attention bytes of one training step (frozen features)."""
+    B, L, D, H, E, S, Vp = c['B'], c['L'], c['D'], c['H'], c['E'], c['T'] + 1, c['V'] + 3
+    f_fwd = (2 * B * L * D * H + 4 * B * D * H + 2 * B * S * E * 4 * H
+             + S * (2 * B * H * H + 2 * B * H * D + 2 * B * D * 4 * H + 2 * B * H * 4 * H) + 2 * B * S * H * Vp)
+    f_step = 3 * f_fwd - 2 * B * L * D * H - 2 * B * D * H
+    e = 4
+    attn_fwd_step = B * L * (H + D) * e + B * L * 4 + B * (H + D) * e
+    attn_bwd_step = B * L * (H + D) * e
+    return dict(gemm_flops_step=f_step, attn_fwd_bytes_per_launch=attn_fwd_step, attn_bwd_bytes_per_launch=attn_bwd_step)
+
+
+def make_model(c, dev):
+    from imagecaptioning_b200.modules import Decoder, LanguageModel
+    torch.manual_seed(123)   # the reference's seed (AlexCap/LSTM_opts.py:50)
+    if c['model'] == 'LSTMwAttentionModel':
+        m = Decoder(c['V'], c['E'], c['D'], c['H'], c['T'], {}, 0.0, dev)
+        m.dropout.p = 0.0    # parity setting; see DESIGN.md (dropout path measured separately)
+    else:
+        m = LanguageModel(c['V'], c['E'], c['D'], c['H'], c['T'], 1, {}, 0.0, dev)
+    return m.to(dev)
+
+
+def time_kernel_events(fn, iters, warm=3):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record()
+    for _ in range(iters):
+        fn()
+    e.record()
+    torch.cuda.synchronize()
+    return s.elapsed_time(e) / iters
+
+
+def dominant_kernel_roofline(c, dev, pk):
+    """The fused attention-step kernel timed alone (CUDA events on the launching stream) at the bench shape.
+    S distinct q/bpre slices per pass over the same Ws/feat, exactly as inside a training step."""
+    from imagecaptioning_b200 import functional as F_
+    B, L, D, H, S = c['B'], c['L'], c['D'], c['H'], c['T'] + 1
+    g = torch.Generator(device='cpu').manual_seed(1)
+    Ws = torch.randn(B, L, H, generator=g).to(dev)
+    feat = torch.randn(B, L, D, generator=g).relu().to(dev)
+    q = torch.randn(S, B, H, generator=g).to(dev)
+    bp = torch.randn(S, B, D, generator=g).to(dev)
+    wv = (torch.randn(H, generator=g) / H ** 0.5).to(dev)
+    state = {'t': 0}
+
+    def fwd():
+        t = state['t'] = (state['t'] + 1) % S
+        F_.attn_step_fwd(Ws, feat, q[t], bp[t], wv)
+
+    ms = time_kernel_events(fwd, 4 * S)
+    w = algorithmic_work(c)
+    ach = w['attn_fwd_bytes_per_launch'] / (ms * 1e-3) / 1e9
+    return dict(kernel='attn_fwd_kernel', bound='hbm', achieved=round(ach, 1), peak=pk['hbm'], unit='GB/s',
+                frac=round(ach / pk['hbm'], 4), traffic=None, ms_per_launch=round(ms, 5),
+                algorithmic_bytes_per_launch=w['attn_fwd_bytes_per_launch'], peak_source=pk['src'],
+                note='working set Ws+feat = %.0f MB vs 126 MB L2: part of it is L2-resident across steps; '
+                     'see profiles/ for dram__bytes' % (2 * B * L * max(H, D) * 4 / 1e6))
+
+
+def cpu_port(c):
+    from oracle import ref_port
+    torch.manual_seed(123)
+    if c['model'] == 'LSTMwAttentionModel':
+        return ref_port.AttnDecoderPort(c['V'], c['E'], c['D'], c['H'], c['T'], dropout_p=0.0)
+    return ref_port.LstmDecoderPort(c['V'], c['E'], c['D'], c['H'], c['T'], 1, 0.0)
+
+
+def time_cpu_port(c, steps, warmup, budget_s=150.0):
+    """captions/s of the reference-structured CPU port with all host threads; bounded per-step sample."""
+    from oracle.synth import synth_inputs
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    port = cpu_port(c)
+    feat, gt = synth_inputs(c['B'], c['L'], c['D'], c['V'], c['T'], seed=123, full_length=True)
+    t0 = time.perf_counter()
+    port.zero_grad(set_to_none=True)
+    port.train_step(feat, gt)                    # first (cold) step sizes the sample
+    t1 = time.perf_counter() - t0
+    bs = c['B']
+    total = steps + max(warmup - 1, 0)
+    if t1 * total > budget_s:
+        bs = max(1, int(c['B'] * budget_s / (t1 * total)))
+    f, g = feat[:bs].contiguous(), gt[:bs].contiguous()
+    for _ in range(max(warmup - 1, 0)):
+        port.zero_grad(set_to_none=True); port.train_step(f, g)
+    ts = []
+    for _ in range(steps):
+        port.zero_grad(set_to_none=True)
+        a = time.perf_counter(); port.train_step(f, g); ts.append(time.perf_counter() - a)
+    ts.sort()
+    med = ts[len(ts) // 2]
+    return dict(value=round(bs / med, 2), unit='captions/s', cores=cores, kind='port',
+                sample=f'{steps} timed steps of batch {bs} (of {c["B"]}) of the same synthetic workload, median step '
+                       f'{med * 1e3:.0f} ms, fp32, oracle/ref_port.py (reference-structured torch CPU path)'), med, bs
+
+
+def run_reference(args, c, rank):
+    if rank != 0:
+        return
+    cb, med, bs = time_cpu_port(c, args.steps, args.warmup)
+    line = dict(impl='reference', metric=METRIC, value=cb['value'], unit='captions/s', n_gpus=args.gpus, steps=args.steps,
+                warmup=args.warmup, ms_per_step=round(med * 1e3, 3), higher_is_better=True, scaling='weak', vs_baseline=None,
+                dtype='f32', data='synthetic', config=workload_config(c, args.gpus), cpu_baseline=cb,
+                e2e=dict(value=cb['value'], unit='captions/s', h2d_bytes_per_step=0, d2h_bytes_per_step=0))
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(c, n):
+    return dict(workload=f"{c['model']} decoder train step fwd+bwd (BASELINE.json configs[1]): B={c['B']}/GPU, "
+                         f"L={c['L']}, D={c['D']}, H={c['H']}, E={c['E']}, V={c['V']}, T={c['T']}, fp32, full-length captions, "
+                         f"dropout p=0",
+                global_batch=c['B'] * n, parallelism=f'dp{n}',
+                l2='no explicit flush: per-step working set (Ws+feat+logits+saved state ~ 400 MB) exceeds the 126 MB L2')
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=20)
+    ap.add_argument('--warmup', type=int, default=5)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--config', default='cfg2', choices=sorted(CONFIGS))
+    ap.add_argument('--no-graph', action='store_true')
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    args = ap.parse_args()
+    c = CONFIGS[args.config]
+    rank = int(os.environ.get('RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    if args.impl == 'reference':
+        run_reference(args, c, rank)
+        return
+    args.warmup = max(args.warmup, 3)
+
+    assert torch.cuda.is_available(), 'bench.py (impl ours) needs a CUDA device: there is no CPU fallback'
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group('nccl', device_id=dev)
+    from imagecaptioning_b200 import _lib
+    from imagecaptioning_b200.ddp import GradAllReducer
+    from imagecaptioning_b200.model import DecoderTrainStep
+    from oracle.synth import synth_inputs       # input generator shared with the oracle arm (not a compute path)
+
+    model = make_model(c, dev)
+    step = DecoderTrainStep(model, use_cuda_graph=not args.no_graph)
+    feat, gt = synth_inputs(c['B'], c['L'], c['D'], c['V'], c['T'], seed=123 + rank, full_length=True)
+    feat_h, gt_h = feat.pin_memory(), gt.pin_memory()
+    step.stage(feat_h.to(dev), gt_h.to(dev))
+    reducer = GradAllReducer(step, world) if world > 1 else None
+    lib = _lib.load()
+
+    def one_step_resident():
+        loss4 = step.run_resident()
+        if reducer:
+            reducer.allreduce()
+        return loss4
+
+    def barrier():
+        if dist:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # launches per step (counted on an un-graphed step)
+    step.use_cuda_graph = False
+    n0 = lib.alexcap_launch_count(); step.run_resident(); torch.cuda.synchronize()
+    launches_per_step = int(lib.alexcap_launch_count() - n0)
+    step.use_cuda_graph = not args.no_graph
+
+    for _ in range(args.warmup):
+        one_step_resident()
+    barrier()
+    with ClockSampler(local) as clk:
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(args.steps):
+            loss4 = one_step_resident()
+        e.record()
+        barrier()
+    ms = s.elapsed_time(e) / args.steps
+    loss_val = float(loss4[0])
+
+    # end to end: pinned host inputs -> H2D -> forward_train (public API) -> allreduce -> loss D2H, every step
+    def one_step_e2e():
+        step.stage(feat_h, gt_h)             # H2D copies from pinned memory into the static device buffers
+        l4 = one_step_resident()
+        return float(l4[0].item())           # D2H read of the loss
+    for _ in range(3):
+        one_step_e2e()
+    barrier()
+    s2, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s2.record()
+    for _ in range(args.steps):
+        one_step_e2e()
+    e2.record()
+    barrier()
+    ms_e2e = s2.elapsed_time(e2) / args.steps
+
+    t = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
+    if dist:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, ms_e2e = float(t[0]), float(t[1])
+
+    if rank == 0:
+        pk = peaks()
+        total = c['B'] * world
+        line = dict(metric=METRIC, value=round(total / (ms * 1e-3), 1), unit='captions/s', n_gpus=world, steps=args.steps,
+                    warmup=args.warmup, ms_per_step=round(ms, 4), higher_is_better=True, scaling='weak', vs_baseline=None,
+                    dtype='f32', data='synthetic', config=workload_config(c, world), loss=round(loss_val, 5),
+                    cuda_graph=not args.no_graph,
+                    e2e=dict(value=round(total / (ms_e2e * 1e-3), 1), unit='captions/s',
+                             h2d_bytes_per_step=int(feat_h.numel() * 4 + gt_h.numel() * 4), d2h_bytes_per_step=4,
+                             ms_per_step=round(ms_e2e, 4)),
+                    gpu_launches=launches_per_step * args.steps, gpu_launches_per_step=launches_per_step,
+                    clocks=clk.summary())
+        w = algorithmic_work(c)
+        line['gemm_group'] = dict(algorithmic_gflop_per_step=round(w['gemm_flops_step'] / 1e9, 2),
+                                  engine='fp32 CUDA-core tiles (exact fp32, 1e-4 parity)')
+        if c['model'] == 'LSTMwAttentionModel':
+            line['roofline'] = dominant_kernel_roofline(c, dev, pk)
+        if world == 1 and not args.no_cpu_baseline:
+            cb, _, _ = time_cpu_port(c, steps=3, warmup=1, budget_s=25.0)
+            line['cpu_baseline'] = cb
+        print(json.dumps(line), flush=True)
+    if dist:
+        dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+    main()

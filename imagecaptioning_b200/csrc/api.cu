@@ -1,0 +1,376 @@
+// api.cu -- the C ABI of libalexcap_b200.so (include/alexcap.h) and the host-side orchestration of the
+// caption-decoder training step: which kernels run, in which order, over which workspace slices.
+//
+// Structure of one attention training step (reference: AlexCap/LSTMwAttentionModel.py:67-72 driving
+// AlexCap/AttentionLanguageModule.py:62-84 and AlexCap/CustomLoss.py:9-15):
+//   hoisted (once):  targets, mean_L(feat), h0/c0, Ws = W(feat) [reference: recomputed S times], embedding gather,
+//                    Xe = Emb W_ih[:, :E]^T + b_ih + b_hh for all S steps, weight concatenations
+//   per step t:      [q | bpre] = h_{t-1} [W_U ; W_beta]^T      (1 GEMM)
+//                    fused attention step                        (1 kernel)
+//                    gates_t += [gctx_t | h_{t-1}] [W_ih[:,E:] | W_hh]^T   (1 GEMM)
+//                    LSTM pointwise -> h_t, c_t                  (1 kernel)
+//   after the loop:  logits = H_all W_o^T + b_o, CE + gradient, regulariser
+//   reverse loop:    pointwise bwd, dgctx GEMM, fused attention bwd, dh_{t-1} GEMM
+//   after the loop:  every weight gradient as ONE GEMM over K = S*B rows (the "fused dW accumulation"),
+//                    dWs in one pass, embedding scatter-add, init-state gradients.
+#include "api_util.h"
+
+using namespace alexcap;
+
+namespace alexcap {
+char* err_buf() {
+  static thread_local char buf[512] = "";
+  return buf;
+}
+unsigned long long& launch_counter() {
+  static unsigned long long n = 0;
+  return n;
+}
+}  // namespace alexcap
+
+namespace {
+
+// ------------------------------------------------------------------------------------------ attention workspace
+struct AttnWs {
+  int32_t *in_bm, *tgt_bm, *in_tm, *tgt_tm;
+  float *m, *XH, *Call, *Ws, *EmbIn, *DGQ, *QB, *BETA, *CTX, *ALPHA, *DE;
+  float *Wcat, *Wub, *bub, *Wback;
+  float *MASK, *Hd;
+  float *logits, *row_loss, *scal;   // scal: [0]=n_valid [1]=ce_sum [2]=reg
+  float *dHout, *dh_next, *dc, *dgctx, *R, *dwv_part, *dWs, *dEmbIn, *dh0, *dc0, *dm;
+  float *cs_scratch, *reg_scratch;
+  int64_t ldV;
+  size_t bytes;
+};
+
+AttnWs attn_layout(const alexcap_dims* d, void* base, bool with_logits) {
+  AttnWs w;
+  Bump a(base);
+  const int64_t B = d->B, L = d->L, D = d->D, H = d->H, E = d->E, Vp = d->Vp, S = d->S, W5 = 5 * H + D;
+  w.ldV = (Vp + 3) & ~int64_t(3);
+  w.in_bm = a.take<int32_t>(B * S); w.tgt_bm = a.take<int32_t>(B * S);
+  w.in_tm = a.take<int32_t>(B * S); w.tgt_tm = a.take<int32_t>(B * S);
+  w.m = a.take<float>(B * D);
+  w.XH = a.take<float>((S + 1) * B * (D + H));
+  w.Call = a.take<float>((S + 1) * B * H);
+  w.Ws = a.take<float>(B * L * H);
+  w.EmbIn = a.take<float>(S * B * E);
+  w.DGQ = a.take<float>(S * B * W5);
+  w.QB = a.take<float>(S * B * (H + D));
+  w.BETA = a.take<float>(S * B * D);
+  w.CTX = a.take<float>(S * B * D);
+  w.ALPHA = a.take<float>(B * S * L);
+  w.DE = a.take<float>(B * S * L);
+  w.Wcat = a.take<float>(4 * H * (D + H));
+  w.Wub = a.take<float>((H + D) * H);
+  w.bub = a.take<float>(H + D);
+  w.Wback = a.take<float>(W5 * H);
+  const bool drop = d->dropout_p > 0.f;
+  w.MASK = drop ? a.take<float>(S * B * H) : nullptr;
+  w.Hd = drop ? a.take<float>(S * B * H) : nullptr;
+  w.logits = with_logits ? a.take<float>(S * B * w.ldV) : nullptr;
+  w.row_loss = a.take<float>(S * B);
+  w.scal = a.take<float>(64);
+  w.dHout = a.take<float>(S * B * H);
+  w.dh_next = a.take<float>(B * H);
+  w.dc = a.take<float>(B * H);
+  w.dgctx = a.take<float>(B * D);
+  w.R = a.take<float>(B * L);
+  w.dwv_part = a.take<float>(B * H);
+  w.dWs = a.take<float>(B * L * H);
+  w.dEmbIn = a.take<float>(S * B * E);
+  w.dh0 = a.take<float>(B * H);
+  w.dc0 = a.take<float>(B * H);
+  w.dm = a.take<float>(B * D);
+  int64_t maxn = Vp;
+  if (W5 > maxn) maxn = W5;
+  w.cs_scratch = a.take<float>(64 * maxn);
+  w.reg_scratch = a.take<float>(256);
+  w.bytes = a.off + 256;
+  return w;
+}
+
+// ------------------------------------------------------------------------------------------ attention forward core
+int attn_fwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const float* feat, const int32_t* gt,
+                  const float* drop_mask, AttnWs& w, cudaStream_t st) {
+  const int B = d->B, L = d->L, D = d->D, H = d->H, E = d->E, Vp = d->Vp, S = d->S;
+  const int64_t DH = D + H, W5 = 5 * (int64_t)H + D, HD = H + D;
+  const int V = Vp - 3;
+  API_CK(make_target(st, gt, B, S - 1, V + 1, V + 2, w.in_bm, w.tgt_bm, w.in_tm, w.tgt_tm));
+  // initial state (AttentionLanguageModule.py:116-125)
+  API_CK(mean_over_L(st, feat, B, L, D, w.m));
+  API_CK(gemm_f32(st, false, true, B, H, D, 1.f, w.m, D, P->init_h_w, D, w.XH + D, DH, P->init_h_b, nullptr, false, ACT_TANH));
+  API_CK(gemm_f32(st, false, true, B, H, D, 1.f, w.m, D, P->init_c_w, D, w.Call, H, P->init_c_b, nullptr, false, ACT_TANH));
+  // hoisted projections
+  API_CK(gemm_f32(st, false, true, B * L, H, D, 1.f, feat, D, P->att_W_w, D, w.Ws, H, P->att_W_b, nullptr, false, ACT_NONE));
+  API_CK(gather_rows(st, P->emb_w, w.in_tm, S * B, E, w.EmbIn, E));
+  API_CK(gemm_f32(st, false, true, S * B, 4 * H, E, 1.f, w.EmbIn, E, P->lstm_w_ih, E + D, w.DGQ, W5, P->lstm_b_ih,
+                  P->lstm_b_hh, false, ACT_NONE));
+  // concatenated weights: Wcat = [W_ih[:,E:] | W_hh] (4H x (D+H));  Wub = [W_U ; W_beta] ((H+D) x H)
+  API_CK(copy_2d(st, 4 * H, D, P->lstm_w_ih + E, E + D, w.Wcat, DH));
+  API_CK(copy_2d(st, 4 * H, H, P->lstm_w_hh, H, w.Wcat + D, DH));
+  API_CK(cudaMemcpyAsync(w.Wub, P->att_U_w, sizeof(float) * H * H, cudaMemcpyDeviceToDevice, st));
+  API_CK(cudaMemcpyAsync(w.Wub + (int64_t)H * H, P->f_beta_w, sizeof(float) * D * H, cudaMemcpyDeviceToDevice, st));
+  API_CK(cudaMemcpyAsync(w.bub, P->att_U_b, sizeof(float) * H, cudaMemcpyDeviceToDevice, st));
+  API_CK(cudaMemcpyAsync(w.bub + H, P->f_beta_b, sizeof(float) * D, cudaMemcpyDeviceToDevice, st));
+
+  for (int t = 0; t < S; ++t) {                                            // AttentionLanguageModule.py:72
+    float* xh = w.XH + (int64_t)t * B * DH;
+    float* qb = w.QB + (int64_t)t * B * HD;
+    float* g = w.DGQ + (int64_t)t * B * W5;
+    API_CK(gemm_f32(st, false, true, B, H + D, H, 1.f, xh + D, DH, w.Wub, H, qb, HD, w.bub, nullptr, false, ACT_NONE));
+    API_CK(attn_step_fwd(st, B, L, D, H, w.Ws, feat, qb, HD, qb + H, HD, P->att_v_w, w.ALPHA + (int64_t)t * L,
+                         (int64_t)S * L, w.CTX + (int64_t)t * B * D, w.BETA + (int64_t)t * B * D, xh, DH));
+    API_CK(gemm_f32(st, false, true, B, 4 * H, D + H, 1.f, xh, DH, w.Wcat, DH, g, W5, nullptr, nullptr, true, ACT_NONE));
+    API_CK(lstm_pointwise_fwd(st, B, H, g, W5, w.Call + (int64_t)t * B * H, w.Call + (int64_t)(t + 1) * B * H,
+                              xh + (int64_t)B * DH + D, DH, nullptr, 0));
+  }
+  if (d->dropout_p > 0.f) {                                                 // :79 dropout(h)
+    if (drop_mask) API_CK(cudaMemcpyAsync(w.MASK, drop_mask, sizeof(float) * S * B * H, cudaMemcpyDeviceToDevice, st));
+    else API_CK(dropout_mask(st, w.MASK, (int64_t)S * B * H, d->dropout_p, d->seed, d->offset));
+    API_CK(mul_2d(st, S * B, H, w.XH + (int64_t)B * DH + D, DH, w.MASK, H, w.Hd, H));
+  }
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------ attention backward core
+// dHout [S*B,H] (time-major) = d loss / d (h_t before dropout is applied => masked inside if dropout is on).
+int attn_bwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const float* feat,
+                  const float* dalphas, const float* reg_r, const alexcap_attn_params* G, float* dfeat,
+                  AttnWs& w, cudaStream_t st) {
+  const int B = d->B, L = d->L, D = d->D, H = d->H, E = d->E, S = d->S;
+  const int64_t DH = D + H, W5 = 5 * (int64_t)H + D, HD = H + D;
+  const bool need_dfeat = d->need_dfeat && dfeat;
+  // Wback = [W_hh ; W_U ; W_beta]  ((4H + H + D) x H): dh_{t-1} = [dgates | dq | dbpre] Wback in one GEMM
+  API_CK(cudaMemcpyAsync(w.Wback, P->lstm_w_hh, sizeof(float) * 4 * H * H, cudaMemcpyDeviceToDevice, st));
+  API_CK(cudaMemcpyAsync(w.Wback + (int64_t)4 * H * H, P->att_U_w, sizeof(float) * H * H, cudaMemcpyDeviceToDevice, st));
+  API_CK(cudaMemcpyAsync(w.Wback + (int64_t)5 * H * H, P->f_beta_w, sizeof(float) * D * H, cudaMemcpyDeviceToDevice, st));
+  API_CK(fill_f32(st, w.dc, (int64_t)B * H, 0.f));
+  API_CK(fill_f32(st, w.dwv_part, (int64_t)B * H, 0.f));
+  if (need_dfeat) API_CK(fill_f32(st, dfeat, (int64_t)B * L * D, 0.f));
+
+  for (int t = S - 1; t >= 0; --t) {
+    float* g = w.DGQ + (int64_t)t * B * W5;
+    const float* qb = w.QB + (int64_t)t * B * HD;
+    API_CK(lstm_pointwise_bwd(st, B, H, g, W5, w.Call + (int64_t)(t + 1) * B * H, w.Call + (int64_t)t * B * H,
+                              w.dHout + (int64_t)t * B * H, H, w.MASK ? w.MASK + (int64_t)t * B * H : nullptr,
+                              (t == S - 1) ? nullptr : w.dh_next, H, w.dc));
+    // d gctx = dgates W_ih[:, E:]
+    API_CK(gemm_f32(st, false, false, B, D, 4 * H, 1.f, g, W5, P->lstm_w_ih + E, E + D, w.dgctx, D, nullptr, nullptr,
+                    false, ACT_NONE));
+    API_CK(attn_step_bwd(st, B, L, D, H, w.Ws, feat, qb, HD, P->att_v_w, w.ALPHA + (int64_t)t * L, (int64_t)S * L,
+                         w.CTX + (int64_t)t * B * D, w.BETA + (int64_t)t * B * D, w.dgctx, D,
+                         dalphas ? dalphas + (int64_t)t * L : nullptr, (int64_t)S * L, reg_r,
+                         g + 4 * H, W5, g + 5 * H, W5, w.DE + (int64_t)t * L, (int64_t)S * L, w.dwv_part,
+                         need_dfeat ? dfeat : nullptr));
+    // dh_{t-1} = [dgates | dq | dbpre] [W_hh ; W_U ; W_beta]
+    API_CK(gemm_f32(st, false, false, B, H, (int)W5, 1.f, g, W5, w.Wback, H, w.dh_next, H, nullptr, nullptr, false, ACT_NONE));
+  }
+
+  const int SB = S * B;
+  // attention.W : dWs in one pass, then one K = B*L GEMM
+  API_CK(attn_dws(st, B, L, H, S, w.Ws, w.QB, HD, P->att_v_w, w.DE, w.dWs));
+  API_CK(gemm_f32(st, true, false, H, D, B * L, 1.f, w.dWs, H, feat, D, G->att_W_w, D, nullptr, nullptr, false, ACT_NONE));
+  API_CK(col_sum(st, w.dWs, B * L, H, H, G->att_W_b, false, w.cs_scratch));
+  if (need_dfeat)
+    API_CK(gemm_f32(st, false, false, B * L, D, H, 1.f, w.dWs, H, P->att_W_w, D, dfeat, D, nullptr, nullptr, true, ACT_NONE));
+  // lstm weights: dW = dgates_all^T [EmbIn | gctx | h_prev], K = S*B
+  API_CK(gemm_f32(st, true, false, 4 * H, E, SB, 1.f, w.DGQ, W5, w.EmbIn, E, G->lstm_w_ih, E + D, nullptr, nullptr, false, ACT_NONE));
+  API_CK(gemm_f32(st, true, false, 4 * H, D, SB, 1.f, w.DGQ, W5, w.XH, DH, G->lstm_w_ih + E, E + D, nullptr, nullptr, false, ACT_NONE));
+  API_CK(gemm_f32(st, true, false, 4 * H, H, SB, 1.f, w.DGQ, W5, w.XH + D, DH, G->lstm_w_hh, H, nullptr, nullptr, false, ACT_NONE));
+  API_CK(col_sum(st, w.DGQ, SB, 4 * H, W5, G->lstm_b_ih, false, w.cs_scratch));
+  API_CK(cudaMemcpyAsync(G->lstm_b_hh, G->lstm_b_ih, sizeof(float) * 4 * H, cudaMemcpyDeviceToDevice, st));
+  // embedding: d EmbIn = dgates_all W_ih[:, :E], scatter-add by input token (row 0 / pad included: no padding_idx)
+  API_CK(gemm_f32(st, false, false, SB, E, 4 * H, 1.f, w.DGQ, W5, P->lstm_w_ih, E + D, w.dEmbIn, E, nullptr, nullptr, false, ACT_NONE));
+  API_CK(fill_f32(st, G->emb_w, (int64_t)d->Vp * E, 0.f));
+  API_CK(scatter_add_rows(st, w.dEmbIn, E, w.in_tm, SB, E, G->emb_w));
+  // attention.U, f_beta
+  API_CK(gemm_f32(st, true, false, H, H, SB, 1.f, w.DGQ + 4 * H, W5, w.XH + D, DH, G->att_U_w, H, nullptr, nullptr, false, ACT_NONE));
+  API_CK(gemm_f32(st, true, false, D, H, SB, 1.f, w.DGQ + 5 * H, W5, w.XH + D, DH, G->f_beta_w, H, nullptr, nullptr, false, ACT_NONE));
+  API_CK(col_sum(st, w.DGQ + 4 * H, SB, H, W5, G->att_U_b, false, w.cs_scratch));
+  API_CK(col_sum(st, w.DGQ + 5 * H, SB, D, W5, G->f_beta_b, false, w.cs_scratch));
+  // attention.v
+  API_CK(col_sum(st, w.dwv_part, B, H, H, G->att_v_w, false, w.cs_scratch));
+  API_CK(reduce_sum(st, w.DE, B * S * L, G->att_v_b));
+  // init_h / init_c (AttentionLanguageModule.py:116-125)
+  API_CK(tanh_bwd(st, B, H, w.dh_next, H, w.XH + D, DH, w.dh0, H));
+  API_CK(tanh_bwd(st, B, H, w.dc, H, w.Call, H, w.dc0, H));
+  API_CK(gemm_f32(st, true, false, H, D, B, 1.f, w.dh0, H, w.m, D, G->init_h_w, D, nullptr, nullptr, false, ACT_NONE));
+  API_CK(gemm_f32(st, true, false, H, D, B, 1.f, w.dc0, H, w.m, D, G->init_c_w, D, nullptr, nullptr, false, ACT_NONE));
+  API_CK(col_sum(st, w.dh0, B, H, H, G->init_h_b, false, w.cs_scratch));
+  API_CK(col_sum(st, w.dc0, B, H, H, G->init_c_b, false, w.cs_scratch));
+  if (need_dfeat) {
+    API_CK(gemm_f32(st, false, false, B, D, H, 1.f, w.dh0, H, P->init_h_w, D, w.dm, D, nullptr, nullptr, false, ACT_NONE));
+    API_CK(gemm_f32(st, false, false, B, D, H, 1.f, w.dc0, H, P->init_c_w, D, w.dm, D, nullptr, nullptr, true, ACT_NONE));
+    API_CK(add_broadcast_L(st, B, L, D, w.dm, 1.f / (float)L, dfeat));
+  }
+  return 0;
+}
+
+int check_attn_args(const alexcap_dims* d, const alexcap_attn_params* P, const void* feat, const void* ws, size_t ws_bytes,
+                    size_t need) {
+  int rc = check_dims_common(d);
+  if (rc) return rc;
+  if (!P || !feat || !ws) return fail(ALEXCAP_E_BADARG, "NULL params / feat / workspace");
+  if (ws_bytes < need) return fail(ALEXCAP_E_WORKSPACE, "workspace too small (see alexcap_attn_workspace_bytes)");
+  if (!aligned16(feat) || !aligned16(ws)) return fail(ALEXCAP_E_BADARG, "feat / workspace must be 16-byte aligned");
+  return 0;
+}
+
+}  // namespace
+
+// =========================================================================================== exported
+extern "C" {
+
+int alexcap_abi_version(void) { return ALEXCAP_ABI_VERSION; }
+const char* alexcap_last_error(void) { return err_buf(); }
+
+unsigned long long alexcap_launch_count(void) { return launch_counter(); }
+
+int alexcap_device_check(void) {
+  int dev = 0;
+  API_CK(cudaGetDevice(&dev));
+  cudaDeviceProp prop;
+  API_CK(cudaGetDeviceProperties(&prop, dev));
+  if (prop.major != 10) return fail(ALEXCAP_E_UNSUPPORTED, "libalexcap_b200 needs an sm_100 (B200) device; no fallback exists");
+  return 0;
+}
+
+size_t alexcap_attn_workspace_bytes(const alexcap_dims* d) {
+  if (!d) return 0;
+  return attn_layout(d, nullptr, true).bytes;
+}
+
+int alexcap_attn_train_fused(const alexcap_dims* d, const alexcap_attn_params* P, const float* feat, const int32_t* gt,
+                             const alexcap_attn_params* G, float* dfeat, float* loss_out, float* alphas_out,
+                             const float* drop_mask, const float* ce_denominator, void* workspace,
+                             size_t workspace_bytes, void* stream) {
+  if (int rc = check_dims_common(d)) return rc;
+  AttnWs w = attn_layout(d, nullptr, true);
+  if (int rc = check_attn_args(d, P, feat, workspace, workspace_bytes, w.bytes)) return rc;
+  if (!gt || !G || !loss_out) return fail(ALEXCAP_E_BADARG, "NULL gt / grads / loss_out");
+  w = attn_layout(d, workspace, true);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int B = d->B, D = d->D, H = d->H, Vp = d->Vp, S = d->S, L = d->L, SB = S * B;
+  const int64_t DH = D + H;
+  if (int rc = attn_fwd_core(d, P, feat, gt, drop_mask, w, st)) return rc;
+  const float* hout = w.Hd ? w.Hd : w.XH + (int64_t)B * DH + D;
+  const int64_t hld = w.Hd ? H : DH;
+  // vocabulary projection for all steps at once (AttentionLanguageModule.py:79) + CustomCrossEntropyLoss
+  API_CK(gemm_f32(st, false, true, SB, Vp, H, 1.f, hout, hld, P->deep_w, H, w.logits, w.ldV, P->deep_b, nullptr, false, ACT_NONE));
+  API_CK(count_valid(st, w.tgt_tm, SB, d->ignore_index, w.scal));
+  API_CK(ce_rows(st, w.logits, w.tgt_tm, SB, Vp, w.ldV, d->label_smoothing, d->ignore_index,
+                 ce_denominator ? ce_denominator : w.scal, w.row_loss, w.logits));
+  API_CK(reduce_sum(st, w.row_loss, SB, w.scal + 1));
+  const bool reg = d->reg_weight != 0.f;
+  if (reg) API_CK(attn_regulariser(st, B, S, L, d->reg_weight, w.ALPHA, w.R, w.scal + 2, w.reg_scratch));
+  API_CK(finalize_loss(st, w.scal + 1, reg ? w.scal + 2 : nullptr, w.scal, loss_out));
+  if (alphas_out)
+    API_CK(cudaMemcpyAsync(alphas_out, w.ALPHA, sizeof(float) * (size_t)B * S * L, cudaMemcpyDeviceToDevice, st));
+  // vocab backward: dH = dlogits W_o ; dW_o = dlogits^T H ; db_o = colsum(dlogits)
+  API_CK(gemm_f32(st, false, false, SB, H, Vp, 1.f, w.logits, w.ldV, P->deep_w, H, w.dHout, H, nullptr, nullptr, false, ACT_NONE));
+  API_CK(gemm_f32(st, true, false, Vp, H, SB, 1.f, w.logits, w.ldV, hout, hld, G->deep_w, H, nullptr, nullptr, false, ACT_NONE));
+  API_CK(col_sum(st, w.logits, SB, Vp, w.ldV, G->deep_b, false, w.cs_scratch));
+  return attn_bwd_core(d, P, feat, nullptr, reg ? w.R : nullptr, G, dfeat, w, st);
+}
+
+int alexcap_attn_forward(const alexcap_dims* d, const alexcap_attn_params* P, const float* feat, const int32_t* gt,
+                         float* preds, float* alphas, const float* drop_mask, void* workspace, size_t workspace_bytes,
+                         void* stream) {
+  if (int rc = check_dims_common(d)) return rc;
+  AttnWs w = attn_layout(d, nullptr, false);
+  if (int rc = check_attn_args(d, P, feat, workspace, workspace_bytes, w.bytes)) return rc;
+  if (!gt || !preds) return fail(ALEXCAP_E_BADARG, "NULL gt / preds");
+  w = attn_layout(d, workspace, false);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int B = d->B, D = d->D, H = d->H, Vp = d->Vp, S = d->S, L = d->L;
+  const int64_t DH = D + H;
+  if (int rc = attn_fwd_core(d, P, feat, gt, drop_mask, w, st)) return rc;
+  for (int t = 0; t < S; ++t) {   // preds[:, t] = deep_output(dropout(h_t))  (AttentionLanguageModule.py:79-81)
+    const float* h = w.Hd ? w.Hd + (int64_t)t * B * H : w.XH + (int64_t)(t + 1) * B * DH + D;
+    API_CK(gemm_f32(st, false, true, B, Vp, H, 1.f, h, w.Hd ? H : DH, P->deep_w, H, preds + (int64_t)t * Vp, (int64_t)S * Vp,
+                    P->deep_b, nullptr, false, ACT_NONE));
+  }
+  if (alphas)
+    API_CK(cudaMemcpyAsync(alphas, w.ALPHA, sizeof(float) * (size_t)B * S * L, cudaMemcpyDeviceToDevice, st));
+  return 0;
+}
+
+int alexcap_attn_backward(const alexcap_dims* d, const alexcap_attn_params* P, const float* feat, const float* dpreds,
+                          const float* dalphas, const alexcap_attn_params* G, float* dfeat, void* workspace,
+                          size_t workspace_bytes, void* stream) {
+  if (int rc = check_dims_common(d)) return rc;
+  AttnWs w = attn_layout(d, nullptr, false);
+  if (int rc = check_attn_args(d, P, feat, workspace, workspace_bytes, w.bytes)) return rc;
+  if (!G) return fail(ALEXCAP_E_BADARG, "NULL grads");
+  w = attn_layout(d, workspace, false);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int B = d->B, D = d->D, H = d->H, Vp = d->Vp, S = d->S;
+  const int64_t DH = D + H;
+  if (dpreds) {
+    for (int t = 0; t < S; ++t) {
+      const float* h = w.Hd ? w.Hd + (int64_t)t * B * H : w.XH + (int64_t)(t + 1) * B * DH + D;
+      const float* dp = dpreds + (int64_t)t * Vp;
+      API_CK(gemm_f32(st, false, false, B, H, Vp, 1.f, dp, (int64_t)S * Vp, P->deep_w, H, w.dHout + (int64_t)t * B * H, H,
+                      nullptr, nullptr, false, ACT_NONE));
+      API_CK(gemm_f32(st, true, false, Vp, H, B, 1.f, dp, (int64_t)S * Vp, h, w.Hd ? H : DH, G->deep_w, H, nullptr, nullptr,
+                      t > 0, ACT_NONE));
+    }
+    API_CK(col_sum(st, dpreds, B * S, Vp, Vp, G->deep_b, false, w.cs_scratch));
+  } else {
+    API_CK(fill_f32(st, w.dHout, (int64_t)S * B * H, 0.f));
+    API_CK(fill_f32(st, G->deep_w, (int64_t)Vp * H, 0.f));
+    API_CK(fill_f32(st, G->deep_b, Vp, 0.f));
+  }
+  return attn_bwd_core(d, P, feat, dalphas, nullptr, G, dfeat, w, st);
+}
+
+int alexcap_make_target(const int32_t* gt, int32_t* in_tok, int32_t* tgt, int32_t B, int32_t T, int32_t start_token,
+                        int32_t end_token, void* stream) {
+  if (!gt || B <= 0 || T <= 0) return fail(ALEXCAP_E_BADARG, "alexcap_make_target: bad arguments");
+  API_CK(make_target(static_cast<cudaStream_t>(stream), gt, B, T, start_token, end_token, in_tok, tgt, nullptr, nullptr));
+  return 0;
+}
+
+int alexcap_cross_entropy(const float* logits, const int32_t* tgt, int32_t N, int32_t C, int64_t ld, float label_smoothing,
+                          int32_t ignore_index, float* loss_out, float* dlogits, float* scratch, void* stream) {
+  if (!logits || !tgt || !loss_out || !scratch || N <= 0 || C <= 0 || ld < C)
+    return fail(ALEXCAP_E_BADARG, "alexcap_cross_entropy: bad arguments");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // scratch: [0..N) row losses, [N] n_valid
+  API_CK(count_valid(st, tgt, N, ignore_index, scratch + N));
+  API_CK(ce_rows(st, logits, tgt, N, C, ld, label_smoothing, ignore_index, scratch + N, scratch, dlogits));
+  API_CK(reduce_sum(st, scratch, N, loss_out));
+  API_CK(cudaMemcpyAsync(loss_out + 1, scratch + N, sizeof(float), cudaMemcpyDeviceToDevice, st));
+  return 0;
+}
+
+int alexcap_gemm_f32(int32_t transa, int32_t transb, int32_t M, int32_t N, int32_t K, float alpha, const float* A,
+                     int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, const float* bias,
+                     const float* bias2, int32_t accumulate, int32_t act, int32_t engine, void* stream) {
+  if (!A || !B || !C || M <= 0 || N <= 0 || K <= 0) return fail(ALEXCAP_E_BADARG, "alexcap_gemm_f32: bad arguments");
+  if (engine != 0) return fail(ALEXCAP_E_UNSUPPORTED, "alexcap_gemm_f32: engine 1 (tcgen05) not built yet");
+  API_CK(gemm_f32(static_cast<cudaStream_t>(stream), transa != 0, transb != 0, M, N, K, alpha, A, lda, B, ldb, C, ldc, bias,
+                  bias2, accumulate != 0, act));
+  return 0;
+}
+
+int alexcap_attn_step_fwd(int32_t B, int32_t L, int32_t D, int32_t H, const float* Ws, const float* feat, const float* q,
+                          int64_t q_ld, const float* bpre, int64_t bpre_ld, const float* w_v, float* alpha,
+                          int64_t alpha_ld, float* ctx, float* beta, float* gctx, int64_t gctx_ld, void* stream) {
+  API_CK(attn_step_fwd(static_cast<cudaStream_t>(stream), B, L, D, H, Ws, feat, q, q_ld, bpre, bpre_ld, w_v, alpha, alpha_ld,
+                       ctx, beta, gctx, gctx_ld));
+  return 0;
+}
+
+int alexcap_attn_step_bwd(int32_t B, int32_t L, int32_t D, int32_t H, const float* Ws, const float* feat, const float* q,
+                          int64_t q_ld, const float* w_v, const float* alpha, int64_t alpha_ld, const float* ctx,
+                          const float* beta, const float* dgctx, int64_t dgctx_ld, const float* dalpha_ext, int64_t ext_ld,
+                          const float* reg_r, float* dq, int64_t dq_ld, float* dbpre, int64_t dbpre_ld, float* de,
+                          int64_t de_ld, float* dwv_part, float* dfeat, void* stream) {
+  API_CK(attn_step_bwd(static_cast<cudaStream_t>(stream), B, L, D, H, Ws, feat, q, q_ld, w_v, alpha, alpha_ld, ctx, beta,
+                       dgctx, dgctx_ld, dalpha_ext, ext_ld, reg_r, dq, dq_ld, dbpre, dbpre_ld, de, de_ld, dwv_part, dfeat));
+  return 0;
+}
+
+}  // extern "C"

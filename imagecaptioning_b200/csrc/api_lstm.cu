@@ -1,0 +1,316 @@
+// api_lstm.cu -- plain LSTM decoder (AlexCap/LanguageModule.py) behind the C ABI: teacher-forced train step
+// (LanguageModule.py:99-107 driven by AlexCap/LSTMModel.py:70-73) and greedy decoding (:130-150).
+//
+// The reference calls nn.LSTM twice -- first over the L encoded regions to obtain a state, then over the S word
+// embeddings from that state.  That is ONE LSTM over the concatenated (L+S)-step sequence from a zero state, which is
+// how it is run here: the input projection X W_ih^T is hoisted into a single GEMM over all L+S steps and each
+// recurrent step is one [B,H]x[H,4H] GEMM + one pointwise kernel.
+#include "api_util.h"
+
+using namespace alexcap;
+
+namespace {
+
+struct LstmWs {
+  int32_t *in_bm, *tgt_bm, *in_tm, *tgt_tm;
+  float *enc_bm, *In0;
+  float *G[ALEXCAP_MAX_LAYERS], *Hs[ALEXCAP_MAX_LAYERS], *Cs[ALEXCAP_MAX_LAYERS];
+  float *MASK, *Hd, *logits, *row_loss, *scal, *dHout, *dA, *dB, *dh_next, *dc, *dpre_bm, *cs_scratch;
+  int64_t ldV;
+  size_t bytes;
+};
+
+LstmWs lstm_layout(const alexcap_dims* d, void* base, bool with_logits) {
+  LstmWs w;
+  Bump a(base);
+  const int64_t B = d->B, L = d->L, H = d->H, E = d->E, Vp = d->Vp, S = d->S, LT = L + S;
+  const int nl = d->num_layers;
+  w.ldV = (Vp + 3) & ~int64_t(3);
+  w.in_bm = a.take<int32_t>(B * S); w.tgt_bm = a.take<int32_t>(B * S);
+  w.in_tm = a.take<int32_t>(B * S); w.tgt_tm = a.take<int32_t>(B * S);
+  w.enc_bm = a.take<float>(B * L * E);
+  w.In0 = a.take<float>(LT * B * E);
+  for (int l = 0; l < nl; ++l) {
+    w.G[l] = a.take<float>(LT * B * 4 * H);
+    w.Hs[l] = a.take<float>((LT + 1) * B * H);
+    w.Cs[l] = a.take<float>((LT + 1) * B * H);
+  }
+  const bool drop = d->dropout_p > 0.f;
+  w.MASK = drop ? a.take<float>(S * B * H) : nullptr;
+  w.Hd = drop ? a.take<float>(S * B * H) : nullptr;
+  w.logits = with_logits ? a.take<float>(S * B * w.ldV) : nullptr;
+  w.row_loss = a.take<float>(S * B);
+  w.scal = a.take<float>(64);
+  w.dHout = a.take<float>(S * B * H);
+  const int64_t wmax = E > H ? E : H;
+  w.dA = a.take<float>(LT * B * wmax);
+  w.dB = a.take<float>(LT * B * wmax);
+  w.dh_next = a.take<float>(B * H);
+  w.dc = a.take<float>(B * H);
+  w.dpre_bm = a.take<float>(B * L * E);
+  int64_t maxn = Vp > 4 * H ? Vp : 4 * H;
+  if (E > maxn) maxn = E;
+  w.cs_scratch = a.take<float>(64 * maxn);
+  w.bytes = a.off + 256;
+  return w;
+}
+
+int check_lstm_args(const alexcap_dims* d, const alexcap_lstm_params* P, const void* feat, const void* ws, size_t ws_bytes,
+                    size_t need) {
+  if (!P || !feat || !ws) return fail(ALEXCAP_E_BADARG, "NULL params / feat / workspace");
+  if (ws_bytes < need) return fail(ALEXCAP_E_WORKSPACE, "workspace too small (see alexcap_lstm_workspace_bytes)");
+  if (!aligned16(feat) || !aligned16(ws)) return fail(ALEXCAP_E_BADARG, "feat / workspace must be 16-byte aligned");
+  return 0;
+}
+
+int check_lstm_dims(const alexcap_dims* d) {
+  if (int rc = check_dims_common(d)) return rc;
+  if (d->num_layers < 1 || d->num_layers > ALEXCAP_MAX_LAYERS) return fail(ALEXCAP_E_BADARG, "num_layers out of range");
+  return 0;
+}
+
+// one LSTM layer over LT steps (hoisted input GEMM + recurrence)
+int run_layer_fwd(const alexcap_dims* d, const float* in, int I, const float* w_ih, const float* w_hh, const float* b_ih,
+                  const float* b_hh, float* G, float* Hs, float* Cs, int LT, cudaStream_t st) {
+  const int B = d->B, H = d->H;
+  API_CK(gemm_f32(st, false, true, LT * B, 4 * H, I, 1.f, in, I, w_ih, I, G, 4 * H, b_ih, b_hh, false, ACT_NONE));
+  API_CK(fill_f32(st, Hs, (int64_t)B * H, 0.f));
+  API_CK(fill_f32(st, Cs, (int64_t)B * H, 0.f));
+  for (int t = 0; t < LT; ++t) {
+    float* g = G + (int64_t)t * B * 4 * H;
+    if (t > 0)   // h_{-1} = 0
+      API_CK(gemm_f32(st, false, true, B, 4 * H, H, 1.f, Hs + (int64_t)t * B * H, H, w_hh, H, g, 4 * H, nullptr, nullptr, true,
+                      ACT_NONE));
+    API_CK(lstm_pointwise_fwd(st, B, H, g, 4 * H, Cs + (int64_t)t * B * H, Cs + (int64_t)(t + 1) * B * H,
+                              Hs + (int64_t)(t + 1) * B * H, H, nullptr, 0));
+  }
+  return 0;
+}
+
+int lstm_fwd_core(const alexcap_dims* d, const alexcap_lstm_params* P, const float* feat, const int32_t* gt,
+                  const float* drop_mask, LstmWs& w, cudaStream_t st) {
+  const int B = d->B, L = d->L, D = d->D, H = d->H, E = d->E, S = d->S, LT = L + S, V = d->Vp - 3;
+  API_CK(make_target(st, gt, B, S - 1, V + 1, V + 2, w.in_bm, w.tgt_bm, w.in_tm, w.tgt_tm));
+  // image_encoder: ReLU(Linear) on every region (LanguageModule.py:35-37,103), then to time-major
+  API_CK(gemm_f32(st, false, true, B * L, E, D, 1.f, feat, D, P->enc_w, D, w.enc_bm, E, P->enc_b, nullptr, false, ACT_RELU));
+  API_CK(permute_01(st, B, L, E, w.enc_bm, w.In0));
+  API_CK(gather_rows(st, P->emb_w, w.in_tm, S * B, E, w.In0 + (int64_t)L * B * E, E));   // :102
+  for (int l = 0; l < d->num_layers; ++l) {
+    const float* in = (l == 0) ? w.In0 : w.Hs[l - 1] + (int64_t)B * H;
+    if (int rc = run_layer_fwd(d, in, l == 0 ? E : H, P->w_ih[l], P->w_hh[l], P->b_ih[l], P->b_hh[l], w.G[l], w.Hs[l], w.Cs[l],
+                               LT, st))
+      return rc;
+  }
+  if (d->dropout_p > 0.f) {   // rnn.drop (:48,:106)
+    if (drop_mask) API_CK(cudaMemcpyAsync(w.MASK, drop_mask, sizeof(float) * S * B * H, cudaMemcpyDeviceToDevice, st));
+    else API_CK(dropout_mask(st, w.MASK, (int64_t)S * B * H, d->dropout_p, d->seed, d->offset));
+    API_CK(mul_2d(st, S * B, H, w.Hs[d->num_layers - 1] + (int64_t)(1 + L) * B * H, H, w.MASK, H, w.Hd, H));
+  }
+  return 0;
+}
+
+const float* top_out(const alexcap_dims* d, const LstmWs& w) {
+  return w.Hd ? w.Hd : w.Hs[d->num_layers - 1] + (int64_t)(1 + d->L) * d->B * d->H;
+}
+
+int lstm_bwd_core(const alexcap_dims* d, const alexcap_lstm_params* P, const float* feat, const alexcap_lstm_params* G,
+                  float* dfeat, LstmWs& w, cudaStream_t st) {
+  const int B = d->B, L = d->L, D = d->D, H = d->H, E = d->E, S = d->S, LT = L + S, nl = d->num_layers;
+  float* dOut = nullptr;       // d loss / d (outputs of layer l), all LT steps, for l < top
+  float* bufs[2] = {w.dA, w.dB};
+  for (int l = nl - 1; l >= 0; --l) {
+    const bool top = (l == nl - 1);
+    const int I = (l == 0) ? E : H;
+    const float* in = (l == 0) ? w.In0 : w.Hs[l - 1] + (int64_t)B * H;
+    API_CK(fill_f32(st, w.dc, (int64_t)B * H, 0.f));
+    for (int t = LT - 1; t >= 0; --t) {
+      float* g = w.G[l] + (int64_t)t * B * 4 * H;
+      const float* dh_a = nullptr; const float* mask = nullptr;
+      if (top) {
+        if (t >= L) {
+          dh_a = w.dHout + (int64_t)(t - L) * B * H;
+          mask = w.MASK ? w.MASK + (int64_t)(t - L) * B * H : nullptr;
+        }
+      } else {
+        dh_a = dOut + (int64_t)t * B * H;
+      }
+      API_CK(lstm_pointwise_bwd(st, B, H, g, 4 * H, w.Cs[l] + (int64_t)(t + 1) * B * H, w.Cs[l] + (int64_t)t * B * H, dh_a, H,
+                                mask, (t == LT - 1) ? nullptr : w.dh_next, H, w.dc));
+      if (t > 0)
+        API_CK(gemm_f32(st, false, false, B, H, 4 * H, 1.f, g, 4 * H, P->w_hh[l], H, w.dh_next, H, nullptr, nullptr, false,
+                        ACT_NONE));
+    }
+    // weight gradients as single K = LT*B GEMMs
+    API_CK(gemm_f32(st, true, false, 4 * H, I, LT * B, 1.f, w.G[l], 4 * H, in, I, G->w_ih[l], I, nullptr, nullptr, false, ACT_NONE));
+    API_CK(gemm_f32(st, true, false, 4 * H, H, LT * B, 1.f, w.G[l], 4 * H, w.Hs[l], H, G->w_hh[l], H, nullptr, nullptr, false,
+                    ACT_NONE));
+    API_CK(col_sum(st, w.G[l], LT * B, 4 * H, 4 * H, G->b_ih[l], false, w.cs_scratch));
+    API_CK(cudaMemcpyAsync(G->b_hh[l], G->b_ih[l], sizeof(float) * 4 * H, cudaMemcpyDeviceToDevice, st));
+    float* dIn = bufs[l & 1];
+    API_CK(gemm_f32(st, false, false, LT * B, I, 4 * H, 1.f, w.G[l], 4 * H, P->w_ih[l], I, dIn, I, nullptr, nullptr, false,
+                    ACT_NONE));
+    dOut = dIn;
+  }
+  // dOut = d In0 [LT,B,E]: words -> embedding rows, regions -> image encoder
+  API_CK(fill_f32(st, G->emb_w, (int64_t)d->Vp * E, 0.f));
+  API_CK(scatter_add_rows(st, dOut + (int64_t)L * B * E, E, w.in_tm, S * B, E, G->emb_w));
+  API_CK(relu_bwd(st, (int64_t)L * B * E, dOut, w.In0, dOut));
+  API_CK(permute_01(st, L, B, E, dOut, w.dpre_bm));
+  API_CK(gemm_f32(st, true, false, E, D, B * L, 1.f, w.dpre_bm, E, feat, D, G->enc_w, D, nullptr, nullptr, false, ACT_NONE));
+  API_CK(col_sum(st, w.dpre_bm, B * L, E, E, G->enc_b, false, w.cs_scratch));
+  if (d->need_dfeat && dfeat)
+    API_CK(gemm_f32(st, false, false, B * L, D, E, 1.f, w.dpre_bm, E, P->enc_w, D, dfeat, D, nullptr, nullptr, false, ACT_NONE));
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t alexcap_lstm_workspace_bytes(const alexcap_dims* d) {
+  if (!d || d->num_layers < 1 || d->num_layers > ALEXCAP_MAX_LAYERS) return 0;
+  return lstm_layout(d, nullptr, true).bytes;
+}
+
+int alexcap_lstm_train_fused(const alexcap_dims* d, const alexcap_lstm_params* P, const float* feat, const int32_t* gt,
+                             const alexcap_lstm_params* G, float* dfeat, float* loss_out, const float* drop_mask,
+                             const float* ce_denominator, void* workspace, size_t workspace_bytes, void* stream) {
+  if (int rc = check_lstm_dims(d)) return rc;
+  LstmWs w = lstm_layout(d, nullptr, true);
+  if (int rc = check_lstm_args(d, P, feat, workspace, workspace_bytes, w.bytes)) return rc;
+  if (!gt || !G || !loss_out) return fail(ALEXCAP_E_BADARG, "NULL gt / grads / loss_out");
+  w = lstm_layout(d, workspace, true);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int B = d->B, H = d->H, Vp = d->Vp, S = d->S, SB = S * B;
+  if (int rc = lstm_fwd_core(d, P, feat, gt, drop_mask, w, st)) return rc;
+  const float* hout = top_out(d, w);
+  API_CK(gemm_f32(st, false, true, SB, Vp, H, 1.f, hout, H, P->out_w, H, w.logits, w.ldV, P->out_b, nullptr, false, ACT_NONE));
+  API_CK(count_valid(st, w.tgt_tm, SB, d->ignore_index, w.scal));
+  API_CK(ce_rows(st, w.logits, w.tgt_tm, SB, Vp, w.ldV, d->label_smoothing, d->ignore_index,
+                 ce_denominator ? ce_denominator : w.scal, w.row_loss, w.logits));
+  API_CK(reduce_sum(st, w.row_loss, SB, w.scal + 1));
+  API_CK(finalize_loss(st, w.scal + 1, nullptr, w.scal, loss_out));
+  API_CK(gemm_f32(st, false, false, SB, H, Vp, 1.f, w.logits, w.ldV, P->out_w, H, w.dHout, H, nullptr, nullptr, false, ACT_NONE));
+  API_CK(gemm_f32(st, true, false, Vp, H, SB, 1.f, w.logits, w.ldV, hout, H, G->out_w, H, nullptr, nullptr, false, ACT_NONE));
+  API_CK(col_sum(st, w.logits, SB, Vp, w.ldV, G->out_b, false, w.cs_scratch));
+  return lstm_bwd_core(d, P, feat, G, dfeat, w, st);
+}
+
+int alexcap_lstm_forward(const alexcap_dims* d, const alexcap_lstm_params* P, const float* feat, const int32_t* gt,
+                         float* preds, const float* drop_mask, void* workspace, size_t workspace_bytes, void* stream) {
+  if (int rc = check_lstm_dims(d)) return rc;
+  LstmWs w = lstm_layout(d, nullptr, false);
+  if (int rc = check_lstm_args(d, P, feat, workspace, workspace_bytes, w.bytes)) return rc;
+  if (!gt || !preds) return fail(ALEXCAP_E_BADARG, "NULL gt / preds");
+  w = lstm_layout(d, workspace, false);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int B = d->B, H = d->H, Vp = d->Vp, S = d->S;
+  if (int rc = lstm_fwd_core(d, P, feat, gt, drop_mask, w, st)) return rc;
+  const float* hout = top_out(d, w);
+  for (int t = 0; t < S; ++t)   // preds[B,S,Vp] batch-major like the reference (LanguageModule.py:106-107)
+    API_CK(gemm_f32(st, false, true, B, Vp, H, 1.f, hout + (int64_t)t * B * H, H, P->out_w, H, preds + (int64_t)t * Vp,
+                    (int64_t)S * Vp, P->out_b, nullptr, false, ACT_NONE));
+  return 0;
+}
+
+int alexcap_lstm_backward(const alexcap_dims* d, const alexcap_lstm_params* P, const float* feat, const float* dpreds,
+                          const alexcap_lstm_params* G, float* dfeat, void* workspace, size_t workspace_bytes, void* stream) {
+  if (int rc = check_lstm_dims(d)) return rc;
+  LstmWs w = lstm_layout(d, nullptr, false);
+  if (int rc = check_lstm_args(d, P, feat, workspace, workspace_bytes, w.bytes)) return rc;
+  if (!G || !dpreds) return fail(ALEXCAP_E_BADARG, "NULL grads / dpreds");
+  w = lstm_layout(d, workspace, false);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int B = d->B, H = d->H, Vp = d->Vp, S = d->S;
+  const float* hout = top_out(d, w);
+  for (int t = 0; t < S; ++t) {
+    const float* dp = dpreds + (int64_t)t * Vp;
+    API_CK(gemm_f32(st, false, false, B, H, Vp, 1.f, dp, (int64_t)S * Vp, P->out_w, H, w.dHout + (int64_t)t * B * H, H, nullptr,
+                    nullptr, false, ACT_NONE));
+    API_CK(gemm_f32(st, true, false, Vp, H, B, 1.f, dp, (int64_t)S * Vp, hout + (int64_t)t * B * H, H, G->out_w, H, nullptr, nullptr,
+                    t > 0, ACT_NONE));
+  }
+  API_CK(col_sum(st, dpreds, B * S, Vp, Vp, G->out_b, false, w.cs_scratch));
+  return lstm_bwd_core(d, P, feat, G, dfeat, w, st);
+}
+
+// ------------------------------------------------------------------------------------------ greedy decoding
+struct LstmDecWs {
+  float *enc_bm, *seqA, *seqB, *Gimg, *Himg, *Cimg, *hst, *cst, *x, *g, *logits;
+  int32_t *tok, *done;
+  size_t bytes;
+};
+static LstmDecWs lstm_dec_layout(const alexcap_dims* d, void* base) {
+  LstmDecWs w;
+  Bump a(base);
+  const int64_t B = d->B, L = d->L, H = d->H, E = d->E, nl = d->num_layers;
+  const int64_t ldV = (d->Vp + 3) & ~int64_t(3);
+  w.enc_bm = a.take<float>(B * L * E);
+  w.seqA = a.take<float>(L * B * E);                 // layer-0 input sequence (time-major)
+  w.seqB = a.take<float>(L * B * H);                 // inputs of layers >= 1
+  w.Gimg = a.take<float>(L * B * 4 * H);
+  w.Himg = a.take<float>((L + 1) * B * H);
+  w.Cimg = a.take<float>((L + 1) * B * H);
+  w.hst = a.take<float>(nl * 2 * B * H);             // [layer][pingpong][B,H]
+  w.cst = a.take<float>(nl * 2 * B * H);
+  w.x = a.take<float>(B * E);
+  w.g = a.take<float>(B * 4 * H);
+  w.logits = a.take<float>(B * ldV);
+  w.tok = a.take<int32_t>(B);
+  w.done = a.take<int32_t>(16);
+  w.bytes = a.off + 256;
+  return w;
+}
+
+size_t alexcap_lstm_decode_workspace_bytes(const alexcap_dims* d) {
+  if (!d || d->num_layers < 1 || d->num_layers > ALEXCAP_MAX_LAYERS) return 0;
+  return lstm_dec_layout(d, nullptr).bytes;
+}
+
+int alexcap_lstm_decode_greedy(const alexcap_dims* d, const alexcap_lstm_params* P, const float* feat, int64_t* ids,
+                               void* workspace, size_t workspace_bytes, void* stream) {
+  if (int rc = check_lstm_dims(d)) return rc;
+  if (int rc = check_lstm_args(d, P, feat, workspace, workspace_bytes, lstm_dec_layout(d, nullptr).bytes)) return rc;
+  if (!ids) return fail(ALEXCAP_E_BADARG, "NULL ids");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int B = d->B, L = d->L, D = d->D, H = d->H, E = d->E, Vp = d->Vp, S = d->S, nl = d->num_layers, V = Vp - 3;
+  const int64_t ldV = (Vp + 3) & ~int64_t(3);
+  LstmDecWs w = lstm_dec_layout(d, workspace);
+  float *enc_bm = w.enc_bm, *seqA = w.seqA, *seqB = w.seqB, *Gimg = w.Gimg, *Himg = w.Himg, *Cimg = w.Cimg;
+  float *hst = w.hst, *cst = w.cst, *x = w.x, *g = w.g, *logits = w.logits;
+  int32_t *tok = w.tok, *done = w.done;
+  // image pass (LanguageModule.py:133,135): state of every layer after the L region steps
+  API_CK(gemm_f32(st, false, true, B * L, E, D, 1.f, feat, D, P->enc_w, D, enc_bm, E, P->enc_b, nullptr, false, ACT_RELU));
+  API_CK(permute_01(st, B, L, E, enc_bm, seqA));
+  for (int l = 0; l < nl; ++l) {
+    const float* in = (l == 0) ? seqA : seqB;
+    if (int rc = run_layer_fwd(d, in, l == 0 ? E : H, P->w_ih[l], P->w_hh[l], P->b_ih[l], P->b_hh[l], Gimg, Himg, Cimg, L, st))
+      return rc;
+    API_CK(cudaMemcpyAsync(hst + (int64_t)(l * 2) * B * H, Himg + (int64_t)L * B * H, sizeof(float) * B * H, cudaMemcpyDeviceToDevice, st));
+    API_CK(cudaMemcpyAsync(cst + (int64_t)(l * 2) * B * H, Cimg + (int64_t)L * B * H, sizeof(float) * B * H, cudaMemcpyDeviceToDevice, st));
+    if (l + 1 < nl)   // this layer's outputs are the next layer's inputs
+      API_CK(cudaMemcpyAsync(seqB, Himg + (int64_t)B * H, sizeof(float) * L * B * H, cudaMemcpyDeviceToDevice, st));
+  }
+  API_CK(fill_i32(st, tok, B, V + 1));
+  API_CK(fill_i32(st, done, 1, 0));
+  API_CK(cudaMemsetAsync(ids, 0, sizeof(int64_t) * (size_t)B * S, st));
+  for (int t = 0; t < S; ++t) {   // :138-149
+    const int cur = t & 1, nxt = cur ^ 1;
+    API_CK(gather_rows(st, P->emb_w, tok, B, E, x, E));
+    const float* in = x; int I = E;
+    for (int l = 0; l < nl; ++l) {
+      float* hc = hst + (int64_t)(l * 2 + cur) * B * H; float* hn = hst + (int64_t)(l * 2 + nxt) * B * H;
+      float* cc = cst + (int64_t)(l * 2 + cur) * B * H; float* cn = cst + (int64_t)(l * 2 + nxt) * B * H;
+      API_CK(gemm_f32(st, false, true, B, 4 * H, I, 1.f, in, I, P->w_ih[l], I, g, 4 * H, P->b_ih[l], P->b_hh[l], false, ACT_NONE));
+      API_CK(gemm_f32(st, false, true, B, 4 * H, H, 1.f, hc, H, P->w_hh[l], H, g, 4 * H, nullptr, nullptr, true, ACT_NONE));
+      API_CK(lstm_pointwise_fwd(st, B, H, g, 4 * H, cc, cn, hn, H, nullptr, 0));
+      in = hn; I = H;
+    }
+    API_CK(gemm_f32(st, false, true, B, Vp, H, 1.f, in, H, P->out_w, H, logits, ldV, P->out_b, nullptr, false, ACT_NONE));
+    API_CK(argmax_rows(st, logits, B, Vp, ldV, tok));
+    API_CK(greedy_commit(st, B, S, 0, t, V + 2, tok, nullptr, ids, nullptr, done));
+  }
+  return 0;
+}
+
+}  // extern "C"

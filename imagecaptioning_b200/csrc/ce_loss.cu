@@ -1,0 +1,88 @@
+// ce_loss.cu -- CustomCrossEntropyLoss (AlexCap/CustomLoss.py:7-14):
+//   nn.CrossEntropyLoss(reduction='mean', ignore_index=0, label_smoothing=0.1) over [N, C] logits,
+// value and gradient in one pass over each row:
+//   loss_row = (1-eps) * (lse - x[y]) + eps * (lse - mean_c x[c]),   only rows with y != ignore_index
+//   dlogits  = (softmax(x) - (1-eps) * onehot(y) - eps/C) * [y != ignore] / denom
+#include "common.cuh"
+#include "kernels.h"
+
+namespace alexcap {
+
+__global__ void __launch_bounds__(256) count_valid_kernel(const int32_t* __restrict__ tgt, int N, int ignore_index,
+                                                          float* __restrict__ out) {
+  __shared__ float scratch[40];
+  float c = 0.f;
+  for (int i = threadIdx.x; i < N; i += blockDim.x) c += (tgt[i] != ignore_index) ? 1.f : 0.f;
+  c = block_sum(c, scratch);
+  if (threadIdx.x == 0) out[0] = c;
+}
+cudaError_t count_valid(cudaStream_t st, const int32_t* tgt, int N, int ignore_index, float* n_valid_out) {
+  ALEXCAP_NOTE_LAUNCH(); count_valid_kernel<<<1, 256, 0, st>>>(tgt, N, ignore_index, n_valid_out);
+  return cudaGetLastError();
+}
+
+constexpr int CE_THREADS = 512;
+__global__ void __launch_bounds__(CE_THREADS) ce_rows_kernel(const float* __restrict__ logits,
+                                                             const int32_t* __restrict__ tgt, int C, int64_t ld,
+                                                             float eps, int ignore_index,
+                                                             const float* __restrict__ denom,
+                                                             float* __restrict__ row_loss, float* dlogits) {
+  __shared__ float scratch[40];
+  const int row = blockIdx.x;
+  const float* x = logits + (int64_t)row * ld;
+  float* dx = dlogits ? dlogits + (int64_t)row * ld : nullptr;
+  const int y = tgt[row];
+  if (y == ignore_index) {   // ignored row: no loss, zero gradient
+    if (threadIdx.x == 0) row_loss[row] = 0.f;
+    if (dx) for (int c = threadIdx.x; c < C; c += CE_THREADS) dx[c] = 0.f;
+    return;
+  }
+  const float xy = x[y];   // read before any (possibly aliasing) gradient write
+  float mx = -INFINITY, sx = 0.f;
+  for (int c = threadIdx.x; c < C; c += CE_THREADS) {
+    const float v = x[c];
+    mx = fmaxf(mx, v);
+    sx += v;
+  }
+  mx = block_max(mx, scratch);
+  sx = block_sum(sx, scratch);
+  float se = 0.f;
+  for (int c = threadIdx.x; c < C; c += CE_THREADS) se += expf(x[c] - mx);
+  se = block_sum(se, scratch);
+  const float lse = mx + logf(se);
+  const float inv_d = 1.f / fmaxf(denom[0], 1.f);
+  if (threadIdx.x == 0) {
+    const float nll = lse - xy;
+    const float smooth = lse - sx / (float)C;
+    row_loss[row] = ((1.f - eps) * nll + eps * smooth) * inv_d;
+  }
+  if (dx) {
+    const float u = eps / (float)C;
+    for (int c = threadIdx.x; c < C; c += CE_THREADS) {
+      float g = expf(x[c] - lse) - u;
+      if (c == y) g -= (1.f - eps);
+      dx[c] = g * inv_d;
+    }
+  }
+}
+
+cudaError_t ce_rows(cudaStream_t st, const float* logits, const int32_t* tgt, int N, int C, int64_t ld, float eps,
+                    int ignore_index, const float* denom, float* row_loss, float* dlogits) {
+  if (N <= 0) return cudaSuccess;
+  ALEXCAP_NOTE_LAUNCH(); ce_rows_kernel<<<N, CE_THREADS, 0, st>>>(logits, tgt, C, ld, eps, ignore_index, denom, row_loss, dlogits);
+  return cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(1024) reduce_sum_kernel(const float* __restrict__ x, int n, float* __restrict__ out) {
+  __shared__ float scratch[40];
+  float acc = 0.f;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) acc += x[i];
+  acc = block_sum(acc, scratch);
+  if (threadIdx.x == 0) out[0] = acc;
+}
+cudaError_t reduce_sum(cudaStream_t st, const float* x, int n, float* out) {
+  ALEXCAP_NOTE_LAUNCH(); reduce_sum_kernel<<<1, 1024, 0, st>>>(x, n, out);
+  return cudaGetLastError();
+}
+
+}  // namespace alexcap

@@ -1,0 +1,81 @@
+// common.cuh -- shared device helpers for libalexcap_b200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <math.h>
+
+namespace alexcap {
+
+#define ACK(expr)                                  \
+  do {                                             \
+    cudaError_t e__ = (expr);                      \
+    if (e__ != cudaSuccess) return e__;            \
+  } while (0)
+
+#define ALEXCAP_LAUNCH_CHECK() ACK(cudaGetLastError())
+
+// Number of kernel launches this library has enqueued (host-side counter; bench.py reports it as gpu_launches).
+unsigned long long& launch_counter();
+#define ALEXCAP_NOTE_LAUNCH() (++alexcap::launch_counter())
+
+static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+static inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }
+static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// Block-wide reductions; `scratch` holds >= 33 floats of shared memory. All threads get the result.
+// blockDim.x must be a multiple of 32 (<= 1024).  Contains two __syncthreads().
+__device__ __forceinline__ float block_sum(float v, float* scratch) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  v = warp_sum(v);
+  if (lane == 0) scratch[warp] = v;
+  __syncthreads();
+  if (warp == 0) {
+    float r = (lane < nwarp) ? scratch[lane] : 0.f;
+    r = warp_sum(r);
+    if (lane == 0) scratch[32] = r;
+  }
+  __syncthreads();
+  float out = scratch[32];
+  __syncthreads();
+  return out;
+}
+__device__ __forceinline__ float block_max(float v, float* scratch) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  v = warp_max(v);
+  if (lane == 0) scratch[warp] = v;
+  __syncthreads();
+  if (warp == 0) {
+    float r = (lane < nwarp) ? scratch[lane] : -INFINITY;
+    r = warp_max(r);
+    if (lane == 0) scratch[32] = r;
+  }
+  __syncthreads();
+  float out = scratch[32];
+  __syncthreads();
+  return out;
+}
+
+__device__ __forceinline__ float sigmoid_f(float x) { return 1.f / (1.f + expf(-x)); }
+
+__device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }
+
+__device__ __forceinline__ float4 f4_zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }
+__device__ __forceinline__ void f4_fma(float4& acc, float s, const float4& v) {
+  acc.x = fmaf(s, v.x, acc.x); acc.y = fmaf(s, v.y, acc.y); acc.z = fmaf(s, v.z, acc.z); acc.w = fmaf(s, v.w, acc.w);
+}
+__device__ __forceinline__ void f4_add(float4& acc, const float4& v) {
+  acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+}
+
+}  // namespace alexcap

@@ -1,0 +1,94 @@
+// kernels.h -- host-side launchers of the sm_100a kernels (internal; the public surface is include/alexcap.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace alexcap {
+
+enum Act { ACT_NONE = 0, ACT_TANH = 1, ACT_RELU = 2 };
+
+// C[M,N] = act(alpha * op(A) op(B) + bias + bias2) (+ C).  See alexcap_gemm_f32 in alexcap.h.
+cudaError_t gemm_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, float alpha,
+                     const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
+                     const float* bias, const float* bias2, bool accumulate, int act);
+
+// ---- attention (attention.cu)
+cudaError_t attn_step_fwd(cudaStream_t st, int B, int L, int D, int H, const float* Ws, const float* feat,
+                          const float* q, int64_t q_ld, const float* bpre, int64_t bpre_ld, const float* wv,
+                          float* alpha, int64_t alpha_ld, float* ctx, float* beta, float* gctx, int64_t gctx_ld,
+                          int rows_per_image = 1);
+cudaError_t attn_step_bwd(cudaStream_t st, int B, int L, int D, int H, const float* Ws, const float* feat,
+                          const float* q, int64_t q_ld, const float* wv, const float* alpha, int64_t alpha_ld,
+                          const float* ctx, const float* beta, const float* dgctx, int64_t dgctx_ld,
+                          const float* dalpha_ext, int64_t ext_ld, const float* reg_r,
+                          float* dq, int64_t dq_ld, float* dbpre, int64_t dbpre_ld, float* de, int64_t de_ld,
+                          float* dwv_part, float* dfeat);
+// dWs[b,l,h] = wv[h] * sum_t de[b,t,l] * (1 - tanh^2(Ws[b,l,h] + q[t,b,h]));  q: [S][B] rows of stride q_ld,
+// de: [B][S][L].
+cudaError_t attn_dws(cudaStream_t st, int B, int L, int H, int S, const float* Ws, const float* q, int64_t q_ld,
+                     const float* wv, const float* de, float* dWs);
+// resid = 1 - sum_t alpha[b,t,l]; r[b,l] = -2*w*resid/(B*L); loss_reg = w*mean(resid^2) -> *loss_reg
+cudaError_t attn_regulariser(cudaStream_t st, int B, int S, int L, float weight, const float* alphas, float* r,
+                             float* loss_reg, float* scratch);
+
+// ---- LSTM pointwise (lstm_pointwise.cu)
+// gates [B,4H] (row stride g_ld) pre-activations -> activations in place; c_prev [B,H] -> c_out [B,H];
+// h written to h_out (row stride h_ld) and optionally h_out2 (row stride h2_ld).
+cudaError_t lstm_pointwise_fwd(cudaStream_t st, int B, int H, float* gates, int64_t g_ld, const float* c_prev,
+                               float* c_out, float* h_out, int64_t h_ld, float* h_out2, int64_t h2_ld);
+// gates hold activations (i,f,g,o) -> overwritten with d(pre-activations).  dh = dh_a + dh_b (either may be NULL;
+// dh_a scaled by mask_a if given).  dc_io [B,H]: in = dc from step t+1, out = dc for step t-1.
+cudaError_t lstm_pointwise_bwd(cudaStream_t st, int B, int H, float* gates, int64_t g_ld, const float* c_t,
+                               const float* c_prev, const float* dh_a, int64_t dha_ld, const float* mask_a,
+                               const float* dh_b, int64_t dhb_ld, float* dc_io);
+
+// ---- loss (ce_loss.cu)
+cudaError_t count_valid(cudaStream_t st, const int32_t* tgt, int N, int ignore_index, float* n_valid_out);
+// per-row masked label-smoothed CE; denom (device float) = divisor; row_loss[N]; dlogits may alias logits.
+cudaError_t ce_rows(cudaStream_t st, const float* logits, const int32_t* tgt, int N, int C, int64_t ld, float eps,
+                    int ignore_index, const float* denom, float* row_loss, float* dlogits);
+// out[0] = sum(x[0..n)) (deterministic single-block tree)
+cudaError_t reduce_sum(cudaStream_t st, const float* x, int n, float* out);
+
+// ---- misc (misc.cu)
+cudaError_t make_target(cudaStream_t st, const int32_t* gt, int B, int T, int start_tok, int end_tok,
+                        int32_t* in_bm, int32_t* tgt_bm, int32_t* in_tm, int32_t* tgt_tm);
+cudaError_t mean_over_L(cudaStream_t st, const float* feat, int B, int L, int D, float* m);
+// out[r,:] = table[idx[r],:]   (rows of `width` floats; out row stride out_ld)
+cudaError_t gather_rows(cudaStream_t st, const float* table, const int32_t* idx, int rows, int width, float* out,
+                        int64_t out_ld);
+// table[idx[r],:] += src[r,:]   (atomic)
+cudaError_t scatter_add_rows(cudaStream_t st, const float* src, int64_t src_ld, const int32_t* idx, int rows,
+                             int width, float* table);
+// out[n] (+)= sum_m X[m*ld + n]     scratch: >= 64*N floats
+cudaError_t col_sum(cudaStream_t st, const float* X, int M, int N, int64_t ld, float* out, bool accumulate,
+                    float* scratch);
+// y = dy * (1 - t*t)  elementwise (tanh backward), n elements, strides for 2-D views
+cudaError_t tanh_bwd(cudaStream_t st, int rows, int cols, const float* dy, int64_t dy_ld, const float* t, int64_t t_ld,
+                     float* out, int64_t out_ld);
+cudaError_t relu_bwd(cudaStream_t st, int64_t n, const float* dy, const float* pre, float* out);
+// dst[r, :cols] = src[r, :cols] with strides
+cudaError_t copy_2d(cudaStream_t st, int rows, int cols, const float* src, int64_t src_ld, float* dst, int64_t dst_ld);
+cudaError_t fill_f32(cudaStream_t st, float* p, int64_t n, float v);
+// dfeat[b,l,:] += dm[b,:] * scale
+cudaError_t add_broadcast_L(cudaStream_t st, int B, int L, int D, const float* dm, float scale, float* dfeat);
+// out[i] = a[i] * b[i]
+cudaError_t mul_2d(cudaStream_t st, int rows, int cols, const float* a, int64_t a_ld, const float* b, int64_t b_ld,
+                   float* out, int64_t out_ld);
+// mask[i] = (philox(seed, offset+i) >= p) ? 1/(1-p) : 0
+cudaError_t dropout_mask(cudaStream_t st, float* mask, int64_t n, float p, uint64_t seed, uint64_t offset);
+// loss_out = {a+b, a, b, n_valid}
+cudaError_t finalize_loss(cudaStream_t st, const float* ce_sum, const float* reg, const float* n_valid, float* loss_out);
+
+// ---- decode (decode.cu)
+// per row argmax over logits[B,C] (row stride ld); first max wins (torch.argmax semantics)
+cudaError_t argmax_rows(cudaStream_t st, const float* logits, int B, int C, int64_t ld, int32_t* out_tok);
+cudaError_t fill_i32(cudaStream_t st, int32_t* p, int64_t n, int32_t v);
+// greedy bookkeeping (AttentionLanguageModule.py:108-112): unless *done, ids[b,t] = tok[b] and (optionally)
+// alphas[b,t,:] = alpha_step[b,:]; then *done |= all(tok == end_tok).  No host sync.
+cudaError_t greedy_commit(cudaStream_t st, int B, int S, int L, int t, int end_tok, const int32_t* tok,
+                          const float* alpha_step, int64_t* ids, float* alphas, int32_t* done);
+// dst[a,b,:] = src[b,a,:]  (src [nb,na,w] -> dst [na,nb,w])
+cudaError_t permute_01(cudaStream_t st, int nb, int na, int w, const float* src, float* dst);
+
+}  // namespace alexcap

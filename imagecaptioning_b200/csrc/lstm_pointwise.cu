@@ -1,0 +1,80 @@
+// lstm_pointwise.cu -- LSTM cell pointwise math, forward and backward (gate order i,f,g,o as torch.nn.LSTMCell /
+// nn.LSTM: AlexCap/AttentionLanguageModule.py:58,78 ; AlexCap/LanguageModule.py:46,104-105).
+// The gate pre-activations come from the GEMMs; these kernels are elementwise and negligible in bytes.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace alexcap {
+
+__global__ void __launch_bounds__(256) lstm_fwd_kernel(int B, int H, float* __restrict__ gates, int64_t g_ld,
+                                                       const float* __restrict__ c_prev, float* __restrict__ c_out,
+                                                       float* __restrict__ h_out, int64_t h_ld,
+                                                       float* __restrict__ h_out2, int64_t h2_ld) {
+  const int H4 = H >> 2;
+  const int64_t n = (int64_t)B * H4;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int b = (int)(i / H4), c = (int)(i % H4);
+    float4* g = reinterpret_cast<float4*>(gates + (int64_t)b * g_ld);
+    float4 gi = g[c], gf = g[H4 + c], gg = g[2 * H4 + c], go = g[3 * H4 + c];
+    const float4 cp = reinterpret_cast<const float4*>(c_prev + (int64_t)b * H)[c];
+    float4 cn, hn;
+#define CELL(x)                                                        \
+    gi.x = sigmoid_f(gi.x); gf.x = sigmoid_f(gf.x); gg.x = tanhf(gg.x); go.x = sigmoid_f(go.x); \
+    cn.x = fmaf(gf.x, cp.x, gi.x * gg.x); hn.x = go.x * tanhf(cn.x);
+    CELL(x) CELL(y) CELL(z) CELL(w)
+#undef CELL
+    g[c] = gi; g[H4 + c] = gf; g[2 * H4 + c] = gg; g[3 * H4 + c] = go;
+    reinterpret_cast<float4*>(c_out + (int64_t)b * H)[c] = cn;
+    reinterpret_cast<float4*>(h_out + (int64_t)b * h_ld)[c] = hn;
+    if (h_out2) reinterpret_cast<float4*>(h_out2 + (int64_t)b * h2_ld)[c] = hn;
+  }
+}
+
+cudaError_t lstm_pointwise_fwd(cudaStream_t st, int B, int H, float* gates, int64_t g_ld, const float* c_prev,
+                               float* c_out, float* h_out, int64_t h_ld, float* h_out2, int64_t h2_ld) {
+  if ((H & 3) || (g_ld & 3) || (h_ld & 3) || (h_out2 && (h2_ld & 3))) return cudaErrorInvalidValue;
+  const int64_t n = (int64_t)B * (H / 4);
+  const int blocks = (int)((n + 255) / 256);
+  ALEXCAP_NOTE_LAUNCH(); lstm_fwd_kernel<<<blocks, 256, 0, st>>>(B, H, gates, g_ld, c_prev, c_out, h_out, h_ld, h_out2, h2_ld);
+  return cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(256) lstm_bwd_kernel(int B, int H, float* __restrict__ gates, int64_t g_ld,
+                                                       const float* __restrict__ c_t, const float* __restrict__ c_prev,
+                                                       const float* __restrict__ dh_a, int64_t dha_ld,
+                                                       const float* __restrict__ mask_a,
+                                                       const float* __restrict__ dh_b, int64_t dhb_ld,
+                                                       float* __restrict__ dc_io) {
+  const int64_t n = (int64_t)B * H;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int b = (int)(i / H), h = (int)(i % H);
+    float* g = gates + (int64_t)b * g_ld;
+    const float gi = g[h], gf = g[H + h], gg = g[2 * H + h], go = g[3 * H + h];
+    float dh = 0.f;
+    if (dh_a) {
+      float v = dh_a[(int64_t)b * dha_ld + h];
+      if (mask_a) v *= mask_a[(int64_t)b * H + h];
+      dh += v;
+    }
+    if (dh_b) dh += dh_b[(int64_t)b * dhb_ld + h];
+    const float tc = tanhf(c_t[(int64_t)b * H + h]);
+    const float d_o = dh * tc * go * (1.f - go);
+    const float dc = dc_io[(int64_t)b * H + h] + dh * go * (1.f - tc * tc);
+    const float d_i = dc * gg * gi * (1.f - gi);
+    const float d_f = dc * c_prev[(int64_t)b * H + h] * gf * (1.f - gf);
+    const float d_g = dc * gi * (1.f - gg * gg);
+    dc_io[(int64_t)b * H + h] = dc * gf;
+    g[h] = d_i; g[H + h] = d_f; g[2 * H + h] = d_g; g[3 * H + h] = d_o;
+  }
+}
+
+cudaError_t lstm_pointwise_bwd(cudaStream_t st, int B, int H, float* gates, int64_t g_ld, const float* c_t,
+                               const float* c_prev, const float* dh_a, int64_t dha_ld, const float* mask_a,
+                               const float* dh_b, int64_t dhb_ld, float* dc_io) {
+  const int64_t n = (int64_t)B * H;
+  const int blocks = (int)((n + 255) / 256);
+  ALEXCAP_NOTE_LAUNCH(); lstm_bwd_kernel<<<blocks, 256, 0, st>>>(B, H, gates, g_ld, c_t, c_prev, dh_a, dha_ld, mask_a, dh_b, dhb_ld, dc_io);
+  return cudaGetLastError();
+}
+
+}  // namespace alexcap

@@ -1,0 +1,256 @@
+// misc.cu -- the small kernels around the hot path: get_target, embedding gather / scatter-add, reductions,
+// dropout mask, elementwise backward helpers.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace alexcap {
+
+// get_target (AlexCap/AttentionLanguageModule.py:197-212, AlexCap/LanguageModule.py:113-128): both variants, written
+// batch-major [B,S] (the reference layout) and time-major [S,B] (what the per-step kernels index).
+// The reference runs a Python double loop with one device sync per element; this is one thread per caption.
+__global__ void make_target_kernel(const int32_t* __restrict__ gt, int B, int T, int start_tok, int end_tok,
+                                   int32_t* in_bm, int32_t* tgt_bm, int32_t* in_tm, int32_t* tgt_tm) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  const int S = T + 1;
+  bool placed = false;
+  for (int t = 0; t < S; ++t) {
+    const int in_v = (t == 0) ? start_tok : gt[(int64_t)b * T + t - 1];
+    int tg = (t < T) ? gt[(int64_t)b * T + t] : 0;
+    if (t >= 1 && !placed && tg == 0) { tg = end_tok; placed = true; }   // first 0 at index >= 1 becomes END
+    if (in_bm) in_bm[(int64_t)b * S + t] = in_v;
+    if (tgt_bm) tgt_bm[(int64_t)b * S + t] = tg;
+    if (in_tm) in_tm[(int64_t)t * B + b] = in_v;
+    if (tgt_tm) tgt_tm[(int64_t)t * B + b] = tg;
+  }
+}
+cudaError_t make_target(cudaStream_t st, const int32_t* gt, int B, int T, int start_tok, int end_tok,
+                        int32_t* in_bm, int32_t* tgt_bm, int32_t* in_tm, int32_t* tgt_tm) {
+  if (B <= 0) return cudaSuccess;
+  ALEXCAP_NOTE_LAUNCH(); make_target_kernel<<<ceil_div(B, 128), 128, 0, st>>>(gt, B, T, start_tok, end_tok, in_bm, tgt_bm, in_tm, tgt_tm);
+  return cudaGetLastError();
+}
+
+// mean over regions (AttentionLanguageModule.py:117)
+__global__ void __launch_bounds__(256) mean_L_kernel(const float* __restrict__ feat, int L, int D, float* __restrict__ m) {
+  const int b = blockIdx.y, D4 = D >> 2;
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= D4) return;
+  const float4* p = reinterpret_cast<const float4*>(feat) + (int64_t)b * L * D4 + c;
+  float4 acc = f4_zero();
+#pragma unroll 4
+  for (int l = 0; l < L; ++l) f4_add(acc, ldg4(p + (int64_t)l * D4));
+  const float inv = 1.f / (float)L;
+  reinterpret_cast<float4*>(m)[(int64_t)b * D4 + c] = make_float4(acc.x * inv, acc.y * inv, acc.z * inv, acc.w * inv);
+}
+cudaError_t mean_over_L(cudaStream_t st, const float* feat, int B, int L, int D, float* m) {
+  if (D & 3) return cudaErrorInvalidValue;
+  const int threads = (D / 4 >= 256) ? 256 : 64;
+  dim3 grid(ceil_div(D / 4, threads), B);
+  ALEXCAP_NOTE_LAUNCH(); mean_L_kernel<<<grid, threads, 0, st>>>(feat, L, D, m);
+  return cudaGetLastError();
+}
+
+// embedding lookup (AttentionLanguageModule.py:69, LanguageModule.py:102)
+__global__ void __launch_bounds__(128) gather_rows_kernel(const float* __restrict__ table, const int32_t* __restrict__ idx,
+                                                          int width4, float* __restrict__ out, int64_t out_ld) {
+  const int r = blockIdx.x;
+  const float4* src = reinterpret_cast<const float4*>(table) + (int64_t)idx[r] * width4;
+  float4* dst = reinterpret_cast<float4*>(out + (int64_t)r * out_ld);
+  for (int c = threadIdx.x; c < width4; c += blockDim.x) dst[c] = ldg4(src + c);
+}
+cudaError_t gather_rows(cudaStream_t st, const float* table, const int32_t* idx, int rows, int width, float* out,
+                        int64_t out_ld) {
+  if ((width & 3) || (out_ld & 3)) return cudaErrorInvalidValue;
+  if (rows <= 0) return cudaSuccess;
+  ALEXCAP_NOTE_LAUNCH(); gather_rows_kernel<<<rows, 128, 0, st>>>(table, idx, width / 4, out, out_ld);
+  return cudaGetLastError();
+}
+
+// embedding backward: index_put_(accumulate=True)
+__global__ void __launch_bounds__(128) scatter_add_kernel(const float* __restrict__ src, int64_t src_ld,
+                                                          const int32_t* __restrict__ idx, int width,
+                                                          float* __restrict__ table) {
+  const int r = blockIdx.x;
+  float* dst = table + (int64_t)idx[r] * width;
+  const float* s = src + (int64_t)r * src_ld;
+  for (int c = threadIdx.x; c < width; c += blockDim.x) atomicAdd(dst + c, s[c]);
+}
+cudaError_t scatter_add_rows(cudaStream_t st, const float* src, int64_t src_ld, const int32_t* idx, int rows,
+                             int width, float* table) {
+  if (rows <= 0) return cudaSuccess;
+  ALEXCAP_NOTE_LAUNCH(); scatter_add_kernel<<<rows, 128, 0, st>>>(src, src_ld, idx, width, table);
+  return cudaGetLastError();
+}
+
+// column sums (bias gradients): two deterministic stages through scratch[nsplit][N]
+constexpr int CS_SPLIT = 64;
+__global__ void __launch_bounds__(256) col_sum_part_kernel(const float* __restrict__ X, int M, int N, int64_t ld,
+                                                           float* __restrict__ part) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  const int s = blockIdx.y;
+  const int rows_per = (M + CS_SPLIT - 1) / CS_SPLIT;
+  const int m0 = s * rows_per, m1 = min(M, m0 + rows_per);
+  float acc = 0.f;
+  for (int m = m0; m < m1; ++m) acc += __ldg(X + (int64_t)m * ld + n);
+  part[(int64_t)s * N + n] = acc;
+}
+__global__ void __launch_bounds__(256) col_sum_final_kernel(const float* __restrict__ part, int N, float* __restrict__ out,
+                                                            int accumulate) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  float acc = 0.f;
+  for (int s = 0; s < CS_SPLIT; ++s) acc += part[(int64_t)s * N + n];
+  out[n] = accumulate ? out[n] + acc : acc;
+}
+cudaError_t col_sum(cudaStream_t st, const float* X, int M, int N, int64_t ld, float* out, bool accumulate,
+                    float* scratch) {
+  if (N <= 0) return cudaSuccess;
+  dim3 grid(ceil_div(N, 256), CS_SPLIT);
+  ALEXCAP_NOTE_LAUNCH(); col_sum_part_kernel<<<grid, 256, 0, st>>>(X, M, N, ld, scratch);
+  ALEXCAP_LAUNCH_CHECK();
+  ALEXCAP_NOTE_LAUNCH(); col_sum_final_kernel<<<ceil_div(N, 256), 256, 0, st>>>(scratch, N, out, accumulate ? 1 : 0);
+  return cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(256) tanh_bwd_kernel(int rows, int cols, const float* __restrict__ dy, int64_t dy_ld,
+                                                       const float* __restrict__ t, int64_t t_ld, float* __restrict__ out,
+                                                       int64_t out_ld) {
+  const int64_t n = (int64_t)rows * cols;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int r = (int)(i / cols), c = (int)(i % cols);
+    const float tv = t[(int64_t)r * t_ld + c];
+    out[(int64_t)r * out_ld + c] = dy[(int64_t)r * dy_ld + c] * (1.f - tv * tv);
+  }
+}
+cudaError_t tanh_bwd(cudaStream_t st, int rows, int cols, const float* dy, int64_t dy_ld, const float* t, int64_t t_ld,
+                     float* out, int64_t out_ld) {
+  const int64_t n = (int64_t)rows * cols;
+  if (n <= 0) return cudaSuccess;
+  ALEXCAP_NOTE_LAUNCH(); tanh_bwd_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>(rows, cols, dy, dy_ld, t, t_ld, out, out_ld);
+  return cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(256) relu_bwd_kernel(int64_t n, const float* __restrict__ dy,
+                                                       const float* __restrict__ y, float* __restrict__ out) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = (y[i] > 0.f) ? dy[i] : 0.f;
+}
+cudaError_t relu_bwd(cudaStream_t st, int64_t n, const float* dy, const float* y, float* out) {
+  if (n <= 0) return cudaSuccess;
+  const int blocks = (int)(((n + 255) / 256 < 4096) ? (n + 255) / 256 : 4096);
+  ALEXCAP_NOTE_LAUNCH(); relu_bwd_kernel<<<blocks, 256, 0, st>>>(n, dy, y, out);
+  return cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(256) copy_2d_kernel(int rows, int cols, const float* __restrict__ src, int64_t src_ld,
+                                                      float* __restrict__ dst, int64_t dst_ld) {
+  const int64_t n = (int64_t)rows * cols;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int r = (int)(i / cols), c = (int)(i % cols);
+    dst[(int64_t)r * dst_ld + c] = src[(int64_t)r * src_ld + c];
+  }
+}
+cudaError_t copy_2d(cudaStream_t st, int rows, int cols, const float* src, int64_t src_ld, float* dst, int64_t dst_ld) {
+  const int64_t n = (int64_t)rows * cols;
+  if (n <= 0) return cudaSuccess;
+  const int blocks = (int)(((n + 255) / 256 < 8192) ? (n + 255) / 256 : 8192);
+  ALEXCAP_NOTE_LAUNCH(); copy_2d_kernel<<<blocks, 256, 0, st>>>(rows, cols, src, src_ld, dst, dst_ld);
+  return cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(256) fill_kernel(float* __restrict__ p, int64_t n, float v) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = v;
+}
+cudaError_t fill_f32(cudaStream_t st, float* p, int64_t n, float v) {
+  if (n <= 0) return cudaSuccess;
+  if (v == 0.f) return cudaMemsetAsync(p, 0, n * sizeof(float), st);
+  const int blocks = (int)(((n + 255) / 256 < 8192) ? (n + 255) / 256 : 8192);
+  ALEXCAP_NOTE_LAUNCH(); fill_kernel<<<blocks, 256, 0, st>>>(p, n, v);
+  return cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(256) add_bcast_L_kernel(int L, int D, const float* __restrict__ dm, float scale,
+                                                          float* __restrict__ dfeat, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int d = (int)(i % D);
+    const int64_t b = i / ((int64_t)L * D);
+    dfeat[i] += dm[b * D + d] * scale;
+  }
+}
+cudaError_t add_broadcast_L(cudaStream_t st, int B, int L, int D, const float* dm, float scale, float* dfeat) {
+  const int64_t n = (int64_t)B * L * D;
+  if (n <= 0) return cudaSuccess;
+  const int blocks = (int)(((n + 255) / 256 < 8192) ? (n + 255) / 256 : 8192);
+  ALEXCAP_NOTE_LAUNCH(); add_bcast_L_kernel<<<blocks, 256, 0, st>>>(L, D, dm, scale, dfeat, n);
+  return cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(256) mul_2d_kernel(int rows, int cols, const float* __restrict__ a, int64_t a_ld,
+                                                     const float* __restrict__ b, int64_t b_ld, float* __restrict__ out,
+                                                     int64_t out_ld) {
+  const int64_t n = (int64_t)rows * cols;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int r = (int)(i / cols), c = (int)(i % cols);
+    out[(int64_t)r * out_ld + c] = a[(int64_t)r * a_ld + c] * b[(int64_t)r * b_ld + c];
+  }
+}
+cudaError_t mul_2d(cudaStream_t st, int rows, int cols, const float* a, int64_t a_ld, const float* b, int64_t b_ld,
+                   float* out, int64_t out_ld) {
+  const int64_t n = (int64_t)rows * cols;
+  if (n <= 0) return cudaSuccess;
+  const int blocks = (int)(((n + 255) / 256 < 8192) ? (n + 255) / 256 : 8192);
+  ALEXCAP_NOTE_LAUNCH(); mul_2d_kernel<<<blocks, 256, 0, st>>>(rows, cols, a, a_ld, b, b_ld, out, out_ld);
+  return cudaGetLastError();
+}
+
+// Philox4x32-10 counter-based generator (Salmon et al. 2011) for the dropout mask of AttentionLanguageModule.py:79.
+// Bit-exact agreement with torch's own Philox stream is not a goal; tests inject explicit masks.
+__device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
+  const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+  for (int i = 0; i < 10; ++i) {
+    const uint32_t hi0 = __umulhi(M0, ctr.x), lo0 = M0 * ctr.x;
+    const uint32_t hi1 = __umulhi(M1, ctr.z), lo1 = M1 * ctr.z;
+    ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
+    key.x += W0; key.y += W1;
+  }
+  return ctr;
+}
+__global__ void __launch_bounds__(256) dropout_mask_kernel(float* __restrict__ mask, int64_t n, float p, float scale,
+                                                           uint64_t seed, uint64_t offset) {
+  const int64_t n4 = (n + 3) / 4;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    const uint64_t c = offset + (uint64_t)i;
+    const uint4 r = philox4x32_10(make_uint4((uint32_t)c, (uint32_t)(c >> 32), 0u, 0u),
+                                  make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
+    const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int64_t e = i * 4 + j;
+      if (e < n) {
+        const float u = (float)(rr[j] >> 8) * (1.0f / 16777216.0f);   // [0,1)
+        mask[e] = (u >= p) ? scale : 0.f;
+      }
+    }
+  }
+}
+cudaError_t dropout_mask(cudaStream_t st, float* mask, int64_t n, float p, uint64_t seed, uint64_t offset) {
+  if (n <= 0) return cudaSuccess;
+  const int64_t n4 = (n + 3) / 4;
+  const int blocks = (int)(((n4 + 255) / 256 < 8192) ? (n4 + 255) / 256 : 8192);
+  ALEXCAP_NOTE_LAUNCH(); dropout_mask_kernel<<<blocks, 256, 0, st>>>(mask, n, p, 1.f / (1.f - p), seed, offset);
+  return cudaGetLastError();
+}
+
+__global__ void finalize_loss_kernel(const float* ce_sum, const float* reg, const float* n_valid, float* out) {
+  const float a = ce_sum ? ce_sum[0] : 0.f, b = reg ? reg[0] : 0.f;
+  out[0] = a + b; out[1] = a; out[2] = b; out[3] = n_valid ? n_valid[0] : 0.f;
+}
+cudaError_t finalize_loss(cudaStream_t st, const float* ce_sum, const float* reg, const float* n_valid, float* loss_out) {
+  ALEXCAP_NOTE_LAUNCH(); finalize_loss_kernel<<<1, 1, 0, st>>>(ce_sum, reg, n_valid, loss_out);
+  return cudaGetLastError();
+}
+
+}  // namespace alexcap

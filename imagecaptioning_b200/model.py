@@ -1,0 +1,165 @@
+"""DecoderTrainStep -- the decoder half of AlexCapModel.forward_train as ONE native call.
+
+Reference contract (AlexCap/LSTMwAttentionModel.py:48-74, AlexCap/LSTMModel.py:53-74): forward_train computes
+    loss = crit(llm(features, gt), llm.get_target(gt, make_target=True)) [+ ((1 - alphas.sum(1))**2).mean()]
+calls loss.backward() itself and returns the loss; the caller then clips and steps (train_LSTMwAttention.py:85-109).
+Here the same contract is served by alexcap_attn_train_fused / alexcap_lstm_train_fused: no logits or autograd
+tape are materialised on the Python side, gradients land in `.grad`.
+
+Optionally the whole call is captured once into a CUDA graph (static input buffers) and replayed: the step is a
+chain of ~150 small launches whose launch latency otherwise rivals the kernel time at batch 128.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import functional as F_
+from .modules import Decoder, LanguageModel, _f32c
+
+
+class DecoderTrainStep:
+    def __init__(self, llm, use_cuda_graph: bool = False, need_dfeat: bool = False):
+        if not isinstance(llm, (Decoder, LanguageModel)):
+            raise TypeError('llm must be an imagecaptioning_b200 Decoder or LanguageModel')
+        self.llm = llm
+        self.is_attn = isinstance(llm, Decoder)
+        self.use_cuda_graph = use_cuda_graph
+        self.need_dfeat = need_dfeat
+        self.eval_mode = False
+        self.ce_denominator = None          # device float tensor: global N_valid / world (data parallel), or None
+        self._key = None
+        self._graph = None
+        self.last_alphas = None
+        self.dfeat = None
+
+    # -- reference API ---------------------------------------------------------------------------------
+    def set_eval(self, value: bool):
+        """AlexCapModel.set_eval (LSTMwAttentionModel.py:43-44): eval_mode => loss only, no backward."""
+        self.eval_mode = value
+
+    def clip_gradient(self, norm):
+        torch.nn.utils.clip_grad_norm_(self.llm.parameters(), max_norm=norm)
+
+    # -- internals --------------------------------------------------------------------------------------
+    def _prepare(self, feat, gt):
+        key = (tuple(feat.shape), tuple(gt.shape), feat.device, self.llm.training, self.need_dfeat)
+        if key == self._key:
+            return
+        self._key, self._graph = key, None
+        dev = feat.device
+        F_.ensure_device(dev)
+        self._params = self.llm.param_list()
+        for p in self._params:
+            if p.dtype != torch.float32 or not p.is_contiguous() or p.device != dev:
+                raise F_._lib.AlexcapError('parameters must be contiguous float32 tensors on the features device')
+        # one flat fp32 gradient buffer, slices 16-byte aligned, vocab projection first (it is final first)
+        order = sorted(range(len(self._params)), key=lambda i: 0 if self._is_vocab(i) else 1)
+        sizes = [(self._params[i].numel() + 3) // 4 * 4 for i in order]
+        self._flat_grads = torch.zeros(sum(sizes), dtype=torch.float32, device=dev)
+        self._grads = [None] * len(self._params)
+        off = 0
+        self._vocab_elems = 0
+        for i, n in zip(order, sizes):
+            self._grads[i] = self._flat_grads[off:off + self._params[i].numel()].view_as(self._params[i])
+            off += n
+            if self._is_vocab(i):
+                self._vocab_elems = off
+        self._dims = self.llm._dims(feat, gt, need_dfeat=self.need_dfeat)
+        nbytes = F_.attn_workspace_bytes(self._dims) if self.is_attn else F_.lstm_workspace_bytes(self._dims)
+        self._ws = F_.workspace(nbytes, dev)
+        self._loss = torch.zeros(4, dtype=torch.float32, device=dev)
+        self._feat = torch.empty_like(feat)
+        self._gt = torch.empty_like(gt)
+        self.dfeat = torch.empty_like(feat) if self.need_dfeat else None
+        self._alphas = None
+
+    def _launch(self):
+        d = self._dims
+        if d.dropout_p > 0:   # fresh mask every step (Philox counter advances)
+            d.offset += 1 << 32
+        mask = self.llm._drop_mask_override
+        if self.is_attn:
+            F_.attn_train_fused(d, self._params, self._feat, self._gt, self._grads, self._ws, dfeat=self.dfeat,
+                                loss_out=self._loss, alphas_out=self._alphas, drop_mask=mask,
+                                ce_denominator=self.ce_denominator)
+        else:
+            P = self.llm._struct(self._params)
+            G = self.llm._struct(self._grads)
+            F_.lstm_train_fused(d, P, self._feat, self._gt, G, self._ws, dfeat=self.dfeat, loss_out=self._loss,
+                                drop_mask=mask, ce_denominator=self.ce_denominator)
+
+    def run_resident(self):
+        """One step on the inputs already staged in the static device buffers (bench: inputs resident in HBM)."""
+        if self.use_cuda_graph and self._dims.dropout_p == 0:
+            if self._graph is None:
+                s = torch.cuda.Stream()
+                s.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(s):
+                    self._launch()           # warm-up outside capture (cudaFuncSetAttribute etc.)
+                torch.cuda.current_stream().wait_stream(s)
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    self._launch()
+                self._graph = g
+            self._graph.replay()
+        else:
+            self._launch()
+        return self._loss
+
+    def stage(self, features, gt_labels):
+        feat = features.detach()
+        if feat.dtype != torch.float32:
+            feat = feat.float()
+        gt = gt_labels.to(torch.int32)
+        if feat.device.type != 'cuda':
+            raise F_._lib.AlexcapError('imagecaptioning_b200 has no CPU path: features must be on a CUDA device')
+        self._prepare(feat, gt)
+        self._feat.copy_(feat, non_blocking=True)
+        self._gt.copy_(gt, non_blocking=True)
+
+    def forward_train(self, features, gt_labels):
+        """features [B,L,D] (the CNN grid after permute/view, LSTMwAttentionModel.py:64-66), gt_labels [B,T] int.
+        Returns the scalar loss tensor (device); parameter .grad fields are ACCUMULATED into, like loss.backward()."""
+        if self.eval_mode:
+            return self.forward_eval(features, gt_labels)
+        self.stage(features, gt_labels)
+        loss4 = self.run_resident()
+        for p, g in zip(self._params, self._grads):
+            if p.requires_grad:
+                if p.grad is None:
+                    p.grad = g.clone()
+                else:
+                    p.grad.add_(g)
+        return loss4[0]
+
+    @torch.no_grad()
+    def forward_eval(self, features, gt_labels):
+        """eval_mode branch (LSTMwAttentionModel.py:50-60): loss only, through the materialising forward."""
+        feat = _f32c(features)
+        from .modules import CustomCrossEntropyLoss
+        if self.is_attn:
+            preds, alphas = self.llm.forward(feat, gt_labels)
+            tgt = self.llm.get_target(gt_labels, make_target=True)
+            loss = CustomCrossEntropyLoss()(preds, tgt)
+            return loss + ((1 - alphas.sum(1)) ** 2).mean()
+        preds = self.llm.forward(feat, gt_labels)
+        return CustomCrossEntropyLoss()(preds, self.llm.get_target(gt_labels, make_target=True))
+
+    def _is_vocab(self, i):
+        names = F_._lib.ATTN_STATE_NAMES if self.is_attn else self.llm.param_names()
+        return names[i].startswith('deep_output.') or names[i].startswith('rnn.linear.')
+
+    def grad_buckets(self, bucket_elems: int = 8 << 20):
+        """Contiguous slices of the flat gradient buffer: [vocab projection] + ~32 MB chunks of the rest."""
+        out = [self._flat_grads[:self._vocab_elems]]
+        n = self._flat_grads.numel()
+        o = self._vocab_elems
+        while o < n:
+            out.append(self._flat_grads[o:min(n, o + bucket_elems)])
+            o += bucket_elems
+        return out
+
+    # convenience for tests
+    def grads_by_name(self):
+        names = F_._lib.ATTN_STATE_NAMES if self.is_attn else self.llm.param_names()
+        return dict(zip(names, self._grads))

@@ -1,0 +1,213 @@
+/* alexcap.h -- C ABI of libalexcap_b200.so: the B200-native (sm_100a) caption-decoder hot path of
+ * AlexIMOVI/ImageCaptioning (AlexCap LSTM and attention-LSTM decoders + CustomCrossEntropyLoss).
+ *
+ * The reference is pure Python/PyTorch and has no FFI; the boundary it exposes is the nn.Module
+ * surface of AlexCap/LanguageModule.py, AlexCap/AttentionLanguageModule.py and AlexCap/CustomLoss.py.
+ * Each entry point below names the reference interface it replaces (paths relative to the reference
+ * repository root).  The Python mirror of that surface lives in imagecaptioning_b200/modules.py and
+ * binds this header with ctypes (imagecaptioning_b200/_lib.py); INTEGRATION.md shows the stub.
+ *
+ * Conventions
+ *   - plain pointers + sizes only; every buffer is a DEVICE buffer owned by the caller (torch);
+ *     the library never allocates or frees device memory and keeps no pointer after return.
+ *   - all work is enqueued on `stream` (a cudaStream_t passed as void*), asynchronously, with no
+ *     device-wide synchronisation: a call is capturable into a CUDA graph.
+ *   - return 0 on success; <0 on failure (ALEXCAP_E_*), message via alexcap_last_error().
+ *   - row-major contiguous tensors; weights in nn.Linear layout [out,in]; LSTM gate blocks stacked
+ *     i,f,g,o along dim 0 (torch.nn.LSTMCell / nn.LSTM); fp32 master parameters and fp32 gradients.
+ *   - token ids are int32; 0 = padding/ignore, START = V+1, END = V+2, classes Vp = V+3
+ *     (AlexCap/AttentionLanguageModule.py:43-44, AlexCap/my_model_preprocess.py:115-134).
+ *   - H, D, E must be multiples of 4 (128-bit loads); pointers 16-byte aligned.
+ *   - no CPU fallback: a device that is not sm_100 fails with ALEXCAP_E_UNSUPPORTED.
+ */
+#ifndef ALEXCAP_H_
+#define ALEXCAP_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ALEXCAP_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define ALEXCAP_API __attribute__((visibility("default")))
+#else
+#define ALEXCAP_API
+#endif
+
+#define ALEXCAP_E_BADARG      (-1)
+#define ALEXCAP_E_UNSUPPORTED (-2)
+#define ALEXCAP_E_CUDA        (-3)
+#define ALEXCAP_E_WORKSPACE   (-4)
+
+#define ALEXCAP_F32  0
+#define ALEXCAP_BF16 1   /* bf16 activations / tensor-core operands, fp32 accumulate + fp32 master weights */
+
+typedef struct alexcap_dims {
+  int32_t B, L, D, H, E, Vp, S;   /* batch, regions, feature dim, hidden, embed, classes V+3, steps T+1 */
+  int32_t num_layers;              /* plain LSTM only (nn.LSTM num_layers); ignored by the attention decoder */
+  int32_t dtype;                   /* ALEXCAP_F32 | ALEXCAP_BF16 : arithmetic type of the GEMM operands */
+  int32_t need_dfeat;              /* 1: also produce d loss / d features (CNN fine-tuning) */
+  int32_t ignore_index;            /* CustomLoss.py:7 -> 0 */
+  float   label_smoothing;         /* CustomLoss.py:7 -> 0.1 */
+  float   reg_weight;              /* LSTMwAttentionModel.py:70-71 -> 1.0 (0 disables the regulariser) */
+  float   dropout_p;               /* AttentionLanguageModule.py:54 -> 0.5 in train(), 0 in eval() */
+  uint64_t seed, offset;           /* Philox counter for the dropout mask when drop_mask == NULL */
+} alexcap_dims;
+
+/* Parameters of AlexCap.AttentionLanguageModule.Decoder (AttentionLanguageModule.py:46-58), state_dict order.
+ * The same struct type, with every member pointing at an fp32 buffer of the same shape, receives gradients. */
+typedef struct alexcap_attn_params {
+  float *init_h_w, *init_h_b;     /* [H,D],[H]   */
+  float *init_c_w, *init_c_b;     /* [H,D],[H]   */
+  float *f_beta_w, *f_beta_b;     /* [D,H],[D]   */
+  float *deep_w, *deep_b;         /* [Vp,H],[Vp] */
+  float *att_U_w, *att_U_b;       /* [H,H],[H]   */
+  float *att_W_w, *att_W_b;       /* [H,D],[H]   */
+  float *att_v_w, *att_v_b;       /* [1,H],[1]   */
+  float *emb_w;                   /* [Vp,E]      */
+  float *lstm_w_ih, *lstm_w_hh;   /* [4H,E+D],[4H,H] */
+  float *lstm_b_ih, *lstm_b_hh;   /* [4H],[4H]   */
+} alexcap_attn_params;
+
+/* Parameters of AlexCap.LanguageModule.LanguageModel (LanguageModule.py:35-49).  Per-layer LSTM tensors are
+ * arrays of num_layers pointers (layer l input size is E for l=0, H above). */
+#define ALEXCAP_MAX_LAYERS 8
+typedef struct alexcap_lstm_params {
+  float *enc_w, *enc_b;           /* image_encoder.encode [E,D],[E] */
+  float *emb_w;                   /* lookup_table [Vp,E] */
+  float *out_w, *out_b;           /* rnn.linear [Vp,H],[Vp] */
+  float *w_ih[ALEXCAP_MAX_LAYERS], *w_hh[ALEXCAP_MAX_LAYERS];   /* [4H,in],[4H,H] */
+  float *b_ih[ALEXCAP_MAX_LAYERS], *b_hh[ALEXCAP_MAX_LAYERS];   /* [4H],[4H] */
+} alexcap_lstm_params;
+
+ALEXCAP_API int alexcap_abi_version(void);
+ALEXCAP_API const char* alexcap_last_error(void);   /* thread-local, static storage */
+/* 0 if the current CUDA device is usable (compute capability 10.x), else ALEXCAP_E_UNSUPPORTED / _CUDA. */
+ALEXCAP_API int alexcap_device_check(void);
+/* Kernel launches enqueued by this library since load (host-side counter; memcpy/memset nodes not counted). */
+ALEXCAP_API unsigned long long alexcap_launch_count(void);
+
+/* ------------------------------------------------------------------ attention decoder (train) ----------
+ * Workspace (bytes) the three calls below need for `dims`; the caller allocates it once and passes it in.
+ * forward() leaves what backward() needs inside the workspace, so the SAME workspace must be handed to the
+ * matching backward(). */
+ALEXCAP_API size_t alexcap_attn_workspace_bytes(const alexcap_dims* dims);
+
+/* Decoder half of AlexCapModel.forward_train (LSTMwAttentionModel.py:67-72): teacher-forced forward
+ * (AttentionLanguageModule.py:62-84), CustomCrossEntropyLoss (CustomLoss.py:9-15), the attention regulariser
+ * and the full backward, in one call.  Logits are never handed to the caller.
+ *   feat [B,L,D] fp32, gt [B,S-1] int32 (0-padded captions, the reference's data.gt_labels)
+ *   grads: every member OVERWRITTEN with d loss/d param;  dfeat [B,L,D] or NULL (needs dims.need_dfeat)
+ *   loss_out[4] (device): {loss_ce + reg, loss_ce, reg, n_valid}
+ *   alphas_out [B,S,L] or NULL;  drop_mask [S,B,H] (0 or 1/(1-p), time-major) or NULL -> Philox(seed,offset)
+ *   ce_denominator (device, 1 float) or NULL: overrides N_valid as the CE divisor (data-parallel global mean). */
+ALEXCAP_API int alexcap_attn_train_fused(const alexcap_dims* dims, const alexcap_attn_params* params,
+                             const float* feat, const int32_t* gt,
+                             const alexcap_attn_params* grads, float* dfeat,
+                             float* loss_out, float* alphas_out, const float* drop_mask,
+                             const float* ce_denominator,
+                             void* workspace, size_t workspace_bytes, void* stream);
+
+/* Decoder.forward, train branch (AttentionLanguageModule.py:62-84): materialises preds [B,S,Vp] and
+ * alphas [B,S,L] exactly like the reference, for callers that build their own loss on top. */
+ALEXCAP_API int alexcap_attn_forward(const alexcap_dims* dims, const alexcap_attn_params* params,
+                         const float* feat, const int32_t* gt,
+                         float* preds, float* alphas, const float* drop_mask,
+                         void* workspace, size_t workspace_bytes, void* stream);
+
+/* Autograd backward of the call above: consumes d preds [B,S,Vp] and d alphas [B,S,L] (either may be NULL = 0). */
+ALEXCAP_API int alexcap_attn_backward(const alexcap_dims* dims, const alexcap_attn_params* params,
+                          const float* feat, const float* dpreds, const float* dalphas,
+                          const alexcap_attn_params* grads, float* dfeat,
+                          void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------ plain LSTM decoder (train) ---------- */
+ALEXCAP_API size_t alexcap_lstm_workspace_bytes(const alexcap_dims* dims);
+
+/* Decoder half of AlexCapModel.forward_train for the plain LSTM (LSTMModel.py:70-73; LanguageModule.py:99-107). */
+ALEXCAP_API int alexcap_lstm_train_fused(const alexcap_dims* dims, const alexcap_lstm_params* params,
+                             const float* feat, const int32_t* gt,
+                             const alexcap_lstm_params* grads, float* dfeat,
+                             float* loss_out, const float* drop_mask, const float* ce_denominator,
+                             void* workspace, size_t workspace_bytes, void* stream);
+/* LanguageModel.forward train branch (LanguageModule.py:99-107): preds [B,S,Vp]. */
+ALEXCAP_API int alexcap_lstm_forward(const alexcap_dims* dims, const alexcap_lstm_params* params,
+                         const float* feat, const int32_t* gt, float* preds, const float* drop_mask,
+                         void* workspace, size_t workspace_bytes, void* stream);
+ALEXCAP_API int alexcap_lstm_backward(const alexcap_dims* dims, const alexcap_lstm_params* params,
+                          const float* feat, const float* dpreds,
+                          const alexcap_lstm_params* grads, float* dfeat,
+                          void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------ targets and loss -------------------
+ * get_target (AttentionLanguageModule.py:197-212 == LanguageModule.py:113-128), both variants at once:
+ *   in_tok[B,T+1] = [START, gt...];   tgt[B,T+1] = [gt..., 0] with the first 0 at index>=1 replaced by END.
+ * Either output may be NULL. */
+ALEXCAP_API int alexcap_make_target(const int32_t* gt, int32_t* in_tok, int32_t* tgt, int32_t B, int32_t T,
+                        int32_t start_token, int32_t end_token, void* stream);
+
+/* CustomCrossEntropyLoss.forward (CustomLoss.py:9-15) on logits [N,C] (row stride ld), targets [N] int32.
+ * loss_out[2] (device) = {mean loss over non-ignored rows, n_valid}; dlogits [N,C] (row stride ld) or NULL
+ * receives d loss/d logits (may alias logits).  scratch: >= 2*N floats. */
+ALEXCAP_API int alexcap_cross_entropy(const float* logits, const int32_t* tgt, int32_t N, int32_t C, int64_t ld,
+                          float label_smoothing, int32_t ignore_index,
+                          float* loss_out, float* dlogits, float* scratch, void* stream);
+
+/* ------------------------------------------------------------------ decoding ---------------------------
+ * Decoder.forward greedy branch (AttentionLanguageModule.py:88-115), batched (the reference's own code only
+ * works for B=1, :108-109).  ids [B,S] int64, alphas [B,S,L]; rows keep decoding until ALL rows emitted END
+ * (:111), exactly like the reference loop; steps never reached stay 0.
+ * The early exit is evaluated on the device: no host synchronisation. */
+ALEXCAP_API size_t alexcap_attn_decode_workspace_bytes(const alexcap_dims* dims, int32_t beam);
+ALEXCAP_API int alexcap_attn_decode_greedy(const alexcap_dims* dims, const alexcap_attn_params* params, const float* feat,
+                               int64_t* ids, float* alphas, void* workspace, size_t workspace_bytes, void* stream);
+/* Decoder.caption (AttentionLanguageModule.py:128-195) for B images at once, beam `beam` per image:
+ * cumulative RAW-logit scores, step-1 top-k from beam row 0, finished beams shrink k, result = completed
+ * beam with the highest score.  ids [B,S] int64 (without START, END included, 0 after), lens [B] int32
+ * (0 = no beam completed: the reference raises ValueError at :191), scores [B], alphas [B,S,L] of the winner. */
+ALEXCAP_API int alexcap_attn_decode_beam(const alexcap_dims* dims, const alexcap_attn_params* params, const float* feat,
+                             int32_t beam, int64_t* ids, int32_t* lens, float* scores, float* alphas,
+                             void* workspace, size_t workspace_bytes, void* stream);
+/* LanguageModel.predict_caption (LanguageModule.py:130-150): ids [B,S] int64. */
+ALEXCAP_API size_t alexcap_lstm_decode_workspace_bytes(const alexcap_dims* dims);
+ALEXCAP_API int alexcap_lstm_decode_greedy(const alexcap_dims* dims, const alexcap_lstm_params* params, const float* feat,
+                               int64_t* ids, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------ kernel-level entry points ----------
+ * The building blocks, exported so the parity tests can pin each kernel on its own.
+ * C[M,N] = act(alpha * op(A) op(B) + bias[N] + bias2[N]) (+ C if accumulate), fp32 SIMT or tensor-core path.
+ *   transa=0: A is [M,K] (lda);  transa=1: A is stored [K,M] (lda).   transb=0: B is [K,N];  transb=1: B is [N,K].
+ *   act: 0 none, 1 tanh, 2 relu.   engine: 0 = fp32 CUDA-core tiles, 1 = tcgen05 tensor-core tiles (3xTF32). */
+ALEXCAP_API int alexcap_gemm_f32(int32_t transa, int32_t transb, int32_t M, int32_t N, int32_t K, float alpha,
+                     const float* A, int64_t lda, const float* B, int64_t ldb,
+                     float* C, int64_t ldc, const float* bias, const float* bias2,
+                     int32_t accumulate, int32_t act, int32_t engine, void* stream);
+
+/* One attention step, Attention.forward with W(features) precomputed (AttentionLanguageModule.py:15-22) and the
+ * beta gate of Decoder.forward (:74-75) fused:  alpha[b,:] (row stride alpha_ld), ctx[B,D], beta[B,D],
+ * gctx[b,:] (row stride gctx_ld) = sigmoid(bpre) * ctx.   q [B,H] (q_ld), bpre [B,D] (bpre_ld). */
+ALEXCAP_API int alexcap_attn_step_fwd(int32_t B, int32_t L, int32_t D, int32_t H,
+                          const float* Ws, const float* feat, const float* q, int64_t q_ld,
+                          const float* bpre, int64_t bpre_ld, const float* w_v,
+                          float* alpha, int64_t alpha_ld, float* ctx, float* beta,
+                          float* gctx, int64_t gctx_ld, void* stream);
+
+/* Backward of one attention step.  In: dgctx [B,D] (ld), saved beta/ctx/alpha/q, optional extra d alpha terms
+ * (dalpha_ext row stride ext_ld; reg_r [B,L]).  Out: dq [B,H] (ld), dbpre [B,D] (ld), de[b,:] (de_ld),
+ * dwv_part [B,H] += per-image partial of d w_v, dfeat [B,L,D] += alpha*dctx (or NULL). */
+ALEXCAP_API int alexcap_attn_step_bwd(int32_t B, int32_t L, int32_t D, int32_t H,
+                          const float* Ws, const float* feat, const float* q, int64_t q_ld, const float* w_v,
+                          const float* alpha, int64_t alpha_ld, const float* ctx, const float* beta,
+                          const float* dgctx, int64_t dgctx_ld,
+                          const float* dalpha_ext, int64_t ext_ld, const float* reg_r,
+                          float* dq, int64_t dq_ld, float* dbpre, int64_t dbpre_ld,
+                          float* de, int64_t de_ld, float* dwv_part, float* dfeat, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ALEXCAP_H_ */
