@@ -41,12 +41,12 @@ class DecoderTrainStep:
         torch.nn.utils.clip_grad_norm_(self.llm.parameters(), max_norm=norm)
 
     # -- internals --------------------------------------------------------------------------------------
-    def _prepare(self, feat, gt):
-        key = (tuple(feat.shape), tuple(gt.shape), feat.device, self.llm.training, self.need_dfeat)
+    def _prepare(self, feat, gt, dev=None):
+        dev = dev if dev is not None else feat.device
+        key = (tuple(feat.shape), tuple(gt.shape), dev, self.llm.training, self.need_dfeat)
         if key == self._key:
             return
         self._key, self._graph = key, None
-        dev = feat.device
         F_.ensure_device(dev)
         self._params = self.llm.param_list()
         for p in self._params:
@@ -68,9 +68,9 @@ class DecoderTrainStep:
         nbytes = F_.attn_workspace_bytes(self._dims) if self.is_attn else F_.lstm_workspace_bytes(self._dims)
         self._ws = F_.workspace(nbytes, dev)
         self._loss = torch.zeros(4, dtype=torch.float32, device=dev)
-        self._feat = torch.empty_like(feat)
-        self._gt = torch.empty_like(gt)
-        self.dfeat = torch.empty_like(feat) if self.need_dfeat else None
+        self._feat = torch.empty(feat.shape, dtype=torch.float32, device=dev)
+        self._gt = torch.empty(gt.shape, dtype=torch.int32, device=dev)
+        self.dfeat = torch.empty_like(self._feat) if self.need_dfeat else None
         self._alphas = None
 
     def _launch(self):
@@ -107,13 +107,16 @@ class DecoderTrainStep:
         return self._loss
 
     def stage(self, features, gt_labels):
+        """Copy one batch into the static device buffers.  Host tensors (ideally pinned) are accepted as the SOURCE of
+        the H2D copy only; all compute happens on the parameters' CUDA device."""
+        dev = next(self.llm.parameters()).device
+        if dev.type != 'cuda':
+            raise F_._lib.AlexcapError('imagecaptioning_b200 has no CPU path: move the decoder to a CUDA device')
         feat = features.detach()
         if feat.dtype != torch.float32:
             feat = feat.float()
-        gt = gt_labels.to(torch.int32)
-        if feat.device.type != 'cuda':
-            raise F_._lib.AlexcapError('imagecaptioning_b200 has no CPU path: features must be on a CUDA device')
-        self._prepare(feat, gt)
+        gt = gt_labels if gt_labels.dtype == torch.int32 else gt_labels.to(torch.int32)
+        self._prepare(feat, gt, dev)
         self._feat.copy_(feat, non_blocking=True)
         self._gt.copy_(gt, non_blocking=True)
 
