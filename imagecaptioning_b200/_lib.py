@@ -49,6 +49,8 @@ PROTOTYPES = {
     'alexcap_last_error': (C.c_char_p, []),
     'alexcap_device_check': (C.c_int, []),
     'alexcap_launch_count': (C.c_ulonglong, []),
+    'alexcap_set_gemm_engine': (C.c_int, [C.c_int]),
+    'alexcap_get_gemm_engine': (C.c_int, []),
     'alexcap_attn_workspace_bytes': (_SZ, [_DP]),
     'alexcap_attn_train_fused': (C.c_int, [_DP, _AP, _P, _P, _AP, _P, _P, _P, _P, _P, _P, _SZ, _P]),
     'alexcap_attn_forward': (C.c_int, [_DP, _AP, _P, _P, _P, _P, _P, _P, _SZ, _P]),

@@ -227,6 +227,13 @@ const char* alexcap_last_error(void) { return err_buf(); }
 
 unsigned long long alexcap_launch_count(void) { return launch_counter(); }
 
+int alexcap_set_gemm_engine(int engine) {
+  if (engine != 0 && engine != 1) return fail(ALEXCAP_E_BADARG, "engine must be 0 (fp32 CUDA cores) or 1 (tcgen05 3xTF32)");
+  gemm_engine() = engine;
+  return 0;
+}
+int alexcap_get_gemm_engine(void) { return gemm_engine(); }
+
 int alexcap_device_check(void) {
   int dev = 0;
   API_CK(cudaGetDevice(&dev));
@@ -349,9 +356,16 @@ int alexcap_gemm_f32(int32_t transa, int32_t transb, int32_t M, int32_t N, int32
                      int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, const float* bias,
                      const float* bias2, int32_t accumulate, int32_t act, int32_t engine, void* stream) {
   if (!A || !B || !C || M <= 0 || N <= 0 || K <= 0) return fail(ALEXCAP_E_BADARG, "alexcap_gemm_f32: bad arguments");
-  if (engine != 0) return fail(ALEXCAP_E_UNSUPPORTED, "alexcap_gemm_f32: engine 1 (tcgen05) not built yet");
-  API_CK(gemm_f32(static_cast<cudaStream_t>(stream), transa != 0, transb != 0, M, N, K, alpha, A, lda, B, ldb, C, ldc, bias,
-                  bias2, accumulate != 0, act));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (engine == 0) {
+    API_CK(gemm_simt_f32(st, transa != 0, transb != 0, M, N, K, alpha, A, lda, B, ldb, C, ldc, bias, bias2, accumulate != 0, act));
+  } else {
+    if (!gemm_tc_supported(M, N, K, A, lda, B, ldb, C))
+      return fail(ALEXCAP_E_UNSUPPORTED, "alexcap_gemm_f32: tensor-core engine needs 16-byte aligned operands with ld % 4 == 0");
+    // engine 1 = heuristic split-K; engine >= 2 forces split-K = engine (tests)
+    API_CK(gemm_tc_f32(st, transa != 0, transb != 0, M, N, K, alpha, A, lda, B, ldb, C, ldc, bias, bias2, accumulate != 0, act,
+                       engine >= 2 ? engine : 0));
+  }
   return 0;
 }
 

@@ -209,9 +209,23 @@ static cudaError_t launch_cfg(cudaStream_t st, bool ta, bool tb, const GemmP& p)
   return cudaGetLastError();
 }
 
+int& gemm_engine() {
+  static int engine = 0;   // 0 = fp32 CUDA-core tiles, 1 = tcgen05 3xTF32 tiles (falls back per call when TMA cannot map the operands)
+  return engine;
+}
+
+// Engine dispatch used by every GEMM on the hot path.
 cudaError_t gemm_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, float alpha,
                      const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
                      const float* bias, const float* bias2, bool accumulate, int act) {
+  if (gemm_engine() == 1 && gemm_tc_supported(M, N, K, A, lda, B, ldb, C))
+    return gemm_tc_f32(st, ta, tb, M, N, K, alpha, A, lda, B, ldb, C, ldc, bias, bias2, accumulate, act, 0);
+  return gemm_simt_f32(st, ta, tb, M, N, K, alpha, A, lda, B, ldb, C, ldc, bias, bias2, accumulate, act);
+}
+
+cudaError_t gemm_simt_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, float alpha,
+                          const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
+                          const float* bias, const float* bias2, bool accumulate, int act) {
   if (M <= 0 || N <= 0) return cudaSuccess;
   GemmP p;
   p.A = A; p.B = B; p.C = C; p.bias = bias; p.bias2 = bias2;

@@ -1,0 +1,394 @@
+// gemm_tc.cu -- tcgen05 / TMEM / TMA GEMM for sm_100a with fp32 in, fp32 out and fp32-grade accuracy (3xTF32).
+//
+//   C[M,N] = act(alpha * op(A) op(B) + bias + bias2) (+ C)         same contract as gemm_f32 (gemm_simt.cu)
+//
+// Why 3xTF32: BASELINE.json's fp32 config demands 1e-4 relative parity on losses AND gradients; a single
+// kind::tf32 MMA keeps 10 mantissa bits (~1e-3).  Each fp32 operand x is split on the fly in shared memory into
+// hi = x & 0xffffe000 (exactly representable in TF32) and lo = x - hi, and every k-step issues
+//     D += A_lo*B_hi;  D += A_hi*B_lo;  D += A_hi*B_hi          (fp32 accumulate in TMEM)
+// which leaves a ~2^-21 relative error.  Reported FLOPs are the algorithmic 2MNK, not 3x.
+//
+// Structure (one 128 x BN output tile per CTA, optional split-K over gridDim.z):
+//   warp 4      : TMA producer  -- cp.async.bulk.tensor.2d, 128B-swizzled tiles, STAGES-deep mbarrier ring
+//   warps 0..3  : hi/lo splitter (generic-proxy smem pass, fence.proxy.async) and, at the end, the epilogue:
+//                 tcgen05.ld 32x32b -> registers -> smem transpose -> coalesced global stores / red.add
+//   warp 5      : TMEM allocator + single-thread tcgen05.mma issuer; tcgen05.commit frees smem stages
+// Operands may be K-major or MN-major in global memory (NT / NN / TN GEMMs without any transposition pass):
+//   K-major  tile: one TMA box {32 k, rows}     -> canonical UMMA K-major SW128 layout  (SBO = 1024 B)
+//   MN-major tile: rows/32 TMA boxes {32 mn, 32 k} -> canonical UMMA MN-major SW128 layout (LBO = 4096 B, SBO = 1024 B)
+// TMA zero-fills out-of-bounds elements, so M, N and K need no padding.
+#include <cuda.h>
+
+#include "common.cuh"
+#include "kernels.h"
+
+namespace alexcap {
+
+namespace tc {
+
+constexpr int BM = 128;
+constexpr int BK = 32;            // fp32 elements per k-block = one 128-byte swizzle row
+constexpr int UMMA_K = 8;         // kind::tf32
+constexpr int NUM_THREADS = 192;
+constexpr uint32_t SPIN_LIMIT = 1u << 27;
+
+struct Params {
+  float* C; const float* bias; const float* bias2;
+  int M, N, K; int64_t ldc; float alpha; int accumulate, act;
+  int kb_per_split, num_kb;
+};
+
+// ------------------------------------------------------------------------------------------------ PTX helpers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// Bounded wait: a protocol bug must trap, not hang the GPU box.
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t spins = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    if (++spins > SPIN_LIMIT) __trap();
+  }
+}
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+      ::"r"(smem_u32(smem_dst)), "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accum) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accum)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// UMMA shared-memory descriptor, 128-byte swizzle (cute::UMMA::SmemDescriptor bit layout).
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFF) >> 4);            // start address, bits [0,14)
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;   // leading-dimension byte offset, bits [16,30)
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;   // stride-dimension byte offset, bits [32,46)
+  d |= (uint64_t)1 << 46;                             // descriptor version (Blackwell)
+  d |= (uint64_t)2 << 61;                             // layout type SWIZZLE_128B
+  return d;
+}
+
+// ------------------------------------------------------------------------------------------------ kernel
+template <int BN, bool A_MN, bool B_MN, int STAGES>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const Params p) {
+  constexpr uint32_t A_BYTES = BM * BK * 4, B_BYTES = BN * BK * 4;
+  constexpr uint32_t STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;    // A_hi, A_lo, B_hi, B_lo
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // manual 1024-byte alignment (swizzle atoms); the launcher over-allocates by 1 KB
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+  uint64_t* conv_bar = full_bar + STAGES;
+  uint64_t* empty_bar = conv_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+  const int kb0 = blockIdx.z * p.kb_per_split;
+  const int kb1 = min(p.num_kb, kb0 + p.kb_per_split);
+  const int nkb = kb1 - kb0;     // >= 1 by construction
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&conv_bar[s], 128);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 5) {   // TMEM allocation (power of two >= 32 columns); the same warp frees it
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(BN));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  if (warp == 4 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 4) {
+    // ================================================================ TMA producer
+    if (lane == 0) {
+      for (int i = 0; i < nkb; ++i) {
+        const int s = i % STAGES;
+        const uint32_t ph = (i / STAGES) & 1;
+        mbar_wait(&empty_bar[s], ph ^ 1);
+        uint8_t* st = smem + s * STAGE_BYTES;
+        mbar_expect_tx(&full_bar[s], A_BYTES + B_BYTES);
+        const int k0 = (kb0 + i) * BK;
+        if (A_MN) {
+#pragma unroll
+          for (int j = 0; j < BM / 32; ++j) tma_load_2d(st + j * 4096, &tmA, m0 + 32 * j, k0, &full_bar[s]);
+        } else {
+          tma_load_2d(st, &tmA, k0, m0, &full_bar[s]);
+        }
+        uint8_t* sb = st + 2 * A_BYTES;
+        if (B_MN) {
+#pragma unroll
+          for (int j = 0; j < BN / 32; ++j) tma_load_2d(sb + j * 4096, &tmB, n0 + 32 * j, k0, &full_bar[s]);
+        } else {
+          tma_load_2d(sb, &tmB, k0, n0, &full_bar[s]);
+        }
+      }
+    }
+  } else if (warp == 5) {
+    // ================================================================ MMA issuer (one elected thread)
+    // instruction descriptor: D=f32, A=B=tf32, majors, N>>3, M>>4   (cute::UMMA::InstrDescriptor bit layout)
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
+                           ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+    for (int i = 0; i < nkb; ++i) {
+      const int s = i % STAGES;
+      const uint32_t ph = (i / STAGES) & 1;
+      mbar_wait(&conv_bar[s], ph);
+      tcgen05_fence_after();
+      if (lane == 0) {
+        const uint32_t a_hi = smem_u32(smem + s * STAGE_BYTES), a_lo = a_hi + A_BYTES;
+        const uint32_t b_hi = a_hi + 2 * A_BYTES, b_lo = b_hi + B_BYTES;
+#pragma unroll
+        for (int k = 0; k < BK / UMMA_K; ++k) {
+          // K-major: +32 bytes inside the swizzled 128-byte row; MN-major: next group of 8 k-rows (+1024 bytes)
+          const uint32_t a_off = A_MN ? k * 1024 : k * 32, b_off = B_MN ? k * 1024 : k * 32;
+          const uint64_t dah = A_MN ? make_desc(a_hi + a_off, 4096, 1024) : make_desc(a_hi + a_off, 0, 1024);
+          const uint64_t dal = A_MN ? make_desc(a_lo + a_off, 4096, 1024) : make_desc(a_lo + a_off, 0, 1024);
+          const uint64_t dbh = B_MN ? make_desc(b_hi + b_off, 4096, 1024) : make_desc(b_hi + b_off, 0, 1024);
+          const uint64_t dbl = B_MN ? make_desc(b_lo + b_off, 4096, 1024) : make_desc(b_lo + b_off, 0, 1024);
+          umma_tf32(tmem_base, dal, dbh, idesc, (i | k) != 0);
+          umma_tf32(tmem_base, dah, dbl, idesc, 1);
+          umma_tf32(tmem_base, dah, dbh, idesc, 1);
+        }
+        umma_commit(&empty_bar[s]);                       // smem stage reusable once these MMAs retire
+        if (i == nkb - 1) umma_commit(tmem_full_bar);     // accumulator complete
+      }
+      __syncwarp();
+    }
+  } else {
+    // ================================================================ warps 0..3: splitter, then epilogue
+    const int t = threadIdx.x;   // 0..127
+    for (int i = 0; i < nkb; ++i) {
+      const int s = i % STAGES;
+      const uint32_t ph = (i / STAGES) & 1;
+      mbar_wait(&full_bar[s], ph);
+      uint8_t* st = smem + s * STAGE_BYTES;
+      // elementwise, so it is oblivious to the swizzle: same byte offset in the hi and lo tiles
+#pragma unroll 4
+      for (int c = t; c < (int)(A_BYTES / 16); c += 128) {
+        uint4 x = *reinterpret_cast<uint4*>(st + c * 16);
+        uint4 h = make_uint4(x.x & 0xffffe000u, x.y & 0xffffe000u, x.z & 0xffffe000u, x.w & 0xffffe000u);
+        float4 l = make_float4(__uint_as_float(x.x) - __uint_as_float(h.x), __uint_as_float(x.y) - __uint_as_float(h.y),
+                               __uint_as_float(x.z) - __uint_as_float(h.z), __uint_as_float(x.w) - __uint_as_float(h.w));
+        *reinterpret_cast<uint4*>(st + c * 16) = h;
+        *reinterpret_cast<float4*>(st + A_BYTES + c * 16) = l;
+      }
+      uint8_t* sb = st + 2 * A_BYTES;
+#pragma unroll 4
+      for (int c = t; c < (int)(B_BYTES / 16); c += 128) {
+        uint4 x = *reinterpret_cast<uint4*>(sb + c * 16);
+        uint4 h = make_uint4(x.x & 0xffffe000u, x.y & 0xffffe000u, x.z & 0xffffe000u, x.w & 0xffffe000u);
+        float4 l = make_float4(__uint_as_float(x.x) - __uint_as_float(h.x), __uint_as_float(x.y) - __uint_as_float(h.y),
+                               __uint_as_float(x.z) - __uint_as_float(h.z), __uint_as_float(x.w) - __uint_as_float(h.w));
+        *reinterpret_cast<uint4*>(sb + c * 16) = h;
+        *reinterpret_cast<float4*>(sb + B_BYTES + c * 16) = l;
+      }
+      fence_proxy_async();            // generic-proxy writes -> visible to the tensor core (async proxy)
+      mbar_arrive(&conv_bar[s]);
+    }
+
+    // ---- epilogue: TMEM -> registers -> smem transpose -> coalesced global
+    mbar_wait(tmem_full_bar, 0);
+    tcgen05_fence_after();
+    float* tile = reinterpret_cast<float*>(smem) + warp * (32 * 33);   // stage memory is idle now (all MMAs retired)
+    const bool first_split = (blockIdx.z == 0);
+    const bool atomic = gridDim.z > 1;
+#pragma unroll 1
+    for (int cc = 0; cc < BN / 32; ++cc) {
+      uint32_t v[32];
+      const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(cc * 32);
+      asm volatile(
+          "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+          "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+          "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+          : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+            "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+            "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+            "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+          : "r"(taddr));
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+      for (int j = 0; j < 32; ++j) tile[lane * 33 + j] = __uint_as_float(v[j]);   // thread = row, j = column
+      __syncwarp();
+      const int n = n0 + cc * 32 + lane;
+      float bsum = 0.f;
+      if (n < p.N && first_split) {
+        if (p.bias) bsum += __ldg(p.bias + n);
+        if (p.bias2) bsum += __ldg(p.bias2 + n);
+      }
+      if (n < p.N) {
+#pragma unroll 4
+        for (int r = 0; r < 32; ++r) {
+          const int m = m0 + warp * 32 + r;
+          if (m >= p.M) break;
+          float x = fmaf(p.alpha, tile[r * 33 + lane], bsum);
+          float* cp = p.C + (int64_t)m * p.ldc + n;
+          if (atomic) {
+            atomicAdd(cp, x);      // C was zeroed (or holds the value to accumulate onto) by the launcher
+          } else {
+            if (p.accumulate) x += *cp;
+            if (p.act == ACT_TANH) x = tanhf(x);
+            else if (p.act == ACT_RELU) x = fmaxf(x, 0.f);
+            *cp = x;
+          }
+        }
+      }
+      __syncwarp();
+    }
+    tcgen05_fence_before();
+  }
+
+  __syncthreads();
+  if (warp == 5) {
+    tcgen05_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(BN));
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(ptr);
+  }
+  return fn;
+}
+
+// 2-D fp32 tensor map: inner (contiguous) extent `inner`, outer extent `outer`, row pitch ld floats, box {32, box_outer}.
+static bool make_map(CUtensorMap* map, const float* base, int64_t inner, int64_t outer, int64_t ld, int box_outer) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return false;
+  cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * sizeof(float)};
+  cuuint32_t box[2] = {32u, (cuuint32_t)box_outer};
+  cuuint32_t estr[2] = {1u, 1u};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS;
+}
+
+template <int BN, bool A_MN, bool B_MN>
+static cudaError_t launch(cudaStream_t st, const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, dim3 grid) {
+  constexpr int STAGES = (BN == 128) ? 3 : 4;
+  constexpr size_t SMEM = (size_t)STAGES * (2 * BM * BK * 4 + 2 * BN * BK * 4) + 1024 /*align*/ + 256 /*barriers*/;
+  static bool configured = false;
+  auto kern = gemm_tc_kernel<BN, A_MN, B_MN, STAGES>;
+  if (!configured) {
+    ACK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+    configured = true;
+  }
+  ALEXCAP_NOTE_LAUNCH();
+  kern<<<grid, NUM_THREADS, SMEM, st>>>(ta, tb, p);
+  return cudaGetLastError();
+}
+
+}  // namespace tc
+
+bool gemm_tc_supported(int M, int N, int K, const float* A, int64_t lda, const float* B, int64_t ldb, const float* C) {
+  (void)M; (void)N; (void)K; (void)C;
+  return (lda % 4 == 0) && (ldb % 4 == 0) && aligned16(A) && aligned16(B) && tc::get_encode() != nullptr;
+}
+
+cudaError_t gemm_tc_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, float alpha,
+                        const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
+                        const float* bias, const float* bias2, bool accumulate, int act, int force_splits) {
+  using namespace tc;
+  if (M <= 0 || N <= 0 || K <= 0) return cudaSuccess;
+  if (!gemm_tc_supported(M, N, K, A, lda, B, ldb, C)) return cudaErrorNotSupported;
+  const bool a_mn = ta;        // transa: A stored [K,M] -> M contiguous
+  const bool b_mn = !tb;       // transb=0: B stored [K,N] -> N contiguous
+  const int num_kb = ceil_div(K, BK);
+  const int tiles128 = ceil_div(M, BM) * ceil_div(N, 128);
+  const int BN = (tiles128 >= 120 || N > 64 * 1024) ? 128 : 64;
+  const int tiles = ceil_div(M, BM) * ceil_div(N, BN);
+  // split-K (fp32 red.add into C) when the output grid alone cannot fill 148 SMs; no split with an activation
+  int splits = 1;
+  if (force_splits > 0) splits = force_splits;
+  else if (act == ACT_NONE && tiles < 100) {
+    splits = 148 / tiles;
+    const int max_by_k = num_kb / 4 > 0 ? num_kb / 4 : 1;     // keep >= 4 k-blocks per CTA
+    if (splits > max_by_k) splits = max_by_k;
+    if (splits < 1) splits = 1;
+  }
+  if (act != ACT_NONE) splits = 1;
+  int kb_per = ceil_div(num_kb, splits);
+  splits = ceil_div(num_kb, kb_per);       // no empty split
+  if (splits > 1 && !accumulate) ACK(cudaMemset2DAsync(C, ldc * sizeof(float), 0, (size_t)N * sizeof(float), M, st));
+
+  CUtensorMap mapA, mapB;
+  bool ok = a_mn ? make_map(&mapA, A, M, K, lda, BK) : make_map(&mapA, A, K, M, lda, BM);
+  ok = ok && (b_mn ? make_map(&mapB, B, N, K, ldb, BK) : make_map(&mapB, B, K, N, ldb, BN));
+  if (!ok) return cudaErrorInvalidValue;
+
+  Params p;
+  p.C = C; p.bias = bias; p.bias2 = bias2; p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.alpha = alpha;
+  p.accumulate = accumulate ? 1 : 0; p.act = act; p.kb_per_split = kb_per; p.num_kb = num_kb;
+  dim3 grid(ceil_div(N, BN), ceil_div(M, BM), splits);
+#define TC_DISPATCH(BN_)                                                                 \
+  do {                                                                                   \
+    if (!a_mn && !b_mn) return launch<BN_, false, false>(st, mapA, mapB, p, grid);       \
+    if (!a_mn && b_mn) return launch<BN_, false, true>(st, mapA, mapB, p, grid);         \
+    if (a_mn && b_mn) return launch<BN_, true, true>(st, mapA, mapB, p, grid);           \
+    return launch<BN_, true, false>(st, mapA, mapB, p, grid);                            \
+  } while (0)
+  if (BN == 128) TC_DISPATCH(128);
+  TC_DISPATCH(64);
+#undef TC_DISPATCH
+}
+
+}  // namespace alexcap

@@ -12,6 +12,16 @@ cudaError_t gemm_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, flo
                      const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
                      const float* bias, const float* bias2, bool accumulate, int act);
 
+cudaError_t gemm_simt_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, float alpha,
+                          const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
+                          const float* bias, const float* bias2, bool accumulate, int act);
+// tcgen05 / TMEM / TMA engine (gemm_tc.cu); force_splits > 0 overrides the split-K heuristic (tests)
+cudaError_t gemm_tc_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, float alpha,
+                        const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
+                        const float* bias, const float* bias2, bool accumulate, int act, int force_splits);
+bool gemm_tc_supported(int M, int N, int K, const float* A, int64_t lda, const float* B, int64_t ldb, const float* C);
+int& gemm_engine();
+
 // ---- attention (attention.cu)
 cudaError_t attn_step_fwd(cudaStream_t st, int B, int L, int D, int H, const float* Ws, const float* feat,
                           const float* q, int64_t q_ld, const float* bpre, int64_t bpre_ld, const float* wv,

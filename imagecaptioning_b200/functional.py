@@ -258,3 +258,13 @@ def lstm_decode_greedy(dims, P: LstmParams, feat):
     check(lib.alexcap_lstm_decode_greedy(C.byref(dims), C.byref(P), _ptr(feat), _ptr(ids), _ptr(ws), ws.numel(),
                                          _stream()), 'alexcap_lstm_decode_greedy')
     return ids
+
+
+# ------------------------------------------------------------------------------------------------ engine selection
+def set_gemm_engine(engine: int):
+    """0 = fp32 CUDA-core tiles, 1 = tcgen05/TMEM/TMA 3xTF32 tiles (process-wide)."""
+    check(_lib.load().alexcap_set_gemm_engine(int(engine)), 'alexcap_set_gemm_engine')
+
+
+def get_gemm_engine() -> int:
+    return int(_lib.load().alexcap_get_gemm_engine())

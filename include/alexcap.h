@@ -90,6 +90,10 @@ ALEXCAP_API const char* alexcap_last_error(void);   /* thread-local, static stor
 ALEXCAP_API int alexcap_device_check(void);
 /* Kernel launches enqueued by this library since load (host-side counter; memcpy/memset nodes not counted). */
 ALEXCAP_API unsigned long long alexcap_launch_count(void);
+/* GEMM engine used by every entry point below: 0 = fp32 CUDA-core tiles, 1 = tcgen05/TMEM/TMA tiles computing in
+ * 3xTF32 (fp32-grade accuracy; calls whose operands TMA cannot map -- ld % 4 != 0 -- use engine 0).  Process-wide. */
+ALEXCAP_API int alexcap_set_gemm_engine(int engine);
+ALEXCAP_API int alexcap_get_gemm_engine(void);
 
 /* ------------------------------------------------------------------ attention decoder (train) ----------
  * Workspace (bytes) the three calls below need for `dims`; the caller allocates it once and passes it in.
@@ -181,7 +185,8 @@ ALEXCAP_API int alexcap_lstm_decode_greedy(const alexcap_dims* dims, const alexc
  * The building blocks, exported so the parity tests can pin each kernel on its own.
  * C[M,N] = act(alpha * op(A) op(B) + bias[N] + bias2[N]) (+ C if accumulate), fp32 SIMT or tensor-core path.
  *   transa=0: A is [M,K] (lda);  transa=1: A is stored [K,M] (lda).   transb=0: B is [K,N];  transb=1: B is [N,K].
- *   act: 0 none, 1 tanh, 2 relu.   engine: 0 = fp32 CUDA-core tiles, 1 = tcgen05 tensor-core tiles (3xTF32). */
+ *   act: 0 none, 1 tanh, 2 relu.   engine: 0 = fp32 CUDA-core tiles, 1 = tcgen05 tensor-core tiles (3xTF32),
+ *   n >= 2 = tcgen05 with split-K forced to n. */
 ALEXCAP_API int alexcap_gemm_f32(int32_t transa, int32_t transb, int32_t M, int32_t N, int32_t K, float alpha,
                      const float* A, int64_t lda, const float* B, int64_t ldb,
                      float* C, int64_t ldc, const float* bias, const float* bias2,

@@ -1,0 +1,110 @@
+"""-m gpu: the tcgen05 / TMEM / TMA GEMM engine (3xTF32) against fp64 math, every operand-major combination,
+edge shapes, split-K, epilogues -- and the full training step running on it."""
+import pytest
+import torch
+
+from tests.util import golden_names, load_golden, rel_err
+
+pytestmark = pytest.mark.gpu
+DEV = 'cuda'
+
+
+@pytest.fixture(scope='module')
+def F_():
+    from imagecaptioning_b200 import functional
+    functional.ensure_device(DEV)
+    return functional
+
+
+@pytest.fixture()
+def tc_engine(F_):
+    F_.set_gemm_engine(1)
+    yield
+    F_.set_gemm_engine(0)
+
+
+def _mk(ta, tb, M, N, K, g, lda_pad=0, ldb_pad=0):
+    A = torch.randn((K, M + lda_pad) if ta else (M, K + lda_pad), generator=g)
+    B = torch.randn((N, K + ldb_pad) if tb else (K, N + ldb_pad), generator=g)
+    Av = A[:, :M] if ta else A[:, :K]
+    Bv = B[:, :K] if tb else B[:, :N]
+    ref = (Av.double().T if ta else Av.double()) @ (Bv.double().T if tb else Bv.double())
+    return A, B, ref
+
+
+@pytest.mark.parametrize('ta,tb', [(False, True), (False, False), (True, False), (True, True)])
+@pytest.mark.parametrize('M,N,K', [(128, 128, 32), (128, 64, 64), (256, 256, 256), (37, 53, 29), (130, 200, 100),
+                                   (128, 2048, 1024), (2176, 515, 96), (1, 7, 3)])
+def test_gemm_tc_layouts_and_edges(F_, ta, tb, M, N, K):
+    g = torch.Generator().manual_seed(M * 1000 + N + K)
+    pad_a = (-M) % 4 if ta else (-K) % 4          # TMA needs ld % 4 == 0
+    pad_b = (-K) % 4 if tb else (-N) % 4
+    A, B, ref = _mk(ta, tb, M, N, K, g, pad_a, pad_b)
+    out = F_.gemm(A.to(DEV), B.to(DEV), transa=ta, transb=tb, M=M, N=N, K=K, lda=A.shape[1], ldb=B.shape[1], engine=1)
+    torch.cuda.synchronize()
+    assert rel_err(out, ref) < 2e-5, rel_err(out, ref)
+
+
+@pytest.mark.parametrize('splits', [2, 3, 16])
+def test_gemm_tc_split_k(F_, splits):
+    g = torch.Generator().manual_seed(splits)
+    M, N, K = 128, 512, 2048
+    A, B, ref = _mk(False, False, M, N, K, g)
+    bias = torch.randn(N, generator=g)
+    C0 = torch.randn(M, N, generator=g)
+    out = F_.gemm(A.to(DEV), B.to(DEV), transa=False, transb=False, bias=bias.to(DEV), engine=splits)
+    assert rel_err(out, ref + bias.double()) < 2e-5
+    Cd = C0.to(DEV)
+    F_.gemm(A.to(DEV), B.to(DEV), transa=False, transb=False, out=Cd, accumulate=True, alpha=0.5, engine=splits)
+    assert rel_err(Cd, 0.5 * ref + C0.double()) < 2e-5
+
+
+def test_gemm_tc_epilogues(F_):
+    g = torch.Generator().manual_seed(5)
+    M, N, K = 70, 45, 36
+    A, B, ref = _mk(False, True, M, N, K, g)
+    b1, b2 = torch.randn(N, generator=g), torch.randn(N, generator=g)
+    C0 = torch.randn(M, N + 3, generator=g)
+    Cd = C0.to(DEV)
+    F_.gemm(A.to(DEV), B.to(DEV), out=Cd, ldc=N + 3, M=M, N=N, K=K, bias=b1.to(DEV), bias2=b2.to(DEV), accumulate=True,
+            act=1, alpha=0.5, engine=1)
+    want = torch.tanh(0.5 * ref + b1.double() + b2.double() + C0[:, :N].double())
+    assert rel_err(Cd[:, :N], want) < 2e-5
+    assert torch.equal(Cd[:, N:].cpu(), C0[:, N:])
+    out = F_.gemm(A.to(DEV), B.to(DEV), act=2, engine=1)
+    assert rel_err(out, ref.clamp_min(0)) < 2e-5
+
+
+def test_gemm_tc_accuracy_is_fp32_grade(F_):
+    """3xTF32 must beat single-pass TF32 by orders of magnitude: K=4096 dot products of O(1) numbers."""
+    g = torch.Generator().manual_seed(9)
+    A, B, ref = _mk(False, True, 256, 256, 4096, g)
+    out = F_.gemm(A.to(DEV), B.to(DEV), engine=1)
+    simt = F_.gemm(A.to(DEV), B.to(DEV), engine=0)
+    e_tc, e_simt = rel_err(out, ref), rel_err(simt, ref)
+    assert e_tc < 5e-6, (e_tc, e_simt)
+
+
+@pytest.mark.parametrize('name', golden_names('attn_'))
+def test_attn_train_fused_on_tensor_engine_vs_golden(name, tc_engine):
+    from imagecaptioning_b200.model import DecoderTrainStep
+    from tests.gpu_util import build_decoder
+    from tests.test_gpu_train import TOL, _check_grads
+    g = load_golden(name)
+    dec = build_decoder(g['cfg'], g['params'])
+    step = DecoderTrainStep(dec, need_dfeat=True)
+    loss = step.forward_train(g['feat'].float().to(DEV), g['gt'].to(DEV))
+    assert abs(float(loss) - g['loss']) < TOL * abs(g['loss'])
+    _check_grads({k: p.grad for k, p in dec.named_parameters()}, g['grads'])
+    assert rel_err(step.dfeat, g['dfeat']) < TOL
+
+
+def test_attn_config2_full_size_on_tensor_engine(tc_engine):
+    from tests.test_gpu_train import test_attn_config2_full_size_vs_reference_port
+    test_attn_config2_full_size_vs_reference_port()
+
+
+def test_lstm_and_midsize_on_tensor_engine(tc_engine):
+    from tests.test_gpu_train import test_attn_midsize_vs_oracle_fp64, test_lstm_two_layers_vs_oracle
+    test_attn_midsize_vs_oracle_fp64()
+    test_lstm_two_layers_vs_oracle()
