@@ -210,7 +210,7 @@ static cudaError_t launch_cfg(cudaStream_t st, bool ta, bool tb, const GemmP& p)
 }
 
 int& gemm_engine() {
-  static int engine = 0;   // 0 = fp32 CUDA-core tiles, 1 = tcgen05 3xTF32 tiles (falls back per call when TMA cannot map the operands)
+  static int engine = 1;   // 1 = tcgen05 3xTF32 tiles (default; per-call fallback when TMA cannot map the operands), 0 = fp32 CUDA-core tiles
   return engine;
 }
 

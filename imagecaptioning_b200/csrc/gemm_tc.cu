@@ -4,7 +4,7 @@
 //
 // Why 3xTF32: BASELINE.json's fp32 config demands 1e-4 relative parity on losses AND gradients; a single
 // kind::tf32 MMA keeps 10 mantissa bits (~1e-3).  Each fp32 operand x is split on the fly in shared memory into
-// hi = x & 0xffffe000 (exactly representable in TF32) and lo = x - hi, and every k-step issues
+// hi = tf32_round(x) and lo = tf32_round(x - hi), and every k-step issues
 //     D += A_lo*B_hi;  D += A_hi*B_lo;  D += A_hi*B_hi          (fp32 accumulate in TMEM)
 // which leaves a ~2^-21 relative error.  Reported FLOPs are the algorithmic 2MNK, not 3x.
 //
@@ -14,8 +14,9 @@
 //                 tcgen05.ld 32x32b -> registers -> smem transpose -> coalesced global stores / red.add
 //   warp 5      : TMEM allocator + single-thread tcgen05.mma issuer; tcgen05.commit frees smem stages
 // Operands may be K-major or MN-major in global memory (NT / NN / TN GEMMs without any transposition pass):
-//   K-major  tile: one TMA box {32 k, rows}     -> canonical UMMA K-major SW128 layout  (SBO = 1024 B)
-//   MN-major tile: rows/32 TMA boxes {32 mn, 32 k} -> canonical UMMA MN-major SW128 layout (LBO = 4096 B, SBO = 1024 B)
+//   K-major  tile: one TMA box {32 k, rows}, swizzle 128B   -> UMMA K-major SWIZZLE_128B layout (SBO = 1024 B)
+//   MN-major tile: rows/32 TMA boxes {32 mn, 32 k}, swizzle 128B_ATOM_32B -> UMMA MN-major SWIZZLE_128B_BASE32B layout,
+//                  the only MN-major layout tf32 operands have (LBO = 4096 B, SBO = 512 B)
 // TMA zero-fills out-of-bounds elements, so M, N and K need no padding.
 #include <cuda.h>
 
@@ -37,6 +38,10 @@ struct Params {
   int M, N, K; int64_t ldc; float alpha; int accumulate, act;
   int kb_per_split, num_kb;
 };
+// MN-major fp32/tf32 tiles (probed on B200, scripts/debug_tc_mn.py): boxes of {32 mn, 32 k} = 32 rows of 128 bytes,
+// TMA swizzle 128B_ATOM_32B, UMMA layout SWIZZLE_128B_BASE32B: LBO = 4096 (next 32-wide mn block), SBO = 512 (next group
+// of 4 k-rows); one K=8 MMA consumes 8 k-rows = 1024 bytes.
+constexpr uint32_t MN_LBO = 4096, MN_SBO = 512, MN_KSTEP = 1024;
 
 // ------------------------------------------------------------------------------------------------ PTX helpers
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -90,14 +95,22 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
+// fp32 -> (hi, lo) with both parts exactly representable in TF32 (low 13 mantissa bits zero), round-to-nearest at both
+// levels so the residual error (~2^-22 |x|) is unbiased; the tensor core would otherwise TRUNCATE the low bits.
+__device__ __forceinline__ void split_tf32(uint32_t x, uint32_t& hi, uint32_t& lo) {
+  hi = (x + 0x1000u) & 0xffffe000u;
+  const float r = __uint_as_float(x) - __uint_as_float(hi);      // exact in fp32
+  lo = (__float_as_uint(r) + 0x1000u) & 0xffffe000u;
+}
+
 // UMMA shared-memory descriptor, 128-byte swizzle (cute::UMMA::SmemDescriptor bit layout).
-__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout_type = 2) {
   uint64_t d = 0;
   d |= (uint64_t)((saddr & 0x3FFFF) >> 4);            // start address, bits [0,14)
   d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;   // leading-dimension byte offset, bits [16,30)
   d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;   // stride-dimension byte offset, bits [32,46)
   d |= (uint64_t)1 << 46;                             // descriptor version (Blackwell)
-  d |= (uint64_t)2 << 61;                             // layout type SWIZZLE_128B
+  d |= (uint64_t)layout_type << 61;                   // 2 = SWIZZLE_128B, 1 = SWIZZLE_128B_BASE32B
   return d;
 }
 
@@ -185,11 +198,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
         for (int k = 0; k < BK / UMMA_K; ++k) {
           // K-major: +32 bytes inside the swizzled 128-byte row; MN-major: next group of 8 k-rows (+1024 bytes)
-          const uint32_t a_off = A_MN ? k * 1024 : k * 32, b_off = B_MN ? k * 1024 : k * 32;
-          const uint64_t dah = A_MN ? make_desc(a_hi + a_off, 4096, 1024) : make_desc(a_hi + a_off, 0, 1024);
-          const uint64_t dal = A_MN ? make_desc(a_lo + a_off, 4096, 1024) : make_desc(a_lo + a_off, 0, 1024);
-          const uint64_t dbh = B_MN ? make_desc(b_hi + b_off, 4096, 1024) : make_desc(b_hi + b_off, 0, 1024);
-          const uint64_t dbl = B_MN ? make_desc(b_lo + b_off, 4096, 1024) : make_desc(b_lo + b_off, 0, 1024);
+          const uint32_t a_off = A_MN ? k * MN_KSTEP : k * 32, b_off = B_MN ? k * MN_KSTEP : k * 32;
+          // MN-major fp32/tf32 operands only exist in the SWIZZLE_128B_BASE32B layout (32-byte swizzle atoms, 4 k-rows
+          // of 128 bytes per atom): LBO = stride between 32-element mn blocks, SBO = stride between 4-row k groups.
+          const uint64_t dah = A_MN ? make_desc(a_hi + a_off, MN_LBO, MN_SBO, 1) : make_desc(a_hi + a_off, 0, 1024);
+          const uint64_t dal = A_MN ? make_desc(a_lo + a_off, MN_LBO, MN_SBO, 1) : make_desc(a_lo + a_off, 0, 1024);
+          const uint64_t dbh = B_MN ? make_desc(b_hi + b_off, MN_LBO, MN_SBO, 1) : make_desc(b_hi + b_off, 0, 1024);
+          const uint64_t dbl = B_MN ? make_desc(b_lo + b_off, MN_LBO, MN_SBO, 1) : make_desc(b_lo + b_off, 0, 1024);
           umma_tf32(tmem_base, dal, dbh, idesc, (i | k) != 0);
           umma_tf32(tmem_base, dah, dbl, idesc, 1);
           umma_tf32(tmem_base, dah, dbh, idesc, 1);
@@ -210,22 +225,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       // elementwise, so it is oblivious to the swizzle: same byte offset in the hi and lo tiles
 #pragma unroll 4
       for (int c = t; c < (int)(A_BYTES / 16); c += 128) {
-        uint4 x = *reinterpret_cast<uint4*>(st + c * 16);
-        uint4 h = make_uint4(x.x & 0xffffe000u, x.y & 0xffffe000u, x.z & 0xffffe000u, x.w & 0xffffe000u);
-        float4 l = make_float4(__uint_as_float(x.x) - __uint_as_float(h.x), __uint_as_float(x.y) - __uint_as_float(h.y),
-                               __uint_as_float(x.z) - __uint_as_float(h.z), __uint_as_float(x.w) - __uint_as_float(h.w));
+        const uint4 x = *reinterpret_cast<uint4*>(st + c * 16);
+        uint4 h, l;
+        split_tf32(x.x, h.x, l.x); split_tf32(x.y, h.y, l.y); split_tf32(x.z, h.z, l.z); split_tf32(x.w, h.w, l.w);
         *reinterpret_cast<uint4*>(st + c * 16) = h;
-        *reinterpret_cast<float4*>(st + A_BYTES + c * 16) = l;
+        *reinterpret_cast<uint4*>(st + A_BYTES + c * 16) = l;
       }
       uint8_t* sb = st + 2 * A_BYTES;
 #pragma unroll 4
       for (int c = t; c < (int)(B_BYTES / 16); c += 128) {
-        uint4 x = *reinterpret_cast<uint4*>(sb + c * 16);
-        uint4 h = make_uint4(x.x & 0xffffe000u, x.y & 0xffffe000u, x.z & 0xffffe000u, x.w & 0xffffe000u);
-        float4 l = make_float4(__uint_as_float(x.x) - __uint_as_float(h.x), __uint_as_float(x.y) - __uint_as_float(h.y),
-                               __uint_as_float(x.z) - __uint_as_float(h.z), __uint_as_float(x.w) - __uint_as_float(h.w));
+        const uint4 x = *reinterpret_cast<uint4*>(sb + c * 16);
+        uint4 h, l;
+        split_tf32(x.x, h.x, l.x); split_tf32(x.y, h.y, l.y); split_tf32(x.z, h.z, l.z); split_tf32(x.w, h.w, l.w);
         *reinterpret_cast<uint4*>(sb + c * 16) = h;
-        *reinterpret_cast<float4*>(sb + B_BYTES + c * 16) = l;
+        *reinterpret_cast<uint4*>(sb + B_BYTES + c * 16) = l;
       }
       fence_proxy_async();            // generic-proxy writes -> visible to the tensor core (async proxy)
       mbar_arrive(&conv_bar[s]);
@@ -309,7 +322,8 @@ static EncodeTiledFn get_encode() {
 }
 
 // 2-D fp32 tensor map: inner (contiguous) extent `inner`, outer extent `outer`, row pitch ld floats, box {32, box_outer}.
-static bool make_map(CUtensorMap* map, const float* base, int64_t inner, int64_t outer, int64_t ld, int box_outer) {
+static bool make_map(CUtensorMap* map, const float* base, int64_t inner, int64_t outer, int64_t ld, int box_outer,
+                     bool mn_major) {
   EncodeTiledFn enc = get_encode();
   if (!enc) return false;
   cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
@@ -317,7 +331,9 @@ static bool make_map(CUtensorMap* map, const float* base, int64_t inner, int64_t
   cuuint32_t box[2] = {32u, (cuuint32_t)box_outer};
   cuuint32_t estr[2] = {1u, 1u};
   CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS;
 }
@@ -371,8 +387,8 @@ cudaError_t gemm_tc_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, 
   if (splits > 1 && !accumulate) ACK(cudaMemset2DAsync(C, ldc * sizeof(float), 0, (size_t)N * sizeof(float), M, st));
 
   CUtensorMap mapA, mapB;
-  bool ok = a_mn ? make_map(&mapA, A, M, K, lda, BK) : make_map(&mapA, A, K, M, lda, BM);
-  ok = ok && (b_mn ? make_map(&mapB, B, N, K, ldb, BK) : make_map(&mapB, B, K, N, ldb, BN));
+  bool ok = a_mn ? make_map(&mapA, A, M, K, lda, BK, true) : make_map(&mapA, A, K, M, lda, BM, false);
+  ok = ok && (b_mn ? make_map(&mapB, B, N, K, ldb, BK, true) : make_map(&mapB, B, K, N, ldb, BN, false));
   if (!ok) return cudaErrorInvalidValue;
 
   Params p;

@@ -90,7 +90,7 @@ ALEXCAP_API const char* alexcap_last_error(void);   /* thread-local, static stor
 ALEXCAP_API int alexcap_device_check(void);
 /* Kernel launches enqueued by this library since load (host-side counter; memcpy/memset nodes not counted). */
 ALEXCAP_API unsigned long long alexcap_launch_count(void);
-/* GEMM engine used by every entry point below: 0 = fp32 CUDA-core tiles, 1 = tcgen05/TMEM/TMA tiles computing in
+/* GEMM engine used by every entry point below (default 1): 0 = fp32 CUDA-core tiles, 1 = tcgen05/TMEM/TMA tiles computing in
  * 3xTF32 (fp32-grade accuracy; calls whose operands TMA cannot map -- ld % 4 != 0 -- use engine 0).  Process-wide. */
 ALEXCAP_API int alexcap_set_gemm_engine(int engine);
 ALEXCAP_API int alexcap_get_gemm_engine(void);

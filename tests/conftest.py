@@ -32,3 +32,12 @@ def reference_modules():
     from AlexCap.LanguageModule import LanguageModel
     from AlexCap.CustomLoss import CustomCrossEntropyLoss
     return dict(Decoder=Decoder, LanguageModel=LanguageModel, CustomCrossEntropyLoss=CustomCrossEntropyLoss)
+
+
+@pytest.fixture(params=[1, 0], ids=['tcgen05', 'simt'])
+def gemm_engine(request):
+    """Run a GPU test once per GEMM engine: 1 = tcgen05/TMEM/TMA 3xTF32 (the default), 0 = fp32 CUDA-core tiles."""
+    from imagecaptioning_b200 import functional as F_
+    F_.set_gemm_engine(request.param)
+    yield request.param
+    F_.set_gemm_engine(1)

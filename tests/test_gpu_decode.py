@@ -8,7 +8,7 @@ from oracle.synth import synth_inputs
 from tests.gpu_util import DEV, build_decoder, build_lstm, random_attn_params
 from tests.util import golden_names, load_golden
 
-pytestmark = pytest.mark.gpu
+pytestmark = [pytest.mark.gpu, pytest.mark.usefixtures('gemm_engine')]
 
 
 @pytest.mark.parametrize('name', golden_names('attn_'))

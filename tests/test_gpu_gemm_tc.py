@@ -3,7 +3,7 @@ edge shapes, split-K, epilogues -- and the full training step running on it."""
 import pytest
 import torch
 
-from tests.util import golden_names, load_golden, rel_err
+from tests.util import rel_err
 
 pytestmark = pytest.mark.gpu
 DEV = 'cuda'
@@ -14,13 +14,6 @@ def F_():
     from imagecaptioning_b200 import functional
     functional.ensure_device(DEV)
     return functional
-
-
-@pytest.fixture()
-def tc_engine(F_):
-    F_.set_gemm_engine(1)
-    yield
-    F_.set_gemm_engine(0)
 
 
 def _mk(ta, tb, M, N, K, g, lda_pad=0, ldb_pad=0):
@@ -83,28 +76,3 @@ def test_gemm_tc_accuracy_is_fp32_grade(F_):
     simt = F_.gemm(A.to(DEV), B.to(DEV), engine=0)
     e_tc, e_simt = rel_err(out, ref), rel_err(simt, ref)
     assert e_tc < 5e-6, (e_tc, e_simt)
-
-
-@pytest.mark.parametrize('name', golden_names('attn_'))
-def test_attn_train_fused_on_tensor_engine_vs_golden(name, tc_engine):
-    from imagecaptioning_b200.model import DecoderTrainStep
-    from tests.gpu_util import build_decoder
-    from tests.test_gpu_train import TOL, _check_grads
-    g = load_golden(name)
-    dec = build_decoder(g['cfg'], g['params'])
-    step = DecoderTrainStep(dec, need_dfeat=True)
-    loss = step.forward_train(g['feat'].float().to(DEV), g['gt'].to(DEV))
-    assert abs(float(loss) - g['loss']) < TOL * abs(g['loss'])
-    _check_grads({k: p.grad for k, p in dec.named_parameters()}, g['grads'])
-    assert rel_err(step.dfeat, g['dfeat']) < TOL
-
-
-def test_attn_config2_full_size_on_tensor_engine(tc_engine):
-    from tests.test_gpu_train import test_attn_config2_full_size_vs_reference_port
-    test_attn_config2_full_size_vs_reference_port()
-
-
-def test_lstm_and_midsize_on_tensor_engine(tc_engine):
-    from tests.test_gpu_train import test_attn_midsize_vs_oracle_fp64, test_lstm_two_layers_vs_oracle
-    test_attn_midsize_vs_oracle_fp64()
-    test_lstm_two_layers_vs_oracle()

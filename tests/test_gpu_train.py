@@ -9,7 +9,7 @@ from oracle.synth import synth_inputs
 from tests.gpu_util import DEV, build_decoder, build_lstm, random_attn_params
 from tests.util import golden_names, load_golden, rel_err
 
-pytestmark = pytest.mark.gpu
+pytestmark = [pytest.mark.gpu, pytest.mark.usefixtures('gemm_engine')]
 TOL = 1e-4
 
 
