@@ -191,7 +191,7 @@ int attn_bwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
   API_CK(col_sum(st, w.DGQ + 5 * H, SB, D, W5, G->f_beta_b, false, w.cs_scratch));
   // attention.v
   API_CK(col_sum(st, w.dwv_part, B, H, H, G->att_v_w, false, w.cs_scratch));
-  API_CK(reduce_sum(st, w.DE, B * S * L, G->att_v_b));
+  API_CK(reduce_sum(st, w.DE, B * S * L, G->att_v_b, w.reg_scratch));
   // init_h / init_c (AttentionLanguageModule.py:116-125)
   API_CK(tanh_bwd(st, B, H, w.dh_next, H, w.XH + D, DH, w.dh0, H));
   API_CK(tanh_bwd(st, B, H, w.dc, H, w.Call, H, w.dc0, H));

@@ -80,7 +80,21 @@ __global__ void __launch_bounds__(1024) reduce_sum_kernel(const float* __restric
   acc = block_sum(acc, scratch);
   if (threadIdx.x == 0) out[0] = acc;
 }
-cudaError_t reduce_sum(cudaStream_t st, const float* x, int n, float* out) {
+// stage 1 of the large-n path: one partial per block (deterministic: fixed block -> element mapping)
+__global__ void __launch_bounds__(256) reduce_partial_kernel(const float* __restrict__ x, int n, float* __restrict__ part) {
+  __shared__ float scratch[40];
+  float acc = 0.f;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) acc += x[i];
+  acc = block_sum(acc, scratch);
+  if (threadIdx.x == 0) part[blockIdx.x] = acc;
+}
+cudaError_t reduce_sum(cudaStream_t st, const float* x, int n, float* out, float* scratch) {
+  if (scratch && n > 16384) {   // scratch: >= 256 floats
+    ALEXCAP_NOTE_LAUNCH(); reduce_partial_kernel<<<256, 256, 0, st>>>(x, n, scratch);
+    ALEXCAP_LAUNCH_CHECK();
+    ALEXCAP_NOTE_LAUNCH(); reduce_sum_kernel<<<1, 1024, 0, st>>>(scratch, 256, out);
+    return cudaGetLastError();
+  }
   ALEXCAP_NOTE_LAUNCH(); reduce_sum_kernel<<<1, 1024, 0, st>>>(x, n, out);
   return cudaGetLastError();
 }

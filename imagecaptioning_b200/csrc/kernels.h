@@ -58,7 +58,7 @@ cudaError_t count_valid(cudaStream_t st, const int32_t* tgt, int N, int ignore_i
 cudaError_t ce_rows(cudaStream_t st, const float* logits, const int32_t* tgt, int N, int C, int64_t ld, float eps,
                     int ignore_index, const float* denom, float* row_loss, float* dlogits);
 // out[0] = sum(x[0..n)) (deterministic single-block tree)
-cudaError_t reduce_sum(cudaStream_t st, const float* x, int n, float* out);
+cudaError_t reduce_sum(cudaStream_t st, const float* x, int n, float* out, float* scratch = nullptr);
 
 // ---- misc (misc.cu)
 cudaError_t make_target(cudaStream_t st, const int32_t* gt, int B, int T, int start_tok, int end_tok,

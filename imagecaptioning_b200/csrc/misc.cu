@@ -31,23 +31,34 @@ cudaError_t make_target(cudaStream_t st, const int32_t* gt, int B, int T, int st
   return cudaGetLastError();
 }
 
-// mean over regions (AttentionLanguageModule.py:117)
+// mean over regions (AttentionLanguageModule.py:117): one CTA per image, D/4 float4 columns x row groups
 __global__ void __launch_bounds__(256) mean_L_kernel(const float* __restrict__ feat, int L, int D, float* __restrict__ m) {
-  const int b = blockIdx.y, D4 = D >> 2;
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= D4) return;
-  const float4* p = reinterpret_cast<const float4*>(feat) + (int64_t)b * L * D4 + c;
-  float4 acc = f4_zero();
-#pragma unroll 4
-  for (int l = 0; l < L; ++l) f4_add(acc, ldg4(p + (int64_t)l * D4));
+  __shared__ float4 red[256];
+  const int b = blockIdx.x, D4 = D >> 2, tid = threadIdx.x;
+  const float4* fb = reinterpret_cast<const float4*>(feat) + (int64_t)b * L * D4;
+  const bool wide = D4 >= 256;
+  const int G = wide ? 1 : 256 / D4;
   const float inv = 1.f / (float)L;
-  reinterpret_cast<float4*>(m)[(int64_t)b * D4 + c] = make_float4(acc.x * inv, acc.y * inv, acc.z * inv, acc.w * inv);
+  for (int c0 = 0; c0 < D4; c0 += 256) {
+    const int c = wide ? c0 + tid : tid % D4;
+    const int g = wide ? 0 : tid / D4;
+    float4 acc = f4_zero();
+    if (c < D4 && g < G) {
+#pragma unroll 8
+      for (int l = g; l < L; l += G) f4_add(acc, ldg4(fb + (int64_t)l * D4 + c));
+    }
+    red[tid] = acc;
+    __syncthreads();
+    if (g == 0 && c < D4) {
+      for (int gg = 1; gg < G; ++gg) f4_add(acc, red[gg * D4 + c]);
+      reinterpret_cast<float4*>(m)[(int64_t)b * D4 + c] = make_float4(acc.x * inv, acc.y * inv, acc.z * inv, acc.w * inv);
+    }
+    __syncthreads();
+  }
 }
 cudaError_t mean_over_L(cudaStream_t st, const float* feat, int B, int L, int D, float* m) {
   if (D & 3) return cudaErrorInvalidValue;
-  const int threads = (D / 4 >= 256) ? 256 : 64;
-  dim3 grid(ceil_div(D / 4, threads), B);
-  ALEXCAP_NOTE_LAUNCH(); mean_L_kernel<<<grid, threads, 0, st>>>(feat, L, D, m);
+  ALEXCAP_NOTE_LAUNCH(); mean_L_kernel<<<B, 256, 0, st>>>(feat, L, D, m);
   return cudaGetLastError();
 }
 

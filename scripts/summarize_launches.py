@@ -1,0 +1,16 @@
+"""Summarise an `ncu --metrics gpu__time_duration.sum --csv` launch list: per-kernel totals and shares."""
+import collections, csv, re, sys
+lines = [l for l in open(sys.argv[1]) if not l.startswith('==')]
+tot = collections.defaultdict(lambda: [0, 0.0])
+for row in csv.DictReader(lines):
+    if row.get('Metric Name') != 'gpu__time_duration.sum':
+        continue
+    name = re.sub(r'\(.*', '', row['Kernel Name'])
+    v = float(row['Metric Value'].replace(',', ''))
+    u = row['Metric Unit']
+    v = v / 1000 if u == 'ns' else v * 1000 if u == 'ms' else v
+    tot[name][0] += 1; tot[name][1] += v
+T = sum(v for _, v in tot.values())
+print(f'total {T:.1f} us over {sum(n for n, _ in tot.values())} launches')
+for k, (n, v) in sorted(tot.items(), key=lambda x: -x[1][1]):
+    print(f'{v:10.1f} us {100 * v / T:5.1f}%  n={n:3d}  avg={v / n:8.1f}  {k[:110]}')
