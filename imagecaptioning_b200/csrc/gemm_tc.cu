@@ -9,10 +9,10 @@
 // which leaves a ~2^-21 relative error.  Reported FLOPs are the algorithmic 2MNK, not 3x.
 //
 // Structure (one 128 x BN output tile per CTA, optional split-K over gridDim.z):
-//   warp 4      : TMA producer  -- cp.async.bulk.tensor.2d, 128B-swizzled tiles, STAGES-deep mbarrier ring
-//   warps 0..3  : hi/lo splitter (generic-proxy smem pass, fence.proxy.async) and, at the end, the epilogue:
+//   warp 8      : TMA producer  -- cp.async.bulk.tensor.2d, 128B-swizzled tiles, STAGES-deep mbarrier ring
+//   warps 0..7  : hi/lo splitter (generic-proxy smem pass, fence.proxy.async) and, at the end, the epilogue:
 //                 tcgen05.ld 32x32b -> registers -> smem transpose -> coalesced global stores / red.add
-//   warp 5      : TMEM allocator + single-thread tcgen05.mma issuer; tcgen05.commit frees smem stages
+//   warp 9      : TMEM allocator + single-thread tcgen05.mma issuer; tcgen05.commit frees smem stages
 // Operands may be K-major or MN-major in global memory (NT / NN / TN GEMMs without any transposition pass):
 //   K-major  tile: one TMA box {32 k, rows}, swizzle 128B   -> UMMA K-major SWIZZLE_128B layout (SBO = 1024 B)
 //   MN-major tile: rows/32 TMA boxes {32 mn, 32 k}, swizzle 128B_ATOM_32B -> UMMA MN-major SWIZZLE_128B_BASE32B layout,
@@ -30,7 +30,10 @@ namespace tc {
 constexpr int BM = 128;
 constexpr int BK = 32;            // fp32 elements per k-block = one 128-byte swizzle row
 constexpr int UMMA_K = 8;         // kind::tf32
-constexpr int NUM_THREADS = 192;
+constexpr int CONV_WARPS = 8;                 // hi/lo splitter + epilogue warps
+constexpr int CONV_THREADS = CONV_WARPS * 32;
+constexpr int TMA_WARP = CONV_WARPS, MMA_WARP = CONV_WARPS + 1;
+constexpr int NUM_THREADS = (CONV_WARPS + 2) * 32;
 constexpr uint32_t SPIN_LIMIT = 1u << 27;
 
 struct Params {
@@ -138,17 +141,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&full_bar[s], 1);
-      mbar_init(&conv_bar[s], 128);
+      mbar_init(&conv_bar[s], CONV_THREADS);
       mbar_init(&empty_bar[s], 1);
     }
     mbar_init(tmem_full_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 5) {   // TMEM allocation (power of two >= 32 columns); the same warp frees it
+  if (warp == MMA_WARP) {   // TMEM allocation (power of two >= 32 columns); the same warp frees it
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(BN));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
-  if (warp == 4 && lane == 0) {
+  if (warp == TMA_WARP && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
   }
@@ -157,7 +160,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp == 4) {
+  if (warp == TMA_WARP) {
     // ================================================================ TMA producer
     if (lane == 0) {
       for (int i = 0; i < nkb; ++i) {
@@ -182,7 +185,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
       }
     }
-  } else if (warp == 5) {
+  } else if (warp == MMA_WARP) {
     // ================================================================ MMA issuer (one elected thread)
     // instruction descriptor: D=f32, A=B=tf32, majors, N>>3, M>>4   (cute::UMMA::InstrDescriptor bit layout)
     const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
@@ -216,15 +219,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
   } else {
     // ================================================================ warps 0..3: splitter, then epilogue
-    const int t = threadIdx.x;   // 0..127
+    const int t = threadIdx.x;   // 0..CONV_THREADS-1
     for (int i = 0; i < nkb; ++i) {
       const int s = i % STAGES;
       const uint32_t ph = (i / STAGES) & 1;
       mbar_wait(&full_bar[s], ph);
       uint8_t* st = smem + s * STAGE_BYTES;
       // elementwise, so it is oblivious to the swizzle: same byte offset in the hi and lo tiles
-#pragma unroll 4
-      for (int c = t; c < (int)(A_BYTES / 16); c += 128) {
+#pragma unroll
+      for (int c = t; c < (int)(A_BYTES / 16); c += CONV_THREADS) {
         const uint4 x = *reinterpret_cast<uint4*>(st + c * 16);
         uint4 h, l;
         split_tf32(x.x, h.x, l.x); split_tf32(x.y, h.y, l.y); split_tf32(x.z, h.z, l.z); split_tf32(x.w, h.w, l.w);
@@ -232,8 +235,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         *reinterpret_cast<uint4*>(st + A_BYTES + c * 16) = l;
       }
       uint8_t* sb = st + 2 * A_BYTES;
-#pragma unroll 4
-      for (int c = t; c < (int)(B_BYTES / 16); c += 128) {
+#pragma unroll
+      for (int c = t; c < (int)(B_BYTES / 16); c += CONV_THREADS) {
         const uint4 x = *reinterpret_cast<uint4*>(sb + c * 16);
         uint4 h, l;
         split_tf32(x.x, h.x, l.x); split_tf32(x.y, h.y, l.y); split_tf32(x.z, h.z, l.z); split_tf32(x.w, h.w, l.w);
@@ -251,9 +254,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const bool first_split = (blockIdx.z == 0);
     const bool atomic = gridDim.z > 1;
 #pragma unroll 1
-    for (int cc = 0; cc < BN / 32; ++cc) {
+    const int q4 = warp & 3;                       // TMEM lane quarter this warp may read (warp id mod 4)
+    for (int cc = (warp >> 2); cc < BN / 32; cc += CONV_WARPS / 4) {
       uint32_t v[32];
-      const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(cc * 32);
+      const uint32_t taddr = tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(cc * 32);
       asm volatile(
           "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
           "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
@@ -276,7 +280,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       if (n < p.N) {
 #pragma unroll 4
         for (int r = 0; r < 32; ++r) {
-          const int m = m0 + warp * 32 + r;
+          const int m = m0 + q4 * 32 + r;
           if (m >= p.M) break;
           float x = fmaf(p.alpha, tile[r * 33 + lane], bsum);
           float* cp = p.C + (int64_t)m * p.ldc + n;
@@ -296,7 +300,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
 
   __syncthreads();
-  if (warp == 5) {
+  if (warp == MMA_WARP) {
     tcgen05_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(BN));
   }
