@@ -30,7 +30,7 @@ namespace tc {
 constexpr int BM = 128;
 constexpr int BK = 32;            // fp32 elements per k-block = one 128-byte swizzle row
 constexpr int UMMA_K = 8;         // kind::tf32
-constexpr int CONV_WARPS = 8;                 // hi/lo splitter + epilogue warps
+constexpr int CONV_WARPS = 16;                // hi/lo splitter + epilogue warps
 constexpr int CONV_THREADS = CONV_WARPS * 32;
 constexpr int TMA_WARP = CONV_WARPS, MMA_WARP = CONV_WARPS + 1;
 constexpr int NUM_THREADS = (CONV_WARPS + 2) * 32;
