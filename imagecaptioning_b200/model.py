@@ -28,7 +28,11 @@ class DecoderTrainStep:
         self.eval_mode = False
         self.ce_denominator = None          # device float tensor: global N_valid / world (data parallel), or None
         self._key = None
-        self._graph = None
+        self._graphs = [None, None]
+        self._cur = 0
+        self._copy_stream = None
+        self._copied = [None, None]         # event: H2D into buffer i finished (copy stream)
+        self._consumed = [None, None]       # event: last step reading buffer i finished (compute stream)
         self.last_alphas = None
         self.dfeat = None
 
@@ -46,7 +50,8 @@ class DecoderTrainStep:
         key = (tuple(feat.shape), tuple(gt.shape), dev, self.llm.training, self.need_dfeat)
         if key == self._key:
             return
-        self._key, self._graph = key, None
+        self._key, self._graphs, self._cur = key, [None, None], 0
+        self._copied, self._consumed = [None, None], [None, None]
         F_.ensure_device(dev)
         self._params = self.llm.param_list()
         for p in self._params:
@@ -68,10 +73,19 @@ class DecoderTrainStep:
         nbytes = F_.attn_workspace_bytes(self._dims) if self.is_attn else F_.lstm_workspace_bytes(self._dims)
         self._ws = F_.workspace(nbytes, dev)
         self._loss = torch.zeros(4, dtype=torch.float32, device=dev)
-        self._feat = torch.empty(feat.shape, dtype=torch.float32, device=dev)
-        self._gt = torch.empty(gt.shape, dtype=torch.int32, device=dev)
+        # two static input buffer sets: the step reads set `_cur` while prefetch() fills the other one
+        self._feats = [torch.empty(feat.shape, dtype=torch.float32, device=dev) for _ in range(2)]
+        self._gts = [torch.empty(gt.shape, dtype=torch.int32, device=dev) for _ in range(2)]
         self.dfeat = torch.empty_like(self._feat) if self.need_dfeat else None
         self._alphas = None
+
+    @property
+    def _feat(self):
+        return self._feats[self._cur]
+
+    @property
+    def _gt(self):
+        return self._gts[self._cur]
 
     def _launch(self):
         d = self._dims
@@ -91,7 +105,7 @@ class DecoderTrainStep:
     def run_resident(self):
         """One step on the inputs already staged in the static device buffers (bench: inputs resident in HBM)."""
         if self.use_cuda_graph and self._dims.dropout_p == 0:
-            if self._graph is None:
+            if self._graphs[self._cur] is None:
                 s = torch.cuda.Stream()
                 s.wait_stream(torch.cuda.current_stream())
                 with torch.cuda.stream(s):
@@ -100,8 +114,8 @@ class DecoderTrainStep:
                 g = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(g):
                     self._launch()
-                self._graph = g
-            self._graph.replay()
+                self._graphs[self._cur] = g
+            self._graphs[self._cur].replay()
         else:
             self._launch()
         return self._loss
@@ -119,6 +133,39 @@ class DecoderTrainStep:
         self._prepare(feat, gt, dev)
         self._feat.copy_(feat, non_blocking=True)
         self._gt.copy_(gt, non_blocking=True)
+
+    def prefetch(self, features, gt_labels):
+        """Start the H2D copy of the NEXT batch (pinned host tensors) into the idle input buffer set on a side stream,
+        so that it overlaps the step running on the current set.  Pair with swap()+run_resident()."""
+        dev = next(self.llm.parameters()).device
+        if self._key is None:
+            self.stage(features, gt_labels)     # first call sizes the buffers
+        if features.dtype != torch.float32 or gt_labels.dtype != torch.int32:
+            raise F_._lib.AlexcapError('prefetch() takes float32 features and int32 captions')
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=dev)
+        nxt = self._cur ^ 1
+        cs = self._copy_stream
+        if self._consumed[nxt] is not None:
+            cs.wait_event(self._consumed[nxt])  # the step that last read this set must have finished
+        with torch.cuda.stream(cs):
+            self._feats[nxt].copy_(features, non_blocking=True)
+            self._gts[nxt].copy_(gt_labels, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(cs)
+        self._copied[nxt] = ev
+
+    def swap(self):
+        """Make the prefetched input set current; the compute stream waits for its H2D copy."""
+        cur = torch.cuda.current_stream()
+        ev = torch.cuda.Event()
+        ev.record(cur)
+        self._consumed[self._cur] = ev
+        self._cur ^= 1
+        if self._copied[self._cur] is None:
+            raise F_._lib.AlexcapError('swap() without a preceding prefetch()')
+        cur.wait_event(self._copied[self._cur])
+        self._copied[self._cur] = None
 
     def forward_train(self, features, gt_labels):
         """features [B,L,D] (the CNN grid after permute/view, LSTMwAttentionModel.py:64-66), gt_labels [B,T] int.
