@@ -12,13 +12,20 @@
 // (~3.5 per SM) in flight and enough bytes to cover the memory latency.
 // Algorithmic bytes per step: B*L*(H+D)*4 (+ small vectors).
 #include <cooperative_groups.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "kernels.h"
+#include "pipe.cuh"
 
 namespace cg = cooperative_groups;
 
 namespace alexcap {
+
+int& attn_engine() {
+  static int e = [] { const char* v = getenv("ALEXCAP_ATT_ENGINE"); return (v && *v) ? atoi(v) : 1; }();
+  return e;
+}
 
 constexpr int ATT_THREADS = 256;
 constexpr int ATT_WARPS = ATT_THREADS / 32;
@@ -201,6 +208,9 @@ cudaError_t attn_step_fwd(cudaStream_t st, int B, int L, int D, int H, const flo
                           const float* q, int64_t q_ld, const float* bpre, int64_t bpre_ld, const float* wv,
                           float* alpha, int64_t alpha_ld, float* ctx, float* beta, float* gctx, int64_t gctx_ld,
                           int rows_per_image) {
+  if (attn_engine() == 1 && attn_stream_supported(D, H))
+    return attn_step_fwd_stream(st, B, L, D, H, Ws, feat, q, q_ld, bpre, bpre_ld, wv, alpha, alpha_ld, ctx, beta, gctx,
+                                gctx_ld, rows_per_image);
   if ((H & 3) || (D & 3) || H > 1024 || (q_ld & 3) || (bpre_ld & 3) || (gctx_ld & 3)) return cudaErrorInvalidValue;
   const int CL = pick_cluster(B, L);
   const int Lc = ceil_div(L, CL);
@@ -402,6 +412,9 @@ cudaError_t attn_step_bwd(cudaStream_t st, int B, int L, int D, int H, const flo
                           const float* dalpha_ext, int64_t ext_ld, const float* reg_r,
                           float* dq, int64_t dq_ld, float* dbpre, int64_t dbpre_ld, float* de, int64_t de_ld,
                           float* dwv_part, float* dfeat) {
+  if (attn_engine() == 1 && attn_stream_supported(D, H))
+    return attn_step_bwd_stream(st, B, L, D, H, Ws, feat, q, q_ld, wv, alpha, alpha_ld, ctx, beta, dgctx, dgctx_ld,
+                                dalpha_ext, ext_ld, reg_r, dq, dq_ld, dbpre, dbpre_ld, de, de_ld, dwv_part, dfeat);
   if ((H & 3) || (D & 3) || H > 1024 || (q_ld & 3) || (dgctx_ld & 3) || (dq_ld & 3) || (dbpre_ld & 3))
     return cudaErrorInvalidValue;
   const int CL = pick_cluster(B, L);

@@ -33,6 +33,20 @@ cudaError_t attn_step_bwd(cudaStream_t st, int B, int L, int D, int H, const flo
                           const float* dalpha_ext, int64_t ext_ld, const float* reg_r,
                           float* dq, int64_t dq_ld, float* dbpre, int64_t dbpre_ld, float* de, int64_t de_ld,
                           float* dwv_part, float* dfeat);
+// TMA-fed streaming variants (attention_stream.cu): the default engine; attention.cu keeps the direct-load kernels
+// (engine 0: ALEXCAP_ATT_ENGINE=0, or shapes the streaming kernels do not cover).
+bool attn_stream_supported(int D, int H);
+int& attn_engine();
+cudaError_t attn_step_fwd_stream(cudaStream_t st, int B, int L, int D, int H, const float* Ws, const float* feat,
+                                 const float* q, int64_t q_ld, const float* bpre, int64_t bpre_ld, const float* wv,
+                                 float* alpha, int64_t alpha_ld, float* ctx, float* beta, float* gctx, int64_t gctx_ld,
+                                 int rows_per_image);
+cudaError_t attn_step_bwd_stream(cudaStream_t st, int B, int L, int D, int H, const float* Ws, const float* feat,
+                                 const float* q, int64_t q_ld, const float* wv, const float* alpha, int64_t alpha_ld,
+                                 const float* ctx, const float* beta, const float* dgctx, int64_t dgctx_ld,
+                                 const float* dalpha_ext, int64_t ext_ld, const float* reg_r,
+                                 float* dq, int64_t dq_ld, float* dbpre, int64_t dbpre_ld, float* de, int64_t de_ld,
+                                 float* dwv_part, float* dfeat);
 // dWs[b,l,h] = wv[h] * sum_t de[b,t,l] * (1 - tanh^2(Ws[b,l,h] + q[t,b,h]));  q: [S][B] rows of stride q_ld,
 // de: [B][S][L].
 cudaError_t attn_dws(cudaStream_t st, int B, int L, int H, int S, const float* Ws, const float* q, int64_t q_ld,

@@ -1,0 +1,89 @@
+// pipe.cuh -- mbarrier + TMA bulk-copy (cp.async.bulk, 1-D) helpers for the streaming kernels (sm_100a).
+#pragma once
+#include "common.cuh"
+
+namespace alexcap {
+namespace pipe {
+
+constexpr uint32_t SPIN_LIMIT = 1u << 27;    // a protocol bug must trap, not hang the GPU box
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t spins = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    if (++spins > SPIN_LIMIT) __trap();
+  }
+}
+// 1-D bulk copy global -> shared (TMA engine), completion counted in bytes on an mbarrier.
+// dst/src 16-byte aligned, bytes a multiple of 16.
+__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+      ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+// Named barrier over the first `nthreads` consumer threads (the producer warp never joins it).
+__device__ __forceinline__ void named_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+// Reductions over `nwarp` consumer warps synchronised with a named barrier. scratch >= 34 floats.
+__device__ __forceinline__ float group_sum(float v, float* scratch, int nwarp, int bar_id) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  v = warp_sum(v);
+  if (lane == 0) scratch[warp] = v;
+  named_sync(bar_id, nwarp * 32);
+  float r = (lane < nwarp) ? scratch[lane] : 0.f;
+  r = warp_sum(r);
+  named_sync(bar_id, nwarp * 32);
+  return r;
+}
+__device__ __forceinline__ float group_max(float v, float* scratch, int nwarp, int bar_id) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  v = warp_max(v);
+  if (lane == 0) scratch[warp] = v;
+  named_sync(bar_id, nwarp * 32);
+  float r = (lane < nwarp) ? scratch[lane] : -INFINITY;
+  r = warp_max(r);
+  named_sync(bar_id, nwarp * 32);
+  return r;
+}
+
+}  // namespace pipe
+
+__device__ __forceinline__ float ex2_ftz(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float rcp_ftz(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+// 2*log2(e): tanh(x) = 1 - 2 r with r = 1 / (2^(TANH_C x) + 1)   (two MUFU ops, ~2e-7 absolute error, saturates correctly)
+constexpr float TANH_C = 2.8853900817779268f;
+__device__ __forceinline__ float tanh_r(float x_scaled) { return rcp_ftz(ex2_ftz(x_scaled) + 1.f); }
+
+// tanh with ~2e-7 absolute error from two MUFU ops (ex2, rcp): 1 - 2 / (e^{2x} + 1).  Saturates correctly
+// (e -> inf gives 1, e -> 0 gives -1).
+__device__ __forceinline__ float tanh_fast(float x) {
+  const float e = __expf(2.f * x);
+  return 1.f - __fdividef(2.f, e + 1.f);
+}
+
+}  // namespace alexcap

@@ -54,7 +54,9 @@ def _attn_ref(Ws, feat, q, bpre, wv):
     return alpha, ctx, beta, beta * ctx
 
 
-@pytest.mark.parametrize('B,L,D,H', [(5, 11, 24, 20), (3, 196, 512, 512), (2, 49, 2048, 1024), (4, 7, 132, 260)])
+# B > 148 SMs: the persistent kernels cut images across CTAs (global-scratch combine, mixed whole/split segments)
+@pytest.mark.parametrize('B,L,D,H', [(5, 11, 24, 20), (3, 196, 512, 512), (2, 49, 2048, 1024), (4, 7, 132, 260),
+                                     (150, 20, 24, 20), (301, 9, 16, 12), (160, 196, 128, 64), (700, 5, 8, 8)])
 def test_attn_step_fwd_and_bwd(F_, B, L, D, H):
     g = torch.Generator().manual_seed(B * 7 + L)
     Ws = torch.randn(B, L, H, generator=g, dtype=torch.float64)
@@ -88,6 +90,26 @@ def test_attn_step_fwd_and_bwd(F_, B, L, D, H):
     a = ra.detach()
     de_ref = a * (dal - (a * dal).sum(1, keepdim=True))
     assert rel_err(de, de_ref) < 2e-5
+
+
+def test_attn_step_back_to_back_is_deterministic(F_):
+    """Many launches in flight with warm caches (the timing in which a ring-protocol race would show): every launch
+    must reproduce the first result bit for bit, for whole-image and split-image partitions."""
+    for B, L, D, H in [(128, 196, 512, 512), (512, 49, 256, 128), (333, 60, 128, 256)]:
+        g = torch.Generator().manual_seed(B)
+        f = lambda *s: torch.randn(*s, generator=g).to(DEV)
+        Ws, feat, q, bpre, wv, dg = f(B, L, H), f(B, L, D).relu(), f(B, H), f(B, D), f(H) / H ** 0.5, f(B, D)
+        first = F_.attn_step_fwd(Ws, feat, q, bpre, wv)
+        bfirst = F_.attn_step_bwd(Ws, feat, q, wv, first[0], first[1], first[2], dg)
+        ref = _attn_ref(Ws.double().cpu(), feat.double().cpu(), q.double().cpu(), bpre.double().cpu(), wv.double().cpu())
+        assert rel_err(first[0], ref[0]) < 1e-5 and rel_err(first[3], ref[3]) < 1e-5
+        outs = [F_.attn_step_fwd(Ws, feat, q, bpre, wv) for _ in range(40)]
+        bouts = [F_.attn_step_bwd(Ws, feat, q, wv, first[0], first[1], first[2], dg) for _ in range(40)]
+        torch.cuda.synchronize()
+        for o in outs:
+            assert all(torch.equal(x, y) for x, y in zip(o, first))
+        for o in bouts:
+            assert all(torch.equal(x, y) for x, y in zip(o[:4], bfirst[:4]))
 
 
 def test_make_target_matches_reference_semantics(F_):
