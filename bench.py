@@ -115,22 +115,35 @@ def make_model(c, dev):
     return m.to(dev)
 
 
-def time_kernel_events(fn, iters, warm=3):
+def time_graph_events(fn, launches_per_graph, reps, warm=2):
+    """`launches_per_graph` launches captured into one CUDA graph, replayed `reps` times and timed with CUDA events on
+    the launching stream: the Python/ctypes call costs ~25 us per launch, more than the kernel itself."""
     for _ in range(warm):
         fn()
     torch.cuda.synchronize()
-    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    s.record()
-    for _ in range(iters):
-        fn()
-    e.record()
-    torch.cuda.synchronize()
-    return s.elapsed_time(e) / iters
+    st = torch.cuda.Stream()
+    st.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(st):
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=st):
+            for _ in range(launches_per_graph):
+                fn()
+        g.replay()
+        st.synchronize()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record(st)
+        for _ in range(reps):
+            g.replay()
+        e.record(st)
+        st.synchronize()
+    torch.cuda.current_stream().wait_stream(st)
+    return s.elapsed_time(e) / (reps * launches_per_graph)
 
 
 def dominant_kernel_roofline(c, dev, pk):
-    """The fused attention-step kernel timed alone (CUDA events on the launching stream) at the bench shape.
-    S distinct q/bpre slices per pass over the same Ws/feat, exactly as inside a training step."""
+    """The fused attention-step kernels (forward and backward: 34 launches per training step, each streaming Ws and
+    feat once) timed alone at the bench shape.  S distinct q/bpre slices per pass over the same Ws/feat, exactly as
+    inside a training step; launches replayed from a CUDA graph, CUDA events on the launching stream."""
     from imagecaptioning_b200 import functional as F_
     B, L, D, H, S = c['B'], c['L'], c['D'], c['H'], c['T'] + 1
     g = torch.Generator(device='cpu').manual_seed(1)
@@ -138,21 +151,41 @@ def dominant_kernel_roofline(c, dev, pk):
     feat = torch.randn(B, L, D, generator=g).relu().to(dev)
     q = torch.randn(S, B, H, generator=g).to(dev)
     bp = torch.randn(S, B, D, generator=g).to(dev)
+    dg = torch.randn(S, B, D, generator=g).to(dev)
     wv = (torch.randn(H, generator=g) / H ** 0.5).to(dev)
+    outs = [F_.attn_step_fwd(Ws, feat, q[t], bp[t], wv) for t in range(S)]
     state = {'t': 0}
 
     def fwd():
         t = state['t'] = (state['t'] + 1) % S
         F_.attn_step_fwd(Ws, feat, q[t], bp[t], wv)
 
-    ms = time_kernel_events(fwd, 4 * S)
+    def bwd():
+        t = state['t'] = (state['t'] + 1) % S
+        a, cx, be, _ = outs[t]
+        F_.attn_step_bwd(Ws, feat, q[t], wv, a, cx, be, dg[t])
+
+    ms_f = time_graph_events(fwd, S, 12)
+    ms_b = time_graph_events(bwd, S, 12)
     w = algorithmic_work(c)
-    ach = w['attn_fwd_bytes_per_launch'] / (ms * 1e-3) / 1e9
-    return dict(kernel='attn_fwd_kernel', bound='hbm', achieved=round(ach, 1), peak=pk['hbm'], unit='GB/s',
-                frac=round(ach / pk['hbm'], 4), traffic=None, ms_per_launch=round(ms, 5),
+    ach = w['attn_fwd_bytes_per_launch'] / (ms_f * 1e-3) / 1e9
+    ach_b = w['attn_bwd_bytes_per_launch'] / (ms_b * 1e-3) / 1e9
+    return dict(kernel='attn_fwd_stream_kernel', bound='hbm', achieved=round(ach, 1), peak=pk['hbm'], unit='GB/s',
+                frac=round(ach / pk['hbm'], 4), traffic=NCU_TRAFFIC.get('attn_fwd'), ms_per_launch=round(ms_f, 5),
                 algorithmic_bytes_per_launch=w['attn_fwd_bytes_per_launch'], peak_source=pk['src'],
-                note='working set Ws+feat = %.0f MB vs 126 MB L2: part of it is L2-resident across steps; '
-                     'see profiles/ for dram__bytes' % (2 * B * L * max(H, D) * 4 / 1e6))
+                backward=dict(kernel='attn_bwd_stream_kernel', achieved=round(ach_b, 1), frac=round(ach_b / pk['hbm'], 4),
+                              ms_per_launch=round(ms_b, 5), algorithmic_bytes_per_launch=w['attn_bwd_bytes_per_launch'],
+                              traffic=NCU_TRAFFIC.get('attn_bwd')),
+                note='Ws+feat = %.0f MB per launch, re-read by each of the 2*S launches of a step; with a 126 MB L2 part '
+                     'of it can hit L2 between consecutive launches (ncu, cache flushed: dram__bytes_read = algorithmic '
+                     'bytes, see profiles/)' % (2 * B * L * max(H, D) * 4 / 1e6))
+
+
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` captures (profiles/)
+NCU_TRAFFIC = {}
+_t = os.path.join(ROOT, 'profiles', 'ncu_traffic.json')
+if os.path.exists(_t):
+    NCU_TRAFFIC = json.load(open(_t))
 
 
 def cpu_port(c):

@@ -13,6 +13,8 @@
 //   reverse loop:    pointwise bwd, dgctx GEMM, fused attention bwd, dh_{t-1} GEMM
 //   after the loop:  every weight gradient as ONE GEMM over K = S*B rows (the "fused dW accumulation"),
 //                    dWs in one pass, embedding scatter-add, init-state gradients.
+#include <stdlib.h>
+
 #include "api_util.h"
 
 using namespace alexcap;
@@ -25,6 +27,10 @@ char* err_buf() {
 unsigned long long& launch_counter() {
   static unsigned long long n = 0;
   return n;
+}
+bool& pdl_enabled() {
+  static bool on = [] { const char* v = getenv("ALEXCAP_PDL"); return !(v && v[0] == '0'); }();
+  return on;
 }
 }  // namespace alexcap
 
@@ -72,9 +78,9 @@ AttnWs attn_layout(const alexcap_dims* d, void* base, bool with_logits) {
   w.row_loss = a.take<float>(S * B);
   w.scal = a.take<float>(64);
   w.dHout = a.take<float>(S * B * H);
-  w.dh_next = a.take<float>(B * H);
+  w.dh_next = a.take<float>(S * B * H);       // slot t: dh_{t-1} produced by reverse step t (zeroed once per step)
   w.dc = a.take<float>(B * H);
-  w.dgctx = a.take<float>(B * D);
+  w.dgctx = a.take<float>(S * B * D);         // slot t: d gctx_t (zeroed once per step: split-K GEMMs red.add into it)
   w.R = a.take<float>(B * L);
   w.dwv_part = a.take<float>(B * H);
   w.dWs = a.take<float>(B * L * H);
@@ -114,11 +120,14 @@ int attn_fwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
   API_CK(cudaMemcpyAsync(w.bub, P->att_U_b, sizeof(float) * H, cudaMemcpyDeviceToDevice, st));
   API_CK(cudaMemcpyAsync(w.bub + H, P->f_beta_b, sizeof(float) * D, cudaMemcpyDeviceToDevice, st));
 
+  // the per-step split-K GEMMs accumulate with red.add: their outputs are zeroed here, once, instead of by a memset
+  // node in front of every GEMM (which would also cut the programmatic-dependent-launch chain of the time loop)
+  API_CK(cudaMemsetAsync(w.QB, 0, sizeof(float) * (size_t)S * B * HD, st));
   for (int t = 0; t < S; ++t) {                                            // AttentionLanguageModule.py:72
     float* xh = w.XH + (int64_t)t * B * DH;
     float* qb = w.QB + (int64_t)t * B * HD;
     float* g = w.DGQ + (int64_t)t * B * W5;
-    API_CK(gemm_f32(st, false, true, B, H + D, H, 1.f, xh + D, DH, w.Wub, H, qb, HD, w.bub, nullptr, false, ACT_NONE));
+    API_CK(gemm_f32(st, false, true, B, H + D, H, 1.f, xh + D, DH, w.Wub, H, qb, HD, w.bub, nullptr, true, ACT_NONE));
     API_CK(attn_step_fwd(st, B, L, D, H, w.Ws, feat, qb, HD, qb + H, HD, P->att_v_w, w.ALPHA + (int64_t)t * L,
                          (int64_t)S * L, w.CTX + (int64_t)t * B * D, w.BETA + (int64_t)t * B * D, xh, DH));
     API_CK(gemm_f32(st, false, true, B, 4 * H, D + H, 1.f, xh, DH, w.Wcat, DH, g, W5, nullptr, nullptr, true, ACT_NONE));
@@ -148,23 +157,27 @@ int attn_bwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
   API_CK(fill_f32(st, w.dc, (int64_t)B * H, 0.f));
   API_CK(fill_f32(st, w.dwv_part, (int64_t)B * H, 0.f));
   if (need_dfeat) API_CK(fill_f32(st, dfeat, (int64_t)B * L * D, 0.f));
+  API_CK(cudaMemsetAsync(w.dgctx, 0, sizeof(float) * (size_t)S * B * D, st));
+  API_CK(cudaMemsetAsync(w.dh_next, 0, sizeof(float) * (size_t)S * B * H, st));
 
   for (int t = S - 1; t >= 0; --t) {
+    float* dgc = w.dgctx + (int64_t)t * B * D;
+    float* dhn = w.dh_next + (int64_t)t * B * H;                  // dh_{t-1}, consumed by reverse step t-1
     float* g = w.DGQ + (int64_t)t * B * W5;
     const float* qb = w.QB + (int64_t)t * B * HD;
     API_CK(lstm_pointwise_bwd(st, B, H, g, W5, w.Call + (int64_t)(t + 1) * B * H, w.Call + (int64_t)t * B * H,
                               w.dHout + (int64_t)t * B * H, H, w.MASK ? w.MASK + (int64_t)t * B * H : nullptr,
-                              (t == S - 1) ? nullptr : w.dh_next, H, w.dc));
+                              (t == S - 1) ? nullptr : dhn + (int64_t)B * H, H, w.dc));
     // d gctx = dgates W_ih[:, E:]
-    API_CK(gemm_f32(st, false, false, B, D, 4 * H, 1.f, g, W5, P->lstm_w_ih + E, E + D, w.dgctx, D, nullptr, nullptr,
-                    false, ACT_NONE));
+    API_CK(gemm_f32(st, false, false, B, D, 4 * H, 1.f, g, W5, P->lstm_w_ih + E, E + D, dgc, D, nullptr, nullptr,
+                    true, ACT_NONE));
     API_CK(attn_step_bwd(st, B, L, D, H, w.Ws, feat, qb, HD, P->att_v_w, w.ALPHA + (int64_t)t * L, (int64_t)S * L,
-                         w.CTX + (int64_t)t * B * D, w.BETA + (int64_t)t * B * D, w.dgctx, D,
+                         w.CTX + (int64_t)t * B * D, w.BETA + (int64_t)t * B * D, dgc, D,
                          dalphas ? dalphas + (int64_t)t * L : nullptr, (int64_t)S * L, reg_r,
                          g + 4 * H, W5, g + 5 * H, W5, w.DE + (int64_t)t * L, (int64_t)S * L, w.dwv_part,
                          need_dfeat ? dfeat : nullptr));
     // dh_{t-1} = [dgates | dq | dbpre] [W_hh ; W_U ; W_beta]
-    API_CK(gemm_f32(st, false, false, B, H, (int)W5, 1.f, g, W5, w.Wback, H, w.dh_next, H, nullptr, nullptr, false, ACT_NONE));
+    API_CK(gemm_f32(st, false, false, B, H, (int)W5, 1.f, g, W5, w.Wback, H, dhn, H, nullptr, nullptr, true, ACT_NONE));
   }
 
   const int SB = S * B;

@@ -244,6 +244,8 @@ __global__ void __launch_bounds__(SA_THREADS, 1) attn_fwd_stream_kernel(const SA
     pipe::mbar_fence_init();
   }
   __syncthreads();
+  pdl_trigger();
+  pdl_wait();
 
   if (warp == SA_CWARPS) {
     if (lane == 0) {
@@ -505,11 +507,11 @@ cudaError_t attn_step_fwd_stream(cudaStream_t st, int B, int L, int D, int H, co
     if (H == 128 * NJ) {                                                                    \
       ACK(set_smem(attn_fwd_stream_kernel<NJ, true>, smem));                                \
       ALEXCAP_NOTE_LAUNCH();                                                                \
-      attn_fwd_stream_kernel<NJ, true><<<g.nCTA, SA_THREADS, smem, st>>>(a);                \
+      ACK(launch_pdl(attn_fwd_stream_kernel<NJ, true>, dim3(g.nCTA), dim3(SA_THREADS), smem, st, a));   \
     } else {                                                                                \
       ACK(set_smem(attn_fwd_stream_kernel<NJ, false>, smem));                               \
       ALEXCAP_NOTE_LAUNCH();                                                                \
-      attn_fwd_stream_kernel<NJ, false><<<g.nCTA, SA_THREADS, smem, st>>>(a);               \
+      ACK(launch_pdl(attn_fwd_stream_kernel<NJ, false>, dim3(g.nCTA), dim3(SA_THREADS), smem, st, a));  \
     }                                                                                       \
     return cudaGetLastError();                                                              \
   } while (0)
@@ -566,6 +568,8 @@ __global__ void __launch_bounds__(SA_THREADS, 1) attn_bwd_stream_kernel(const SA
     pipe::mbar_fence_init();
   }
   __syncthreads();
+  pdl_trigger();
+  pdl_wait();
 
   if (warp == SA_CWARPS) {
     if (lane == 0) {
@@ -818,8 +822,7 @@ cudaError_t attn_step_bwd_stream(cudaStream_t st, int B, int L, int D, int H, co
   const size_t smem = (size_t)g.NST * g.stage_floats * 4 + bwd_fixed_smem(D, H, seg_pad, rp_pad, g.maxseg);
   ACK(set_smem(attn_bwd_stream_kernel, smem));
   ALEXCAP_NOTE_LAUNCH();
-  attn_bwd_stream_kernel<<<g.nCTA, SA_THREADS, smem, st>>>(a);
-  return cudaGetLastError();
+  return launch_pdl(attn_bwd_stream_kernel, dim3(g.nCTA), dim3(SA_THREADS), smem, st, a);
 }
 
 

@@ -18,6 +18,28 @@ namespace alexcap {
 unsigned long long& launch_counter();
 #define ALEXCAP_NOTE_LAUNCH() (++alexcap::launch_counter())
 
+// Programmatic dependent launch (PDL).  The per-timestep chain (query GEMM -> attention -> gates GEMM -> LSTM pointwise,
+// and its mirror image in the backward pass) is ~140 short kernels; with PDL the next kernel's CTAs are scheduled
+// while the previous kernel drains and run their prologue (barrier init, TMEM allocation, tensor-map prefetch)
+// before blocking in pdl_wait() until the previous grid has completed and flushed its writes.  Both instructions
+// are no-ops in a kernel launched without the attribute.  Rule: no global read of produced data and no global
+// write before pdl_wait().
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+bool& pdl_enabled();     // api.cu; ALEXCAP_PDL=0 disables
+
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                     Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 static inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }
 static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }

@@ -159,6 +159,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_trigger();      // the next kernel in the stream may start its own prologue
+  pdl_wait();         // everything above overlapped the previous kernel's tail; its results are visible from here on
 
   if (warp == TMA_WARP) {
     // ================================================================ TMA producer
@@ -353,8 +355,7 @@ static cudaError_t launch(cudaStream_t st, const CUtensorMap& ta, const CUtensor
     configured = true;
   }
   ALEXCAP_NOTE_LAUNCH();
-  kern<<<grid, NUM_THREADS, SMEM, st>>>(ta, tb, p);
-  return cudaGetLastError();
+  return launch_pdl(kern, grid, dim3(NUM_THREADS), SMEM, st, ta, tb, p);
 }
 
 }  // namespace tc

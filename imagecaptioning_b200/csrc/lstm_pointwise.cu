@@ -12,6 +12,8 @@ __global__ void __launch_bounds__(256) lstm_fwd_kernel(int B, int H, float* __re
                                                        float* __restrict__ h_out2, int64_t h2_ld) {
   const int H4 = H >> 2;
   const int64_t n = (int64_t)B * H4;
+  pdl_trigger();
+  pdl_wait();
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const int b = (int)(i / H4), c = (int)(i % H4);
     float4* g = reinterpret_cast<float4*>(gates + (int64_t)b * g_ld);
@@ -35,8 +37,8 @@ cudaError_t lstm_pointwise_fwd(cudaStream_t st, int B, int H, float* gates, int6
   if ((H & 3) || (g_ld & 3) || (h_ld & 3) || (h_out2 && (h2_ld & 3))) return cudaErrorInvalidValue;
   const int64_t n = (int64_t)B * (H / 4);
   const int blocks = (int)((n + 255) / 256);
-  ALEXCAP_NOTE_LAUNCH(); lstm_fwd_kernel<<<blocks, 256, 0, st>>>(B, H, gates, g_ld, c_prev, c_out, h_out, h_ld, h_out2, h2_ld);
-  return cudaGetLastError();
+  ALEXCAP_NOTE_LAUNCH();
+  return launch_pdl(lstm_fwd_kernel, dim3(blocks), dim3(256), 0, st, B, H, gates, g_ld, c_prev, c_out, h_out, h_ld, h_out2, h2_ld);
 }
 
 __global__ void __launch_bounds__(256) lstm_bwd_kernel(int B, int H, float* __restrict__ gates, int64_t g_ld,
@@ -46,6 +48,8 @@ __global__ void __launch_bounds__(256) lstm_bwd_kernel(int B, int H, float* __re
                                                        const float* __restrict__ dh_b, int64_t dhb_ld,
                                                        float* __restrict__ dc_io) {
   const int64_t n = (int64_t)B * H;
+  pdl_trigger();
+  pdl_wait();
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const int b = (int)(i / H), h = (int)(i % H);
     float* g = gates + (int64_t)b * g_ld;
@@ -73,8 +77,8 @@ cudaError_t lstm_pointwise_bwd(cudaStream_t st, int B, int H, float* gates, int6
                                const float* dh_b, int64_t dhb_ld, float* dc_io) {
   const int64_t n = (int64_t)B * H;
   const int blocks = (int)((n + 255) / 256);
-  ALEXCAP_NOTE_LAUNCH(); lstm_bwd_kernel<<<blocks, 256, 0, st>>>(B, H, gates, g_ld, c_t, c_prev, dh_a, dha_ld, mask_a, dh_b, dhb_ld, dc_io);
-  return cudaGetLastError();
+  ALEXCAP_NOTE_LAUNCH();
+  return launch_pdl(lstm_bwd_kernel, dim3(blocks), dim3(256), 0, st, B, H, gates, g_ld, c_t, c_prev, dh_a, dha_ld, mask_a, dh_b, dhb_ld, dc_io);
 }
 
 }  // namespace alexcap
