@@ -284,10 +284,9 @@ def main():
     lib = _lib.load()
 
     def one_step_resident():
-        loss4 = step.run_resident()
-        if reducer:
-            reducer.allreduce()
-        return loss4
+        if reducer:                  # all-reduce of the vocab-projection bucket overlapped with the reverse chain
+            return reducer.step_overlapped()
+        return step.run_resident()
 
     def barrier():
         if dist:

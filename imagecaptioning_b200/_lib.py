@@ -53,6 +53,7 @@ PROTOTYPES = {
     'alexcap_get_gemm_engine': (C.c_int, []),
     'alexcap_attn_workspace_bytes': (_SZ, [_DP]),
     'alexcap_attn_train_fused': (C.c_int, [_DP, _AP, _P, _P, _AP, _P, _P, _P, _P, _P, _P, _SZ, _P]),
+    'alexcap_attn_train_phase': (C.c_int, [_DP, _AP, _P, _P, _AP, _P, _P, _P, _P, _P, _P, _SZ, C.c_int32, _P]),
     'alexcap_attn_forward': (C.c_int, [_DP, _AP, _P, _P, _P, _P, _P, _P, _SZ, _P]),
     'alexcap_attn_backward': (C.c_int, [_DP, _AP, _P, _P, _P, _AP, _P, _P, _SZ, _P]),
     'alexcap_lstm_workspace_bytes': (_SZ, [_DP]),

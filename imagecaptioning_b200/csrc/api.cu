@@ -261,37 +261,59 @@ size_t alexcap_attn_workspace_bytes(const alexcap_dims* d) {
   return attn_layout(d, nullptr, true).bytes;
 }
 
-int alexcap_attn_train_fused(const alexcap_dims* d, const alexcap_attn_params* P, const float* feat, const int32_t* gt,
+// phase bit 1: forward + loss + vocabulary backward (deep_output.{weight,bias} gradients final afterwards);
+// phase bit 2: reverse-time chain + every other weight gradient.  3 = the whole step.
+static int attn_train_phases(const alexcap_dims* d, const alexcap_attn_params* P, const float* feat, const int32_t* gt,
                              const alexcap_attn_params* G, float* dfeat, float* loss_out, float* alphas_out,
                              const float* drop_mask, const float* ce_denominator, void* workspace,
-                             size_t workspace_bytes, void* stream) {
+                             size_t workspace_bytes, int phase, void* stream) {
   if (int rc = check_dims_common(d)) return rc;
   AttnWs w = attn_layout(d, nullptr, true);
   if (int rc = check_attn_args(d, P, feat, workspace, workspace_bytes, w.bytes)) return rc;
   if (!gt || !G || !loss_out) return fail(ALEXCAP_E_BADARG, "NULL gt / grads / loss_out");
+  if (phase < 1 || phase > 3) return fail(ALEXCAP_E_BADARG, "phase must be 1, 2 or 3");
   w = attn_layout(d, workspace, true);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int B = d->B, D = d->D, H = d->H, Vp = d->Vp, S = d->S, L = d->L, SB = S * B;
   const int64_t DH = D + H;
-  if (int rc = attn_fwd_core(d, P, feat, gt, drop_mask, w, st)) return rc;
-  const float* hout = w.Hd ? w.Hd : w.XH + (int64_t)B * DH + D;
-  const int64_t hld = w.Hd ? H : DH;
-  // vocabulary projection for all steps at once (AttentionLanguageModule.py:79) + CustomCrossEntropyLoss
-  API_CK(gemm_f32(st, false, true, SB, Vp, H, 1.f, hout, hld, P->deep_w, H, w.logits, w.ldV, P->deep_b, nullptr, false, ACT_NONE));
-  API_CK(count_valid(st, w.tgt_tm, SB, d->ignore_index, w.scal));
-  API_CK(ce_rows(st, w.logits, w.tgt_tm, SB, Vp, w.ldV, d->label_smoothing, d->ignore_index,
-                 ce_denominator ? ce_denominator : w.scal, w.row_loss, w.logits));
-  API_CK(reduce_sum(st, w.row_loss, SB, w.scal + 1));
   const bool reg = d->reg_weight != 0.f;
-  if (reg) API_CK(attn_regulariser(st, B, S, L, d->reg_weight, w.ALPHA, w.R, w.scal + 2, w.reg_scratch));
-  API_CK(finalize_loss(st, w.scal + 1, reg ? w.scal + 2 : nullptr, w.scal, loss_out));
-  if (alphas_out)
-    API_CK(cudaMemcpyAsync(alphas_out, w.ALPHA, sizeof(float) * (size_t)B * S * L, cudaMemcpyDeviceToDevice, st));
-  // vocab backward: dH = dlogits W_o ; dW_o = dlogits^T H ; db_o = colsum(dlogits)
-  API_CK(gemm_f32(st, false, false, SB, H, Vp, 1.f, w.logits, w.ldV, P->deep_w, H, w.dHout, H, nullptr, nullptr, false, ACT_NONE));
-  API_CK(gemm_f32(st, true, false, Vp, H, SB, 1.f, w.logits, w.ldV, hout, hld, G->deep_w, H, nullptr, nullptr, false, ACT_NONE));
-  API_CK(col_sum(st, w.logits, SB, Vp, w.ldV, G->deep_b, false, w.cs_scratch));
-  return attn_bwd_core(d, P, feat, nullptr, reg ? w.R : nullptr, G, dfeat, w, st);
+  if (phase & 1) {
+    if (int rc = attn_fwd_core(d, P, feat, gt, drop_mask, w, st)) return rc;
+    const float* hout = w.Hd ? w.Hd : w.XH + (int64_t)B * DH + D;
+    const int64_t hld = w.Hd ? H : DH;
+    // vocabulary projection for all steps at once (AttentionLanguageModule.py:79) + CustomCrossEntropyLoss
+    API_CK(gemm_f32(st, false, true, SB, Vp, H, 1.f, hout, hld, P->deep_w, H, w.logits, w.ldV, P->deep_b, nullptr, false, ACT_NONE));
+    API_CK(count_valid(st, w.tgt_tm, SB, d->ignore_index, w.scal));
+    API_CK(ce_rows(st, w.logits, w.tgt_tm, SB, Vp, w.ldV, d->label_smoothing, d->ignore_index,
+                   ce_denominator ? ce_denominator : w.scal, w.row_loss, w.logits));
+    API_CK(reduce_sum(st, w.row_loss, SB, w.scal + 1));
+    if (reg) API_CK(attn_regulariser(st, B, S, L, d->reg_weight, w.ALPHA, w.R, w.scal + 2, w.reg_scratch));
+    API_CK(finalize_loss(st, w.scal + 1, reg ? w.scal + 2 : nullptr, w.scal, loss_out));
+    if (alphas_out)
+      API_CK(cudaMemcpyAsync(alphas_out, w.ALPHA, sizeof(float) * (size_t)B * S * L, cudaMemcpyDeviceToDevice, st));
+    // vocab backward: dW_o = dlogits^T H ; db_o = colsum(dlogits) ; dH = dlogits W_o
+    API_CK(gemm_f32(st, true, false, Vp, H, SB, 1.f, w.logits, w.ldV, hout, hld, G->deep_w, H, nullptr, nullptr, false, ACT_NONE));
+    API_CK(col_sum(st, w.logits, SB, Vp, w.ldV, G->deep_b, false, w.cs_scratch));
+    API_CK(gemm_f32(st, false, false, SB, H, Vp, 1.f, w.logits, w.ldV, P->deep_w, H, w.dHout, H, nullptr, nullptr, false, ACT_NONE));
+  }
+  if (phase & 2) return attn_bwd_core(d, P, feat, nullptr, reg ? w.R : nullptr, G, dfeat, w, st);
+  return 0;
+}
+
+int alexcap_attn_train_fused(const alexcap_dims* d, const alexcap_attn_params* P, const float* feat, const int32_t* gt,
+                             const alexcap_attn_params* G, float* dfeat, float* loss_out, float* alphas_out,
+                             const float* drop_mask, const float* ce_denominator, void* workspace,
+                             size_t workspace_bytes, void* stream) {
+  return attn_train_phases(d, P, feat, gt, G, dfeat, loss_out, alphas_out, drop_mask, ce_denominator, workspace,
+                           workspace_bytes, 3, stream);
+}
+
+int alexcap_attn_train_phase(const alexcap_dims* d, const alexcap_attn_params* P, const float* feat, const int32_t* gt,
+                             const alexcap_attn_params* G, float* dfeat, float* loss_out, float* alphas_out,
+                             const float* drop_mask, const float* ce_denominator, void* workspace,
+                             size_t workspace_bytes, int32_t phase, void* stream) {
+  return attn_train_phases(d, P, feat, gt, G, dfeat, loss_out, alphas_out, drop_mask, ce_denominator, workspace,
+                           workspace_bytes, phase, stream);
 }
 
 int alexcap_attn_forward(const alexcap_dims* d, const alexcap_attn_params* P, const float* feat, const int32_t* gt,

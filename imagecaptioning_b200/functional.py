@@ -162,16 +162,18 @@ def attn_workspace_bytes(dims: Dims) -> int:
 
 
 def attn_train_fused(dims, params, feat, gt, grads, ws, dfeat=None, loss_out=None, alphas_out=None, drop_mask=None,
-                     ce_denominator=None):
+                     ce_denominator=None, phase=3):
+    """phase 3: the whole step.  phase 1 (forward + loss + vocab backward) then phase 2 (reverse chain + the other
+    weight gradients) is the same step in two calls (data-parallel overlap of the first gradient bucket)."""
     lib = ensure_device(feat.device)
     _req(feat, gt, dfeat, loss_out, alphas_out, drop_mask, ce_denominator, ws)
     if loss_out is None:
         loss_out = torch.empty(4, dtype=torch.float32, device=feat.device)
     P = attn_param_struct(params)
     G = attn_param_struct(grads)
-    check(lib.alexcap_attn_train_fused(C.byref(dims), C.byref(P), _ptr(feat), _ptr(gt), C.byref(G), _ptr(dfeat),
+    check(lib.alexcap_attn_train_phase(C.byref(dims), C.byref(P), _ptr(feat), _ptr(gt), C.byref(G), _ptr(dfeat),
                                        _ptr(loss_out), _ptr(alphas_out), _ptr(drop_mask), _ptr(ce_denominator),
-                                       _ptr(ws), ws.numel(), _stream()), 'alexcap_attn_train_fused')
+                                       _ptr(ws), ws.numel(), int(phase), _stream()), 'alexcap_attn_train_phase')
     return loss_out
 
 

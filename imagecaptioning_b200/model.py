@@ -28,7 +28,7 @@ class DecoderTrainStep:
         self.eval_mode = False
         self.ce_denominator = None          # device float tensor: global N_valid / world (data parallel), or None
         self._key = None
-        self._graphs = [None, None]
+        self._graphs = {}                   # (input set, phase) -> captured CUDA graph
         self._cur = 0
         self._copy_stream = None
         self._copied = [None, None]         # event: H2D into buffer i finished (copy stream)
@@ -50,7 +50,7 @@ class DecoderTrainStep:
         key = (tuple(feat.shape), tuple(gt.shape), dev, self.llm.training, self.need_dfeat)
         if key == self._key:
             return
-        self._key, self._graphs, self._cur = key, [None, None], 0
+        self._key, self._graphs, self._cur = key, {}, 0
         self._copied, self._consumed = [None, None], [None, None]
         F_.ensure_device(dev)
         self._params = self.llm.param_list()
@@ -87,37 +87,43 @@ class DecoderTrainStep:
     def _gt(self):
         return self._gts[self._cur]
 
-    def _launch(self):
+    def _launch(self, phase=3):
         d = self._dims
-        if d.dropout_p > 0:   # fresh mask every step (Philox counter advances)
+        if d.dropout_p > 0 and phase != 2:   # fresh mask every step (Philox counter advances)
             d.offset += 1 << 32
         mask = self.llm._drop_mask_override
         if self.is_attn:
             F_.attn_train_fused(d, self._params, self._feat, self._gt, self._grads, self._ws, dfeat=self.dfeat,
                                 loss_out=self._loss, alphas_out=self._alphas, drop_mask=mask,
-                                ce_denominator=self.ce_denominator)
+                                ce_denominator=self.ce_denominator, phase=phase)
+        elif phase == 2:
+            return                               # plain LSTM: one call does the whole step (phase 1)
         else:
             P = self.llm._struct(self._params)
             G = self.llm._struct(self._grads)
             F_.lstm_train_fused(d, P, self._feat, self._gt, G, self._ws, dfeat=self.dfeat, loss_out=self._loss,
                                 drop_mask=mask, ce_denominator=self.ce_denominator)
 
-    def run_resident(self):
-        """One step on the inputs already staged in the static device buffers (bench: inputs resident in HBM)."""
+    def run_resident(self, phase=3):
+        """One step on the inputs already staged in the static device buffers (bench: inputs resident in HBM).
+        phase=1 then phase=2 run the same step in two launches (see GradAllReducer.step_overlapped)."""
         if self.use_cuda_graph and self._dims.dropout_p == 0:
-            if self._graphs[self._cur] is None:
+            key = (self._cur, phase)
+            if key not in self._graphs:
                 s = torch.cuda.Stream()
                 s.wait_stream(torch.cuda.current_stream())
                 with torch.cuda.stream(s):
-                    self._launch()           # warm-up outside capture (cudaFuncSetAttribute etc.)
+                    self._launch(phase)      # warm-up outside capture (cudaFuncSetAttribute, scratch allocation)
                 torch.cuda.current_stream().wait_stream(s)
                 g = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(g):
-                    self._launch()
-                self._graphs[self._cur] = g
-            self._graphs[self._cur].replay()
+                    self._launch(phase)
+                self._graphs[key] = g
+                if phase == 2:               # the warm-up consumed phase 1's saved state (gates -> dgates in place)
+                    self._launch(1)
+            self._graphs[key].replay()
         else:
-            self._launch()
+            self._launch(phase)
         return self._loss
 
     def stage(self, features, gt_labels):

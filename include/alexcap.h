@@ -116,6 +116,17 @@ ALEXCAP_API int alexcap_attn_train_fused(const alexcap_dims* dims, const alexcap
                              const float* ce_denominator,
                              void* workspace, size_t workspace_bytes, void* stream);
 
+/* The same step in two calls, so that a data-parallel caller can start the all-reduce of the vocabulary-projection
+ * gradients (the largest tensors, final after phase 1) while phase 2 runs (the reference is
+ * single-GPU and has no counterpart).  phase 1: forward + loss + vocab backward; phase 2: reverse-time chain and all
+ * other weight gradients (same arguments and workspace as phase 1); phase 3: both (== alexcap_attn_train_fused). */
+ALEXCAP_API int alexcap_attn_train_phase(const alexcap_dims* dims, const alexcap_attn_params* params,
+                             const float* feat, const int32_t* gt,
+                             const alexcap_attn_params* grads, float* dfeat,
+                             float* loss_out, float* alphas_out, const float* drop_mask,
+                             const float* ce_denominator,
+                             void* workspace, size_t workspace_bytes, int32_t phase, void* stream);
+
 /* Decoder.forward, train branch (AttentionLanguageModule.py:62-84): materialises preds [B,S,Vp] and
  * alphas [B,S,L] exactly like the reference, for callers that build their own loss on top. */
 ALEXCAP_API int alexcap_attn_forward(const alexcap_dims* dims, const alexcap_attn_params* params,
