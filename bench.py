@@ -32,6 +32,9 @@ CONFIGS = {
     'cfg2': dict(model='LSTMwAttentionModel', B=128, L=196, D=512, H=512, E=512, V=10000, T=16, dtype='f32'),
     'cfg1': dict(model='LSTMModel', B=16, L=1, D=512, H=512, E=512, V=10000, T=16, dtype='f32'),
     'cfg3_f32': dict(model='LSTMwAttentionModel', B=512, L=49, D=2048, H=1024, E=1024, V=10000, T=16, dtype='f32'),
+    # BASELINE.json configs[2] / configs[4]: bf16 tensor-core GEMMs with fp32 master weights / accumulation (E = 1024 assumed)
+    'cfg3': dict(model='LSTMwAttentionModel', B=512, L=49, D=2048, H=1024, E=1024, V=10000, T=16, dtype='bf16'),
+    'cfg5': dict(model='LSTMwAttentionModel', B=256, L=49, D=2048, H=1024, E=1024, V=32000, T=32, dtype='bf16'),
 }
 METRIC = 'captions/sec (attn-LSTM fwd+bwd, T=16)'
 
@@ -110,6 +113,7 @@ def make_model(c, dev):
     if c['model'] == 'LSTMwAttentionModel':
         m = Decoder(c['V'], c['E'], c['D'], c['H'], c['T'], {}, 0.0, dev)
         m.dropout.p = 0.0    # parity setting; see DESIGN.md (dropout path measured separately)
+        m.compute_dtype = 'bf16' if c['dtype'] == 'bf16' else 'f32'
     else:
         m = LanguageModel(c['V'], c['E'], c['D'], c['H'], c['T'], 1, {}, 0.0, dev)
     return m.to(dev)
@@ -238,7 +242,7 @@ def run_reference(args, c, rank):
 
 def workload_config(c, n):
     return dict(workload=f"{c['model']} decoder train step fwd+bwd (BASELINE.json configs[1]): B={c['B']}/GPU, "
-                         f"L={c['L']}, D={c['D']}, H={c['H']}, E={c['E']}, V={c['V']}, T={c['T']}, fp32, full-length captions, "
+                         f"L={c['L']}, D={c['D']}, H={c['H']}, E={c['E']}, V={c['V']}, T={c['T']}, {c['dtype']}, full-length captions, "
                          f"dropout p=0",
                 global_batch=c['B'] * n, parallelism=f'dp{n}',
                 l2='no explicit flush: per-step working set (Ws+feat+logits+saved state ~ 400 MB) exceeds the 126 MB L2')
@@ -343,7 +347,7 @@ def main():
         total = c['B'] * world
         line = dict(metric=METRIC, value=round(total / (ms * 1e-3), 1), unit='captions/s', n_gpus=world, steps=args.steps,
                     warmup=args.warmup, ms_per_step=round(ms, 4), higher_is_better=True, scaling='weak', vs_baseline=None,
-                    dtype='f32', data='synthetic', config=workload_config(c, world), loss=round(loss_val, 5),
+                    dtype=c['dtype'], data='synthetic', config=workload_config(c, world), loss=round(loss_val, 5),
                     cuda_graph=not args.no_graph,
                     e2e=dict(value=round(total / (ms_e2e * 1e-3), 1), unit='captions/s',
                              h2d_bytes_per_step=int(feat_h.numel() * 4 + gt_h.numel() * 4), d2h_bytes_per_step=4,
@@ -352,7 +356,8 @@ def main():
                     clocks=clk.summary())
         w = algorithmic_work(c)
         line['gemm_group'] = dict(algorithmic_gflop_per_step=round(w['gemm_flops_step'] / 1e9, 2),
-                                  engine='tcgen05 3xTF32 (fp32 in/out, 1e-4 parity)')
+                                  engine='tcgen05 3xTF32 (fp32 in/out, 1e-4 parity)' if c['dtype'] == 'f32' else
+                                  'tcgen05 bf16 operands, fp32 accumulate (2e-2 parity)')
         if c['model'] == 'LSTMwAttentionModel':
             line['roofline'] = dominant_kernel_roofline(c, dev, pk)
         if world == 1 and not args.no_cpu_baseline:

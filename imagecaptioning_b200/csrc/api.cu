@@ -241,7 +241,7 @@ const char* alexcap_last_error(void) { return err_buf(); }
 unsigned long long alexcap_launch_count(void) { return launch_counter(); }
 
 int alexcap_set_gemm_engine(int engine) {
-  if (engine != 0 && engine != 1) return fail(ALEXCAP_E_BADARG, "engine must be 0 (fp32 CUDA cores) or 1 (tcgen05 3xTF32)");
+  if (engine < 0 || engine > 2) return fail(ALEXCAP_E_BADARG, "engine must be 0 (fp32 CUDA cores), 1 (tcgen05 3xTF32) or 2 (tcgen05 bf16)");
   gemm_engine() = engine;
   return 0;
 }
@@ -268,6 +268,7 @@ static int attn_train_phases(const alexcap_dims* d, const alexcap_attn_params* P
                              const float* drop_mask, const float* ce_denominator, void* workspace,
                              size_t workspace_bytes, int phase, void* stream) {
   if (int rc = check_dims_common(d)) return rc;
+  DtypeScope dtype_scope(d);
   AttnWs w = attn_layout(d, nullptr, true);
   if (int rc = check_attn_args(d, P, feat, workspace, workspace_bytes, w.bytes)) return rc;
   if (!gt || !G || !loss_out) return fail(ALEXCAP_E_BADARG, "NULL gt / grads / loss_out");
@@ -320,6 +321,7 @@ int alexcap_attn_forward(const alexcap_dims* d, const alexcap_attn_params* P, co
                          float* preds, float* alphas, const float* drop_mask, void* workspace, size_t workspace_bytes,
                          void* stream) {
   if (int rc = check_dims_common(d)) return rc;
+  DtypeScope dtype_scope(d);
   AttnWs w = attn_layout(d, nullptr, false);
   if (int rc = check_attn_args(d, P, feat, workspace, workspace_bytes, w.bytes)) return rc;
   if (!gt || !preds) return fail(ALEXCAP_E_BADARG, "NULL gt / preds");
@@ -342,6 +344,7 @@ int alexcap_attn_backward(const alexcap_dims* d, const alexcap_attn_params* P, c
                           const float* dalphas, const alexcap_attn_params* G, float* dfeat, void* workspace,
                           size_t workspace_bytes, void* stream) {
   if (int rc = check_dims_common(d)) return rc;
+  DtypeScope dtype_scope(d);
   AttnWs w = attn_layout(d, nullptr, false);
   if (int rc = check_attn_args(d, P, feat, workspace, workspace_bytes, w.bytes)) return rc;
   if (!G) return fail(ALEXCAP_E_BADARG, "NULL grads");
@@ -397,9 +400,11 @@ int alexcap_gemm_f32(int32_t transa, int32_t transb, int32_t M, int32_t N, int32
   } else {
     if (!gemm_tc_supported(M, N, K, A, lda, B, ldb, C))
       return fail(ALEXCAP_E_UNSUPPORTED, "alexcap_gemm_f32: tensor-core engine needs 16-byte aligned operands with ld % 4 == 0");
-    // engine 1 = heuristic split-K; engine >= 2 forces split-K = engine (tests)
+    // engine 1 = 3xTF32, heuristic split-K; 2..99 = 3xTF32 with split-K forced to `engine` (tests);
+    // 100 = bf16 operands / fp32 accumulate, heuristic split-K; 100 + s = bf16 with split-K forced to s
+    const int mode = engine >= 100 ? 1 : 0, force = engine >= 100 ? engine - 100 : (engine >= 2 ? engine : 0);
     API_CK(gemm_tc_f32(st, transa != 0, transb != 0, M, N, K, alpha, A, lda, B, ldb, C, ldc, bias, bias2, accumulate != 0, act,
-                       engine >= 2 ? engine : 0));
+                       force, mode));
   }
   return 0;
 }

@@ -176,6 +176,7 @@ int alexcap_lstm_train_fused(const alexcap_dims* d, const alexcap_lstm_params* P
                              const alexcap_lstm_params* G, float* dfeat, float* loss_out, const float* drop_mask,
                              const float* ce_denominator, void* workspace, size_t workspace_bytes, void* stream) {
   if (int rc = check_lstm_dims(d)) return rc;
+  DtypeScope dtype_scope(d);
   LstmWs w = lstm_layout(d, nullptr, true);
   if (int rc = check_lstm_args(d, P, feat, workspace, workspace_bytes, w.bytes)) return rc;
   if (!gt || !G || !loss_out) return fail(ALEXCAP_E_BADARG, "NULL gt / grads / loss_out");
@@ -199,6 +200,7 @@ int alexcap_lstm_train_fused(const alexcap_dims* d, const alexcap_lstm_params* P
 int alexcap_lstm_forward(const alexcap_dims* d, const alexcap_lstm_params* P, const float* feat, const int32_t* gt,
                          float* preds, const float* drop_mask, void* workspace, size_t workspace_bytes, void* stream) {
   if (int rc = check_lstm_dims(d)) return rc;
+  DtypeScope dtype_scope(d);
   LstmWs w = lstm_layout(d, nullptr, false);
   if (int rc = check_lstm_args(d, P, feat, workspace, workspace_bytes, w.bytes)) return rc;
   if (!gt || !preds) return fail(ALEXCAP_E_BADARG, "NULL gt / preds");
@@ -216,6 +218,7 @@ int alexcap_lstm_forward(const alexcap_dims* d, const alexcap_lstm_params* P, co
 int alexcap_lstm_backward(const alexcap_dims* d, const alexcap_lstm_params* P, const float* feat, const float* dpreds,
                           const alexcap_lstm_params* G, float* dfeat, void* workspace, size_t workspace_bytes, void* stream) {
   if (int rc = check_lstm_dims(d)) return rc;
+  DtypeScope dtype_scope(d);
   LstmWs w = lstm_layout(d, nullptr, false);
   if (int rc = check_lstm_args(d, P, feat, workspace, workspace_bytes, w.bytes)) return rc;
   if (!G || !dpreds) return fail(ALEXCAP_E_BADARG, "NULL grads / dpreds");
@@ -270,6 +273,7 @@ size_t alexcap_lstm_decode_workspace_bytes(const alexcap_dims* d) {
 int alexcap_lstm_decode_greedy(const alexcap_dims* d, const alexcap_lstm_params* P, const float* feat, int64_t* ids,
                                void* workspace, size_t workspace_bytes, void* stream) {
   if (int rc = check_lstm_dims(d)) return rc;
+  DtypeScope dtype_scope(d);
   if (int rc = check_lstm_args(d, P, feat, workspace, workspace_bytes, lstm_dec_layout(d, nullptr).bytes)) return rc;
   if (!ids) return fail(ALEXCAP_E_BADARG, "NULL ids");
   cudaStream_t st = static_cast<cudaStream_t>(stream);

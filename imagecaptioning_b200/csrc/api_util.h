@@ -44,9 +44,20 @@ inline int check_dims_common(const alexcap_dims* d) {
     return fail(ALEXCAP_E_BADARG, "non-positive dimension in alexcap_dims");
   if ((d->D & 3) || (d->H & 3) || (d->E & 3)) return fail(ALEXCAP_E_BADARG, "D, H and E must be multiples of 4");
   if (d->H > 1024) return fail(ALEXCAP_E_UNSUPPORTED, "H > 1024 not supported by the attention kernels");
-  if (d->dtype != ALEXCAP_F32) return fail(ALEXCAP_E_UNSUPPORTED, "only dtype ALEXCAP_F32 is implemented in this build");
+  if (d->dtype != ALEXCAP_F32 && d->dtype != ALEXCAP_BF16) return fail(ALEXCAP_E_UNSUPPORTED, "dtype must be ALEXCAP_F32 or ALEXCAP_BF16");
   if (d->dropout_p < 0.f || d->dropout_p >= 1.f) return fail(ALEXCAP_E_BADARG, "dropout_p must be in [0,1)");
   return 0;
 }
+
+// dims.dtype == ALEXCAP_BF16: every GEMM of the call runs on the tcgen05 bf16 engine (operands rounded to bf16 in shared
+// memory, fp32 accumulation in TMEM); parameters, activations, gradients and the attention/softmax/CE arithmetic stay
+// fp32 ("bf16 with fp32 master/accumulate" of BASELINE.json configs 3 and 5).  Scoped: the process-wide engine is restored.
+struct DtypeScope {
+  int saved;
+  explicit DtypeScope(const alexcap_dims* d) : saved(gemm_engine()) {
+    if (d && d->dtype == ALEXCAP_BF16) gemm_engine() = 2;
+  }
+  ~DtypeScope() { gemm_engine() = saved; }
+};
 
 }  // namespace alexcap

@@ -218,8 +218,10 @@ int& gemm_engine() {
 cudaError_t gemm_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, float alpha,
                      const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
                      const float* bias, const float* bias2, bool accumulate, int act) {
-  if (gemm_engine() == 1 && gemm_tc_supported(M, N, K, A, lda, B, ldb, C))
-    return gemm_tc_f32(st, ta, tb, M, N, K, alpha, A, lda, B, ldb, C, ldc, bias, bias2, accumulate, act, 0);
+  // engine 1: tcgen05 3xTF32 (fp32-grade); engine 2: tcgen05 bf16 operands / fp32 accumulate (mixed-precision configs)
+  if (gemm_engine() >= 1 && gemm_tc_supported(M, N, K, A, lda, B, ldb, C))
+    return gemm_tc_f32(st, ta, tb, M, N, K, alpha, A, lda, B, ldb, C, ldc, bias, bias2, accumulate, act, 0,
+                       gemm_engine() == 2 ? 1 : 0);
   return gemm_simt_f32(st, ta, tb, M, N, K, alpha, A, lda, B, ldb, C, ldc, bias, bias2, accumulate, act);
 }
 

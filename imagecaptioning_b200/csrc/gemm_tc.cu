@@ -94,6 +94,42 @@ __device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t a_desc, uint
       ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accum)
       : "memory");
 }
+__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accum) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accum)
+      : "memory");
+}
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {      // round to nearest even
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+// fp32 tile [ROWS][32 k] as TMA delivered it -> bf16 tile, k-chunk-major core matrices: (r, k) at (k/8)*ROWS*16 + r*16 + (k%8)*2.
+// K-major source: 128-byte rows, 16-byte chunk c of row r stored at chunk c ^ (r & 7) (SWIZZLE_128B).
+// MN-major source: boxes of {32 mn, 32 k}, un-swizzled: (k, mn) at (mn/32)*4096 + k*128 + (mn%32)*4.
+template <int ROWS, bool MN>
+__device__ __forceinline__ void convert_bf16(const uint8_t* src, uint8_t* dst, int t) {
+  for (int idx = t; idx < ROWS * 4; idx += CONV_THREADS) {
+    const int r = idx % ROWS, pch = idx / ROWS;          // row, 8-wide k chunk
+    float v[8];
+    if (!MN) {
+      const uint8_t* row = src + r * 128;
+      const float4 x0 = *reinterpret_cast<const float4*>(row + (((2 * pch) ^ (r & 7)) << 4));
+      const float4 x1 = *reinterpret_cast<const float4*>(row + (((2 * pch + 1) ^ (r & 7)) << 4));
+      v[0] = x0.x; v[1] = x0.y; v[2] = x0.z; v[3] = x0.w; v[4] = x1.x; v[5] = x1.y; v[6] = x1.z; v[7] = x1.w;
+    } else {
+      const float* col = reinterpret_cast<const float*>(src + (r >> 5) * 4096 + (r & 31) * 4) + pch * 8 * 32;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = col[j * 32];
+    }
+    uint4 o;
+    o.x = pack_bf16(v[0], v[1]); o.y = pack_bf16(v[2], v[3]); o.z = pack_bf16(v[4], v[5]); o.w = pack_bf16(v[6], v[7]);
+    *reinterpret_cast<uint4*>(dst + pch * (ROWS * 16) + r * 16) = o;
+  }
+}
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
@@ -118,7 +154,10 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes
 }
 
 // ------------------------------------------------------------------------------------------------ kernel
-template <int BN, bool A_MN, bool B_MN, int STAGES>
+// MODE 0: 3xTF32 (fp32-grade accuracy).  MODE 1: bf16 operands, fp32 accumulate (the mixed-precision configs): the
+// converter warps round the fp32 tile to bf16 and re-lay it out K-major / no-swizzle (core matrices of 8 rows x 16 bytes)
+// in the slot the 3xTF32 path uses for the `lo` tile; one kind::f16 MMA per 16 k replaces three kind::tf32 per 8 k.
+template <int BN, bool A_MN, bool B_MN, int STAGES, int MODE>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const Params p) {
   constexpr uint32_t A_BYTES = BM * BK * 4, B_BYTES = BN * BK * 4;
@@ -200,6 +239,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       if (lane == 0) {
         const uint32_t a_hi = smem_u32(smem + s * STAGE_BYTES), a_lo = a_hi + A_BYTES;
         const uint32_t b_hi = a_hi + 2 * A_BYTES, b_lo = b_hi + B_BYTES;
+        if (MODE == 1) {
+          // bf16 tiles: k-chunk-major core matrices.  LBO = stride between 16-byte k chunks = rows*16, SBO = 128 (next 8 rows)
+          const uint32_t idesc16 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            const uint64_t da = make_desc(a_lo + k * 2 * (BM * 16), BM * 16, 128, 0);
+            const uint64_t db = make_desc(b_lo + k * 2 * (BN * 16), BN * 16, 128, 0);
+            umma_bf16(tmem_base, da, db, idesc16, (i | k) != 0);
+          }
+        } else {
 #pragma unroll
         for (int k = 0; k < BK / UMMA_K; ++k) {
           // K-major: +32 bytes inside the swizzled 128-byte row; MN-major: next group of 8 k-rows (+1024 bytes)
@@ -214,6 +263,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           umma_tf32(tmem_base, dah, dbl, idesc, 1);
           umma_tf32(tmem_base, dah, dbh, idesc, 1);
         }
+        }
         umma_commit(&empty_bar[s]);                       // smem stage reusable once these MMAs retire
         if (i == nkb - 1) umma_commit(tmem_full_bar);     // accumulator complete
       }
@@ -227,6 +277,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const uint32_t ph = (i / STAGES) & 1;
       mbar_wait(&full_bar[s], ph);
       uint8_t* st = smem + s * STAGE_BYTES;
+      if (MODE == 1) {
+        convert_bf16<BM, A_MN>(st, st + A_BYTES, t);
+        convert_bf16<BN, B_MN>(st + 2 * A_BYTES, st + 2 * A_BYTES + B_BYTES, t);
+      } else {
       // elementwise, so it is oblivious to the swizzle: same byte offset in the hi and lo tiles
 #pragma unroll
       for (int c = t; c < (int)(A_BYTES / 16); c += CONV_THREADS) {
@@ -244,6 +298,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         split_tf32(x.x, h.x, l.x); split_tf32(x.y, h.y, l.y); split_tf32(x.z, h.z, l.z); split_tf32(x.w, h.w, l.w);
         *reinterpret_cast<uint4*>(sb + c * 16) = h;
         *reinterpret_cast<uint4*>(sb + B_BYTES + c * 16) = l;
+      }
       }
       fence_proxy_async();            // generic-proxy writes -> visible to the tensor core (async proxy)
       mbar_arrive(&conv_bar[s]);
@@ -329,7 +384,7 @@ static EncodeTiledFn get_encode() {
 
 // 2-D fp32 tensor map: inner (contiguous) extent `inner`, outer extent `outer`, row pitch ld floats, box {32, box_outer}.
 static bool make_map(CUtensorMap* map, const float* base, int64_t inner, int64_t outer, int64_t ld, int box_outer,
-                     bool mn_major) {
+                     bool mn_major, bool plain = false) {
   EncodeTiledFn enc = get_encode();
   if (!enc) return false;
   cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
@@ -338,18 +393,18 @@ static bool make_map(CUtensorMap* map, const float* base, int64_t inner, int64_t
   cuuint32_t estr[2] = {1u, 1u};
   CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE,
-                   mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                   plain ? CU_TENSOR_MAP_SWIZZLE_NONE : mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS;
 }
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, int MODE>
 static cudaError_t launch(cudaStream_t st, const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, dim3 grid) {
   constexpr int STAGES = (BN == 128) ? 3 : 4;
   constexpr size_t SMEM = (size_t)STAGES * (2 * BM * BK * 4 + 2 * BN * BK * 4) + 1024 /*align*/ + 256 /*barriers*/;
   static bool configured = false;
-  auto kern = gemm_tc_kernel<BN, A_MN, B_MN, STAGES>;
+  auto kern = gemm_tc_kernel<BN, A_MN, B_MN, STAGES, MODE>;
   if (!configured) {
     ACK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
     configured = true;
@@ -367,7 +422,7 @@ bool gemm_tc_supported(int M, int N, int K, const float* A, int64_t lda, const f
 
 cudaError_t gemm_tc_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, float alpha,
                         const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
-                        const float* bias, const float* bias2, bool accumulate, int act, int force_splits) {
+                        const float* bias, const float* bias2, bool accumulate, int act, int force_splits, int mode) {
   using namespace tc;
   if (M <= 0 || N <= 0 || K <= 0) return cudaSuccess;
   if (!gemm_tc_supported(M, N, K, A, lda, B, ldb, C)) return cudaErrorNotSupported;
@@ -392,23 +447,28 @@ cudaError_t gemm_tc_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, 
   if (splits > 1 && !accumulate) ACK(cudaMemset2DAsync(C, ldc * sizeof(float), 0, (size_t)N * sizeof(float), M, st));
 
   CUtensorMap mapA, mapB;
-  bool ok = a_mn ? make_map(&mapA, A, M, K, lda, BK, true) : make_map(&mapA, A, K, M, lda, BM, false);
-  ok = ok && (b_mn ? make_map(&mapB, B, N, K, ldb, BK, true) : make_map(&mapB, B, K, N, ldb, BN, false));
+  const bool plain = (mode == 1);      // the bf16 converter transposes MN-major boxes itself: un-swizzled boxes
+  bool ok = a_mn ? make_map(&mapA, A, M, K, lda, BK, true, plain) : make_map(&mapA, A, K, M, lda, BM, false);
+  ok = ok && (b_mn ? make_map(&mapB, B, N, K, ldb, BK, true, plain) : make_map(&mapB, B, K, N, ldb, BN, false));
   if (!ok) return cudaErrorInvalidValue;
 
   Params p;
   p.C = C; p.bias = bias; p.bias2 = bias2; p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.alpha = alpha;
   p.accumulate = accumulate ? 1 : 0; p.act = act; p.kb_per_split = kb_per; p.num_kb = num_kb;
   dim3 grid(ceil_div(N, BN), ceil_div(M, BM), splits);
-#define TC_DISPATCH(BN_)                                                                 \
-  do {                                                                                   \
-    if (!a_mn && !b_mn) return launch<BN_, false, false>(st, mapA, mapB, p, grid);       \
-    if (!a_mn && b_mn) return launch<BN_, false, true>(st, mapA, mapB, p, grid);         \
-    if (a_mn && b_mn) return launch<BN_, true, true>(st, mapA, mapB, p, grid);           \
-    return launch<BN_, true, false>(st, mapA, mapB, p, grid);                            \
+#define TC_DISPATCH(BN_, MODE_)                                                                 \
+  do {                                                                                          \
+    if (!a_mn && !b_mn) return launch<BN_, false, false, MODE_>(st, mapA, mapB, p, grid);       \
+    if (!a_mn && b_mn) return launch<BN_, false, true, MODE_>(st, mapA, mapB, p, grid);         \
+    if (a_mn && b_mn) return launch<BN_, true, true, MODE_>(st, mapA, mapB, p, grid);           \
+    return launch<BN_, true, false, MODE_>(st, mapA, mapB, p, grid);                            \
   } while (0)
-  if (BN == 128) TC_DISPATCH(128);
-  TC_DISPATCH(64);
+  if (mode == 1) {
+    if (BN == 128) TC_DISPATCH(128, 1);
+    TC_DISPATCH(64, 1);
+  }
+  if (BN == 128) TC_DISPATCH(128, 0);
+  TC_DISPATCH(64, 0);
 #undef TC_DISPATCH
 }
 

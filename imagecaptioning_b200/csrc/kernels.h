@@ -18,7 +18,7 @@ cudaError_t gemm_simt_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K
 // tcgen05 / TMEM / TMA engine (gemm_tc.cu); force_splits > 0 overrides the split-K heuristic (tests)
 cudaError_t gemm_tc_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, float alpha,
                         const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
-                        const float* bias, const float* bias2, bool accumulate, int act, int force_splits);
+                        const float* bias, const float* bias2, bool accumulate, int act, int force_splits, int mode = 0);
 bool gemm_tc_supported(int M, int N, int K, const float* A, int64_t lda, const float* B, int64_t ldb, const float* C);
 int& gemm_engine();
 

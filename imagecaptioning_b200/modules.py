@@ -17,6 +17,7 @@ import torch
 import torch.nn as nn
 
 from . import functional as F_
+from . import _lib
 from ._lib import ATTN_STATE_NAMES, AlexcapError
 
 
@@ -29,6 +30,16 @@ def _f32c(t):
 
 
 # =============================================================================================== loss
+def _compute_dtype(mod):
+    """`mod.compute_dtype` ('f32' default, or 'bf16'): bf16 runs every GEMM of the training path on the tcgen05 bf16
+    engine (operands rounded to bf16, fp32 accumulation; parameters/activations/gradients stay fp32) -- the
+    mixed-precision mode of BASELINE.json configs 3 and 5.  The reference itself is fp32-only (train_LSTM.py:16)."""
+    cd = getattr(mod, 'compute_dtype', 'f32')
+    if cd not in ('f32', 'bf16'):
+        raise AlexcapError("compute_dtype must be 'f32' or 'bf16'")
+    return _lib.BF16 if cd == 'bf16' else _lib.F32
+
+
 class _CEFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx, inp, target):
@@ -182,7 +193,7 @@ class Decoder(nn.Module, _DecodeMixin):
         p = float(self.dropout.p) if (self.training and train_dropout) else 0.0
         seed = int(torch.randint(0, 2 ** 62, (1,)).item()) if p > 0 else 0
         return F_.make_dims(B, L, D, self.rnn_size, self.embedding_size, self.vocabulary_size + 3, S,
-                            need_dfeat=need_dfeat, dropout_p=p, seed=seed)
+                            dtype=_compute_dtype(self), need_dfeat=need_dfeat, dropout_p=p, seed=seed)
 
     def forward(self, img_features, captions):
         feat = img_features if img_features.dtype == torch.float32 and img_features.is_contiguous() \
@@ -309,7 +320,8 @@ class LanguageModel(nn.Module, _DecodeMixin):
         p = float(self.rnn.drop.p) if (self.training and train_dropout) else 0.0
         seed = int(torch.randint(0, 2 ** 62, (1,)).item()) if p > 0 else 0
         return F_.make_dims(B, L, D, self.rnn_size, self.embedding_size, self.vocab_size + 3, self.seq_length + 1,
-                            num_layers=self.num_layers, need_dfeat=need_dfeat, dropout_p=p, seed=seed, reg_weight=0.0)
+                            num_layers=self.num_layers, dtype=_compute_dtype(self), need_dfeat=need_dfeat, dropout_p=p,
+                            seed=seed, reg_weight=0.0)
 
     def forward(self, image_vectors, gt_sequence):
         feat = image_vectors if image_vectors.dtype == torch.float32 and image_vectors.is_contiguous() \

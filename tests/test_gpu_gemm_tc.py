@@ -76,3 +76,24 @@ def test_gemm_tc_accuracy_is_fp32_grade(F_):
     simt = F_.gemm(A.to(DEV), B.to(DEV), engine=0)
     e_tc, e_simt = rel_err(out, ref), rel_err(simt, ref)
     assert e_tc < 5e-6, (e_tc, e_simt)
+
+
+@pytest.mark.parametrize('ta,tb', [(False, True), (False, False), (True, False), (True, True)])
+@pytest.mark.parametrize('M,N,K', [(128, 128, 32), (128, 64, 64), (256, 256, 256), (37, 53, 29), (130, 200, 100),
+                                   (128, 2048, 1024), (2176, 515, 96)])
+def test_gemm_bf16_engine_layouts(F_, ta, tb, M, N, K):
+    """bf16-operand engine (dims.dtype = ALEXCAP_BF16 path): exactly the fp64 product of the bf16-ROUNDED operands up to
+    fp32 accumulation error, for every operand-major combination (this pins the in-kernel convert / re-layout)."""
+    g = torch.Generator().manual_seed(M * 1000 + N + K + 7)
+    pad_a = (-M) % 4 if ta else (-K) % 4
+    pad_b = (-K) % 4 if tb else (-N) % 4
+    A, B, _ = _mk(ta, tb, M, N, K, g, pad_a, pad_b)
+    Av = (A[:, :M] if ta else A[:, :K]).bfloat16().double()
+    Bv = (B[:, :K] if tb else B[:, :N]).bfloat16().double()
+    ref = (Av.T if ta else Av) @ (Bv.T if tb else Bv)
+    bias = torch.randn(N, generator=g)
+    out = F_.gemm(A.to(DEV), B.to(DEV), transa=ta, transb=tb, M=M, N=N, K=K, lda=A.shape[1], ldb=B.shape[1],
+                  bias=bias.to(DEV), engine=100)
+    assert rel_err(out, ref + bias.double()) < 2e-5, rel_err(out, ref + bias.double())
+    out = F_.gemm(A.to(DEV), B.to(DEV), transa=ta, transb=tb, M=M, N=N, K=K, lda=A.shape[1], ldb=B.shape[1], engine=103)
+    assert rel_err(out, ref) < 2e-5            # split-K forced to 3

@@ -217,3 +217,29 @@ def test_two_phase_step_equals_fused(graph):
         assert rel_err(b._loss, want_loss) < 1e-6
         assert rel_err(b._flat_grads, want) < 1e-5
         assert torch.equal(b.grad_buckets()[0], vocab)               # phase 2 does not touch bucket 0
+
+
+BF16_TOL = 2e-2     # BASELINE.json north_star: 2e-2 relative for the bf16 configs
+
+
+@pytest.mark.parametrize('shape', [dict(B=16, L=49, D=128, H=64, E=64, V=300, T=8), dict(B=8, L=20, D=64, H=128, E=32, V=1000, T=16)])
+def test_attn_train_bf16_vs_oracle_fp64(shape):
+    """compute_dtype='bf16' (dims.dtype = ALEXCAP_BF16: bf16 tensor-core GEMMs, fp32 master/accumulate) against the fp64
+    oracle: loss and every gradient within 2e-2 relative (configs 3 and 5 of BASELINE.json at test size)."""
+    from imagecaptioning_b200.model import DecoderTrainStep
+    cfg = {k: shape[k] for k in ('V', 'E', 'D', 'H', 'T')}
+    p = random_attn_params(cfg, seed=9, dtype=torch.float32)
+    dec = build_decoder(cfg, p)
+    dec.compute_dtype = 'bf16'
+    feat, gt = synth_inputs(shape['B'], shape['L'], cfg['D'], cfg['V'], cfg['T'], seed=4)
+    step = DecoderTrainStep(dec)
+    loss = step.forward_train(feat.to(DEV), gt.to(DEV))
+    ref = R.attn_train_step({k: v.double() for k, v in p.items()}, feat.double(), gt, cfg['V'])
+    assert abs(float(loss) - float(ref['loss'])) < BF16_TOL * abs(float(ref['loss']))
+    _check_grads({k: q.grad for k, q in dec.named_parameters()}, ref['grads'], tol=BF16_TOL)
+    # and it is really the bf16 engine: not bit-identical to the fp32 path
+    dec32 = build_decoder(cfg, p)
+    l32 = DecoderTrainStep(dec32).forward_train(feat.to(DEV), gt.to(DEV))
+    assert float(l32) != float(loss)
+    from imagecaptioning_b200 import functional as F_
+    assert F_.get_gemm_engine() in (0, 1)          # the scoped override was restored
