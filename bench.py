@@ -30,11 +30,11 @@ sys.path.insert(0, ROOT)
 CONFIGS = {
     # BASELINE.json configs[1]: the configuration the metric is quoted on at N=1
     'cfg2': dict(model='LSTMwAttentionModel', B=128, L=196, D=512, H=512, E=512, V=10000, T=16, dtype='f32'),
-    'cfg1': dict(model='LSTMModel', B=16, L=1, D=512, H=512, E=512, V=10000, T=16, dtype='f32'),
-    'cfg3_f32': dict(model='LSTMwAttentionModel', B=512, L=49, D=2048, H=1024, E=1024, V=10000, T=16, dtype='f32'),
+    'cfg1': dict(ref='BASELINE.json configs[0]', model='LSTMModel', B=16, L=1, D=512, H=512, E=512, V=10000, T=16, dtype='f32'),
+    'cfg3_f32': dict(ref='BASELINE.json configs[2] shape in fp32', model='LSTMwAttentionModel', B=512, L=49, D=2048, H=1024, E=1024, V=10000, T=16, dtype='f32'),
     # BASELINE.json configs[2] / configs[4]: bf16 tensor-core GEMMs with fp32 master weights / accumulation (E = 1024 assumed)
-    'cfg3': dict(model='LSTMwAttentionModel', B=512, L=49, D=2048, H=1024, E=1024, V=10000, T=16, dtype='bf16'),
-    'cfg5': dict(model='LSTMwAttentionModel', B=256, L=49, D=2048, H=1024, E=1024, V=32000, T=32, dtype='bf16'),
+    'cfg3': dict(ref='BASELINE.json configs[2]', model='LSTMwAttentionModel', B=512, L=49, D=2048, H=1024, E=1024, V=10000, T=16, dtype='bf16'),
+    'cfg5': dict(ref='BASELINE.json configs[4]', model='LSTMwAttentionModel', B=256, L=49, D=2048, H=1024, E=1024, V=32000, T=32, dtype='bf16'),
 }
 METRIC = 'captions/sec (attn-LSTM fwd+bwd, T=16)'
 
@@ -241,7 +241,7 @@ def run_reference(args, c, rank):
 
 
 def workload_config(c, n):
-    return dict(workload=f"{c['model']} decoder train step fwd+bwd (BASELINE.json configs[1]): B={c['B']}/GPU, "
+    return dict(workload=f"{c['model']} decoder train step fwd+bwd ({c.get('ref', 'BASELINE.json configs[1]')}): B={c['B']}/GPU, "
                          f"L={c['L']}, D={c['D']}, H={c['H']}, E={c['E']}, V={c['V']}, T={c['T']}, {c['dtype']}, full-length captions, "
                          f"dropout p=0",
                 global_batch=c['B'] * n, parallelism=f'dp{n}',

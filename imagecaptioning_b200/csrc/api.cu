@@ -184,7 +184,6 @@ int attn_bwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
   // attention.W : dWs in one pass, then one K = B*L GEMM
   API_CK(attn_dws(st, B, L, H, S, w.Ws, w.QB, HD, P->att_v_w, w.DE, w.dWs));
   API_CK(gemm_f32(st, true, false, H, D, B * L, 1.f, w.dWs, H, feat, D, G->att_W_w, D, nullptr, nullptr, false, ACT_NONE));
-  API_CK(col_sum(st, w.dWs, B * L, H, H, G->att_W_b, false, w.cs_scratch));
   if (need_dfeat)
     API_CK(gemm_f32(st, false, false, B * L, D, H, 1.f, w.dWs, H, P->att_W_w, D, dfeat, D, nullptr, nullptr, true, ACT_NONE));
   // lstm weights: dW = dgates_all^T [EmbIn | gctx | h_prev], K = S*B
@@ -201,6 +200,9 @@ int attn_bwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
   API_CK(gemm_f32(st, true, false, H, H, SB, 1.f, w.DGQ + 4 * H, W5, w.XH + D, DH, G->att_U_w, H, nullptr, nullptr, false, ACT_NONE));
   API_CK(gemm_f32(st, true, false, D, H, SB, 1.f, w.DGQ + 5 * H, W5, w.XH + D, DH, G->f_beta_w, H, nullptr, nullptr, false, ACT_NONE));
   API_CK(col_sum(st, w.DGQ + 4 * H, SB, H, W5, G->att_U_b, false, w.cs_scratch));
+  // d b_W = sum_{b,l} dWs = sum_{b,t,l} dz = sum_{b,t} dq = d b_U: the same number; taken from the dq path, whose sums are
+  // formed without the cancellation that a column sum of dWs would re-introduce (see attention_stream.cu, pass D)
+  API_CK(cudaMemcpyAsync(G->att_W_b, G->att_U_b, sizeof(float) * H, cudaMemcpyDeviceToDevice, st));
   API_CK(col_sum(st, w.DGQ + 5 * H, SB, D, W5, G->f_beta_b, false, w.cs_scratch));
   // attention.v
   API_CK(col_sum(st, w.dwv_part, B, H, H, G->att_v_w, false, w.cs_scratch));
@@ -241,7 +243,7 @@ const char* alexcap_last_error(void) { return err_buf(); }
 unsigned long long alexcap_launch_count(void) { return launch_counter(); }
 
 int alexcap_set_gemm_engine(int engine) {
-  if (engine < 0 || engine > 2) return fail(ALEXCAP_E_BADARG, "engine must be 0 (fp32 CUDA cores), 1 (tcgen05 3xTF32) or 2 (tcgen05 bf16)");
+  if (engine < 0 || engine > 3) return fail(ALEXCAP_E_BADARG, "engine must be 0 (fp32 CUDA cores), 1 (tcgen05 3xTF32) or 2 (tcgen05 bf16)");
   gemm_engine() = engine;
   return 0;
 }
@@ -402,7 +404,9 @@ int alexcap_gemm_f32(int32_t transa, int32_t transb, int32_t M, int32_t N, int32
       return fail(ALEXCAP_E_UNSUPPORTED, "alexcap_gemm_f32: tensor-core engine needs 16-byte aligned operands with ld % 4 == 0");
     // engine 1 = 3xTF32, heuristic split-K; 2..99 = 3xTF32 with split-K forced to `engine` (tests);
     // 100 = bf16 operands / fp32 accumulate, heuristic split-K; 100 + s = bf16 with split-K forced to s
-    const int mode = engine >= 100 ? 1 : 0, force = engine >= 100 ? engine - 100 : (engine >= 2 ? engine : 0);
+    // 200 (+s) = bf16x3 (hi/lo bf16 pairs, three kind::f16 MMAs)
+    const int mode = engine >= 200 ? 2 : engine >= 100 ? 1 : 0;
+    const int force = engine >= 200 ? engine - 200 : engine >= 100 ? engine - 100 : (engine >= 2 ? engine : 0);
     API_CK(gemm_tc_f32(st, transa != 0, transb != 0, M, N, K, alpha, A, lda, B, ldb, C, ldc, bias, bias2, accumulate != 0, act,
                        force, mode));
   }

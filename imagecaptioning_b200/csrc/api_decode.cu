@@ -126,6 +126,7 @@ size_t alexcap_attn_decode_workspace_bytes(const alexcap_dims* d, int32_t beam) 
 int alexcap_attn_decode_greedy(const alexcap_dims* d, const alexcap_attn_params* P, const float* feat, int64_t* ids,
                                float* alphas, void* workspace, size_t workspace_bytes, void* stream) {
   if (int rc = check_dec(d, P, feat, workspace, workspace_bytes, 1)) return rc;
+  ExactScope exact_scope;
   if (!ids) return fail(ALEXCAP_E_BADARG, "NULL ids");
   DecWs w = dec_layout(d, 1, workspace);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -147,6 +148,7 @@ int alexcap_attn_decode_beam(const alexcap_dims* d, const alexcap_attn_params* P
                              int64_t* ids, int32_t* lens, float* scores, float* alphas, void* workspace,
                              size_t workspace_bytes, void* stream) {
   if (int rc = check_dec(d, P, feat, workspace, workspace_bytes, beam)) return rc;
+  ExactScope exact_scope;
   if (!ids || !lens || !scores) return fail(ALEXCAP_E_BADARG, "NULL ids / lens / scores");
   const int K = beam;
   DecWs w = dec_layout(d, K, workspace);

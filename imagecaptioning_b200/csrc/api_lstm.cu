@@ -273,7 +273,7 @@ size_t alexcap_lstm_decode_workspace_bytes(const alexcap_dims* d) {
 int alexcap_lstm_decode_greedy(const alexcap_dims* d, const alexcap_lstm_params* P, const float* feat, int64_t* ids,
                                void* workspace, size_t workspace_bytes, void* stream) {
   if (int rc = check_lstm_dims(d)) return rc;
-  DtypeScope dtype_scope(d);
+  ExactScope exact_scope;
   if (int rc = check_lstm_args(d, P, feat, workspace, workspace_bytes, lstm_dec_layout(d, nullptr).bytes)) return rc;
   if (!ids) return fail(ALEXCAP_E_BADARG, "NULL ids");
   cudaStream_t st = static_cast<cudaStream_t>(stream);

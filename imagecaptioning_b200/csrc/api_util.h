@@ -60,4 +60,11 @@ struct DtypeScope {
   ~DtypeScope() { gemm_engine() = saved; }
 };
 
+// Decoding must reproduce the reference's token ids exactly (fp32): never run it on a reduced-precision engine.
+struct ExactScope {
+  int saved;
+  ExactScope() : saved(gemm_engine()) { if (saved >= 2) gemm_engine() = 1; }
+  ~ExactScope() { gemm_engine() = saved; }
+};
+
 }  // namespace alexcap

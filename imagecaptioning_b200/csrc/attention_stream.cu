@@ -166,7 +166,7 @@ struct Ring {
 };
 
 // Small per-image vectors that open every segment (the "header piece"): up to 4 rows copied back to back.
-struct Header { const float* p[4]; int64_t ld[4]; int n[4]; int count; };
+struct Header { const float* p[5]; int64_t ld[5]; int n[5]; int count; };
 
 // Producer: for every image segment of this CTA's row range stream [header] [X0 rows] [X1 rows] (R-row pieces).
 __device__ __forceinline__ void produce(const Ring& ring, int64_t row0, int64_t row1, int L, int R, int rpi,
@@ -551,8 +551,10 @@ __global__ void __launch_bounds__(SA_THREADS, 1) attn_bwd_stream_kernel(const SA
   ring.empty = ring.full + SA_MAX_NST;
   float4* red = reinterpret_cast<float4*>(ring.empty + SA_MAX_NST);   // [4][SA_CTHREADS]
   float* dctx_s = reinterpret_cast<float*>(red + 4 * SA_CTHREADS);    // [D]
-  float* q_s = dctx_s + D;                                            // [H]
-  float* al_all = q_s + H;                                            // [rp_pad] alpha of this CTA's whole row range
+  float* cx_s = dctx_s + D;                                           // [D] ctx[b,:]
+  float* q_s = cx_s + D;                                              // [H]
+  float* w0_s = q_s + H;                                              // [H] Ws[b,0,:]
+  float* al_all = w0_s + H;                                            // [rp_pad] alpha of this CTA's whole row range
   float* da_s = al_all + a.rp_pad;                                    // [seg_pad]
   float* scratch = da_s + a.seg_pad;                                  // [40]
   int* segb = reinterpret_cast<int*>(scratch + 40);                   // [maxseg]
@@ -578,7 +580,8 @@ __global__ void __launch_bounds__(SA_THREADS, 1) attn_bwd_stream_kernel(const SA
       hd.p[1] = a.dgctx; hd.ld[1] = a.dgctx_ld; hd.n[1] = D;
       hd.p[2] = a.beta; hd.ld[2] = D; hd.n[2] = D;
       hd.p[3] = a.ctx; hd.ld[3] = D; hd.n[3] = D;
-      hd.count = 4;
+      hd.p[4] = a.Ws; hd.ld[4] = (int64_t)L * H; hd.n[4] = H;          // Ws[b,0,:]: the reference row of pass D
+      hd.count = 5;
       produce(ring, row0, row1, L, R, 1, hd, a.feat, D, a.Ws, H);     // feat pieces, then Ws pieces
     }
     return;
@@ -614,12 +617,16 @@ __global__ void __launch_bounds__(SA_THREADS, 1) attn_bwd_stream_kernel(const SA
     {
       const float4* hq = reinterpret_cast<const float4*>(ring.stage(k));
       const float4* hdg = hq + H4; const float4* hbe = hdg + D4; const float4* hcx = hbe + D4;
-      for (int ff = tid; ff < H4; ff += SA_CTHREADS) reinterpret_cast<float4*>(q_s)[ff] = hq[ff];
+      for (int ff = tid; ff < H4; ff += SA_CTHREADS) {
+        reinterpret_cast<float4*>(q_s)[ff] = hq[ff];
+        reinterpret_cast<float4*>(w0_s)[ff] = (hcx + D4)[ff];
+      }
       for (int c = tid; c < D4; c += SA_CTHREADS) {
         const float4 dg = hdg[c], be = hbe[c];
         reinterpret_cast<float4*>(dctx_s)[c] = make_float4(dg.x * be.x, dg.y * be.y, dg.z * be.z, dg.w * be.w);
+        const float4 cx = hcx[c];
+        reinterpret_cast<float4*>(cx_s)[c] = cx;
         if (l0 == 0) {                             // the segment holding the image's first row writes d bpre
-          const float4 cx = hcx[c];
           float4 db;
           db.x = dg.x * cx.x * be.x * (1.f - be.x); db.y = dg.y * cx.y * be.y * (1.f - be.y);
           db.z = dg.z * cx.z * be.z * (1.f - be.z); db.w = dg.w * cx.w * be.w * (1.f - be.w);
@@ -632,6 +639,9 @@ __global__ void __launch_bounds__(SA_THREADS, 1) attn_bwd_stream_kernel(const SA
     k.next(ring.NST); kg = (kg + 1 == SA_NG) ? 0 : kg + 1;
 
     // ---- B: d alpha[l] = dctx . feat[b,l,:] (+ upstream terms);  dfeat += alpha[l] * dctx        (:21)
+    // The softmax backward only sees d alpha up to a per-image constant; dctx . ctx (= sum_l alpha_l dctx . feat_l) is
+    // removed INSIDE the dot product -- dctx . (feat_l - ctx) -- so the later dalpha - sum_l alpha dalpha does not cancel
+    // two large fp32 numbers (this is what bounds the accuracy of dq, hence of attention.U's gradient).
     float4* dfb = a.dfeat ? reinterpret_cast<float4*>(a.dfeat) + ((int64_t)b * L + l0) * D4 : nullptr;
     for (int r0 = 0; r0 < nl; r0 += R, k.next(ring.NST), kg = (kg + 1 == SA_NG) ? 0 : kg + 1) {
       if (kg != grp) continue;
@@ -647,10 +657,11 @@ __global__ void __launch_bounds__(SA_THREADS, 1) attn_bwd_stream_kernel(const SA
 #pragma unroll 4
         for (int c = lane; c < D4; c += 32) {
           const float4 dc = reinterpret_cast<const float4*>(dctx_s)[c];
+          const float4 cx = reinterpret_cast<const float4*>(cx_s)[c];
           const float4 x0 = st[rr * D4 + c];
-          const float4 x1 = has2 ? st[rr2 * D4 + c] : f4_zero();
-          d0 = fmaf(x0.x, dc.x, d0); d0 = fmaf(x0.y, dc.y, d0); d0 = fmaf(x0.z, dc.z, d0); d0 = fmaf(x0.w, dc.w, d0);
-          d1 = fmaf(x1.x, dc.x, d1); d1 = fmaf(x1.y, dc.y, d1); d1 = fmaf(x1.z, dc.z, d1); d1 = fmaf(x1.w, dc.w, d1);
+          const float4 x1 = has2 ? st[rr2 * D4 + c] : cx;
+          d0 = fmaf(x0.x - cx.x, dc.x, d0); d0 = fmaf(x0.y - cx.y, dc.y, d0); d0 = fmaf(x0.z - cx.z, dc.z, d0); d0 = fmaf(x0.w - cx.w, dc.w, d0);
+          d1 = fmaf(x1.x - cx.x, dc.x, d1); d1 = fmaf(x1.y - cx.y, dc.y, d1); d1 = fmaf(x1.z - cx.z, dc.z, d1); d1 = fmaf(x1.w - cx.w, dc.w, d1);
           if (dfb) {
             float4 o = dfb[(int64_t)i0 * D4 + c];
             f4_fma(o, al0, dc);
@@ -689,8 +700,17 @@ __global__ void __launch_bounds__(SA_THREADS, 1) attn_bwd_stream_kernel(const SA
 
     // ---- D: score backward partial sums, thread-per-column over the segment's Ws rows               (:18-19)
     float4 x1 = f4_zero(), x2 = f4_zero(), y1 = f4_zero(), y2 = f4_zero();
+    // sum_l de_l = 0 over the image, so any per-(image, h) constant may be subtracted from t_l and from t_l^2:
+    // with tc = tanh(Ws[b,0,h] + q_h) the sums run over (t_l - tc) and (tc^2 - t_l^2), which are SMALL whenever t varies
+    // little along l -- the case in which the textbook form sum_l de_l (1 - t_l^2) cancels catastrophically in fp32.
     float4 qq = (g < G && f < H4) ? reinterpret_cast<const float4*>(q_s)[f] : f4_zero();
     qq = make_float4(TANH_C * qq.x, TANH_C * qq.y, TANH_C * qq.z, TANH_C * qq.w);
+    float4 tc = f4_zero();
+    if (g < G && f < H4) {
+      const float4 w0 = reinterpret_cast<const float4*>(w0_s)[f];
+      tc.x = fmaf(-2.f, tanh_r(fmaf(w0.x, TANH_C, qq.x)), 1.f); tc.y = fmaf(-2.f, tanh_r(fmaf(w0.y, TANH_C, qq.y)), 1.f);
+      tc.z = fmaf(-2.f, tanh_r(fmaf(w0.z, TANH_C, qq.z)), 1.f); tc.w = fmaf(-2.f, tanh_r(fmaf(w0.w, TANH_C, qq.w)), 1.f);
+    }
     for (int r0 = 0; r0 < nl; r0 += R, k.next(ring.NST), kg = (kg + 1 == SA_NG) ? 0 : kg + 1) {
       if (kg != grp) continue;
       ring.wait_full(k);
@@ -703,7 +723,7 @@ __global__ void __launch_bounds__(SA_THREADS, 1) attn_bwd_stream_kernel(const SA
           const float4 w = st[rr * H4 + f];
           float t, u;
 #define SA_BWD_ELEM(X)                                                                    \
-  t = fmaf(-2.f, tanh_r(fmaf(w.X, TANH_C, qq.X)), 1.f); u = fmaf(-t, t, 1.f);             \
+  t = fmaf(-2.f, tanh_r(fmaf(w.X, TANH_C, qq.X)), 1.f); u = (tc.X - t) * (tc.X + t); t -= tc.X;   \
   x1.X = fmaf(ad, u, x1.X); x2.X = fmaf(al, u, x2.X); y1.X = fmaf(ad, t, y1.X); y2.X = fmaf(al, t, y2.X);
           SA_BWD_ELEM(x) SA_BWD_ELEM(y) SA_BWD_ELEM(z) SA_BWD_ELEM(w)
 #undef SA_BWD_ELEM
@@ -795,7 +815,7 @@ __global__ void __launch_bounds__(SA_THREADS, 1) attn_bwd_stream_kernel(const SA
 }
 
 static size_t bwd_fixed_smem(int D, int H, int seg_pad, int rp_pad, int maxseg) {
-  return 2 * SA_MAX_NST * 8 + (size_t)4 * SA_CTHREADS * 16 + (size_t)(D + H + seg_pad + rp_pad + 40) * 4 +
+  return 2 * SA_MAX_NST * 8 + (size_t)4 * SA_CTHREADS * 16 + (size_t)(2 * D + 2 * H + seg_pad + rp_pad + 40) * 4 +
          (size_t)2 * maxseg * 4 + 16;
 }
 
@@ -808,7 +828,7 @@ cudaError_t attn_step_bwd_stream(cudaStream_t st, int B, int L, int D, int H, co
   if (!attn_stream_supported(D, H) || (q_ld & 3) || (dgctx_ld & 3) || (dq_ld & 3) || (dbpre_ld & 3))
     return cudaErrorInvalidValue;
   if (B <= 0 || L <= 0) return cudaSuccess;
-  const int header = H + 3 * D;
+  const int header = 2 * H + 3 * D;
   const Geometry g0 = pick_geometry(B, L, D, H, 0, header);
   const Geometry g = pick_geometry(B, L, D, H, bwd_fixed_smem(D, H, (L + 3) & ~3, (g0.rp + 3) & ~3, g0.maxseg), header);
   const int seg_pad = (g.seg_rows + 3) & ~3, rp_pad = (g.rp + 3) & ~3;

@@ -110,8 +110,8 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {      // roun
 // fp32 tile [ROWS][32 k] as TMA delivered it -> bf16 tile, k-chunk-major core matrices: (r, k) at (k/8)*ROWS*16 + r*16 + (k%8)*2.
 // K-major source: 128-byte rows, 16-byte chunk c of row r stored at chunk c ^ (r & 7) (SWIZZLE_128B).
 // MN-major source: boxes of {32 mn, 32 k}, un-swizzled: (k, mn) at (mn/32)*4096 + k*128 + (mn%32)*4.
-template <int ROWS, bool MN>
-__device__ __forceinline__ void convert_bf16(const uint8_t* src, uint8_t* dst, int t) {
+template <int ROWS, bool MN, bool WITH_LO>
+__device__ __forceinline__ void convert_bf16(const uint8_t* src, uint8_t* dst, uint8_t* dst_lo, int t) {
   for (int idx = t; idx < ROWS * 4; idx += CONV_THREADS) {
     const int r = idx % ROWS, pch = idx / ROWS;          // row, 8-wide k chunk
     float v[8];
@@ -127,6 +127,15 @@ __device__ __forceinline__ void convert_bf16(const uint8_t* src, uint8_t* dst, i
     }
     uint4 o;
     o.x = pack_bf16(v[0], v[1]); o.y = pack_bf16(v[2], v[3]); o.z = pack_bf16(v[4], v[5]); o.w = pack_bf16(v[6], v[7]);
+    if (WITH_LO) {            // lo = bf16(x - float(hi)): x = hi + lo up to 2^-17 |x|
+      uint4 l;
+#define LO_PAIR(W, A, B) l.W = pack_bf16(A - __uint_as_float(o.W << 16), B - __uint_as_float(o.W & 0xffff0000u))
+      LO_PAIR(x, v[0], v[1]); LO_PAIR(y, v[2], v[3]); LO_PAIR(z, v[4], v[5]); LO_PAIR(w, v[6], v[7]);
+#undef LO_PAIR
+      // the source chunk pair is dead once v[] is loaded: the lo tile overwrites the fp32 tile's first half in place?  No --
+      // other threads still read it; the lo tile goes to its own region.
+      *reinterpret_cast<uint4*>(dst_lo + pch * (ROWS * 16) + r * 16) = make_uint4(l.x, l.y, l.z, l.w);
+    }
     *reinterpret_cast<uint4*>(dst + pch * (ROWS * 16) + r * 16) = o;
   }
 }
@@ -239,14 +248,22 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       if (lane == 0) {
         const uint32_t a_hi = smem_u32(smem + s * STAGE_BYTES), a_lo = a_hi + A_BYTES;
         const uint32_t b_hi = a_hi + 2 * A_BYTES, b_lo = b_hi + B_BYTES;
-        if (MODE == 1) {
+        if (MODE >= 1) {
           // bf16 tiles: k-chunk-major core matrices.  LBO = stride between 16-byte k chunks = rows*16, SBO = 128 (next 8 rows)
           const uint32_t idesc16 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
             const uint64_t da = make_desc(a_lo + k * 2 * (BM * 16), BM * 16, 128, 0);
             const uint64_t db = make_desc(b_lo + k * 2 * (BN * 16), BN * 16, 128, 0);
-            umma_bf16(tmem_base, da, db, idesc16, (i | k) != 0);
+            if (MODE == 2) {     // bf16x3: x = hi + lo (16 significand bits); lo*hi + hi*lo + hi*hi, fp32 accumulate
+              const uint64_t dal = make_desc(a_lo + A_BYTES / 2 + k * 2 * (BM * 16), BM * 16, 128, 0);
+              const uint64_t dbl = make_desc(b_lo + B_BYTES / 2 + k * 2 * (BN * 16), BN * 16, 128, 0);
+              umma_bf16(tmem_base, dal, db, idesc16, (i | k) != 0);
+              umma_bf16(tmem_base, da, dbl, idesc16, 1);
+              umma_bf16(tmem_base, da, db, idesc16, 1);
+            } else {
+              umma_bf16(tmem_base, da, db, idesc16, (i | k) != 0);
+            }
           }
         } else {
 #pragma unroll
@@ -277,9 +294,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const uint32_t ph = (i / STAGES) & 1;
       mbar_wait(&full_bar[s], ph);
       uint8_t* st = smem + s * STAGE_BYTES;
-      if (MODE == 1) {
-        convert_bf16<BM, A_MN>(st, st + A_BYTES, t);
-        convert_bf16<BN, B_MN>(st + 2 * A_BYTES, st + 2 * A_BYTES + B_BYTES, t);
+      if (MODE >= 1) {
+        // bf16 tiles live in the `lo` slot: hi in its first half, (MODE 2) the bf16 residual in its second half
+        convert_bf16<BM, A_MN, MODE == 2>(st, st + A_BYTES, st + A_BYTES + A_BYTES / 2, t);
+        convert_bf16<BN, B_MN, MODE == 2>(st + 2 * A_BYTES, st + 2 * A_BYTES + B_BYTES, st + 2 * A_BYTES + B_BYTES + B_BYTES / 2, t);
       } else {
       // elementwise, so it is oblivious to the swizzle: same byte offset in the hi and lo tiles
 #pragma unroll
@@ -447,7 +465,7 @@ cudaError_t gemm_tc_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, 
   if (splits > 1 && !accumulate) ACK(cudaMemset2DAsync(C, ldc * sizeof(float), 0, (size_t)N * sizeof(float), M, st));
 
   CUtensorMap mapA, mapB;
-  const bool plain = (mode == 1);      // the bf16 converter transposes MN-major boxes itself: un-swizzled boxes
+  const bool plain = (mode >= 1);      // the bf16 converter transposes MN-major boxes itself: un-swizzled boxes
   bool ok = a_mn ? make_map(&mapA, A, M, K, lda, BK, true, plain) : make_map(&mapA, A, K, M, lda, BM, false);
   ok = ok && (b_mn ? make_map(&mapB, B, N, K, ldb, BK, true, plain) : make_map(&mapB, B, K, N, ldb, BN, false));
   if (!ok) return cudaErrorInvalidValue;
@@ -466,6 +484,10 @@ cudaError_t gemm_tc_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, 
   if (mode == 1) {
     if (BN == 128) TC_DISPATCH(128, 1);
     TC_DISPATCH(64, 1);
+  }
+  if (mode == 2) {
+    if (BN == 128) TC_DISPATCH(128, 2);
+    TC_DISPATCH(64, 2);
   }
   if (BN == 128) TC_DISPATCH(128, 0);
   TC_DISPATCH(64, 0);

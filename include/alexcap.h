@@ -90,8 +90,11 @@ ALEXCAP_API const char* alexcap_last_error(void);   /* thread-local, static stor
 ALEXCAP_API int alexcap_device_check(void);
 /* Kernel launches enqueued by this library since load (host-side counter; memcpy/memset nodes not counted). */
 ALEXCAP_API unsigned long long alexcap_launch_count(void);
-/* GEMM engine used by every entry point below (default 1): 0 = fp32 CUDA-core tiles, 1 = tcgen05/TMEM/TMA tiles computing in
- * 3xTF32 (fp32-grade accuracy; calls whose operands TMA cannot map -- ld % 4 != 0 -- use engine 0).  Process-wide. */
+/* GEMM engine used by the training entry points below (default 3).  0 = fp32 CUDA-core tiles; 1 = tcgen05/TMEM/TMA tiles
+ * in 3xTF32 (operands split into tf32 hi/lo in shared memory, ~2^-21; the decode entry points always use it: exact token
+ * ids); 2 = tcgen05 bf16 operands / fp32 accumulate (what dims.dtype = ALEXCAP_BF16 selects for the duration of a call);
+ * 3 = tcgen05 bf16x3 (operands split into bf16 hi/lo pairs, three kind::f16 MMAs, ~2^-17: 1e-5-level gradients, 1.3x
+ * faster than engine 1).  Calls whose operands TMA cannot map (ld % 4 != 0) use engine 0.  Process-wide. */
 ALEXCAP_API int alexcap_set_gemm_engine(int engine);
 ALEXCAP_API int alexcap_get_gemm_engine(void);
 
@@ -196,7 +199,7 @@ ALEXCAP_API int alexcap_lstm_decode_greedy(const alexcap_dims* dims, const alexc
  * The building blocks, exported so the parity tests can pin each kernel on its own.
  * C[M,N] = act(alpha * op(A) op(B) + bias[N] + bias2[N]) (+ C if accumulate), fp32 SIMT or tensor-core path.
  *   transa=0: A is [M,K] (lda);  transa=1: A is stored [K,M] (lda).   transb=0: B is [K,N];  transb=1: B is [N,K].
- *   act: 0 none, 1 tanh, 2 relu.   engine: 0 = fp32 CUDA-core tiles, 1 = tcgen05 tensor-core tiles (3xTF32),
+ *   act: 0 none, 1 tanh, 2 relu.   engine: 0 = fp32 CUDA-core tiles, 1 = tcgen05 3xTF32, 100 = tcgen05 bf16, 200 = tcgen05 bf16x3,
  *   n >= 2 = tcgen05 with split-K forced to n. */
 ALEXCAP_API int alexcap_gemm_f32(int32_t transa, int32_t transb, int32_t M, int32_t N, int32_t K, float alpha,
                      const float* A, int64_t lda, const float* B, int64_t ldb,

@@ -12,7 +12,7 @@ cfg = dict(B=24, L=49, D=256, H=192, E=96, V=700, T=9)
 p = random_attn_params(cfg, seed=8)
 feat, gt = synth_inputs(cfg['B'], cfg['L'], cfg['D'], cfg['V'], cfg['T'], seed=5, dtype=torch.float64)
 ref = R.attn_train_step(p, feat, gt, cfg['V'], need_dfeat=True)
-for eng in (0, 1):
+for eng in (0, 1, 3):
     F_.set_gemm_engine(eng)
     dec = build_decoder(cfg, p)
     step = DecoderTrainStep(dec, need_dfeat=True)

@@ -34,10 +34,10 @@ def reference_modules():
     return dict(Decoder=Decoder, LanguageModel=LanguageModel, CustomCrossEntropyLoss=CustomCrossEntropyLoss)
 
 
-@pytest.fixture(params=[1, 0], ids=['tcgen05', 'simt'])
+@pytest.fixture(params=[3, 1, 0], ids=['bf16x3', 'tcgen05', 'simt'])
 def gemm_engine(request):
-    """Run a GPU test once per GEMM engine: 1 = tcgen05/TMEM/TMA 3xTF32 (the default), 0 = fp32 CUDA-core tiles."""
+    """Run a GPU test once per GEMM engine: 3 = tcgen05 bf16x3 (the training default), 1 = tcgen05/TMEM/TMA 3xTF32, 0 = fp32 CUDA-core tiles."""
     from imagecaptioning_b200 import functional as F_
     F_.set_gemm_engine(request.param)
     yield request.param
-    F_.set_gemm_engine(1)
+    F_.set_gemm_engine(3)
