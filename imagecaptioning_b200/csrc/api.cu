@@ -74,7 +74,7 @@ AttnWs attn_layout(const alexcap_dims* d, void* base, bool with_logits) {
   const bool drop = d->dropout_p > 0.f;
   w.MASK = drop ? a.take<float>(S * B * H) : nullptr;
   w.Hd = drop ? a.take<float>(S * B * H) : nullptr;
-  w.logits = with_logits ? a.take<float>(S * B * w.ldV) : nullptr;
+  w.logits = with_logits ? a.take<float>((int64_t)vocab_chunk_rows((int)(S * B), w.ldV) * w.ldV) : nullptr;   // ONE chunk
   w.row_loss = a.take<float>(S * B);
   w.scal = a.take<float>(64);
   w.dHout = a.take<float>(S * B * H);
@@ -284,20 +284,16 @@ static int attn_train_phases(const alexcap_dims* d, const alexcap_attn_params* P
     if (int rc = attn_fwd_core(d, P, feat, gt, drop_mask, w, st)) return rc;
     const float* hout = w.Hd ? w.Hd : w.XH + (int64_t)B * DH + D;
     const int64_t hld = w.Hd ? H : DH;
-    // vocabulary projection for all steps at once (AttentionLanguageModule.py:79) + CustomCrossEntropyLoss
-    API_CK(gemm_f32(st, false, true, SB, Vp, H, 1.f, hout, hld, P->deep_w, H, w.logits, w.ldV, P->deep_b, nullptr, false, ACT_NONE));
+    // vocabulary projection (AttentionLanguageModule.py:79) + CustomCrossEntropyLoss + vocab backward, in L2-sized row chunks
     API_CK(count_valid(st, w.tgt_tm, SB, d->ignore_index, w.scal));
-    API_CK(ce_rows(st, w.logits, w.tgt_tm, SB, Vp, w.ldV, d->label_smoothing, d->ignore_index,
-                   ce_denominator ? ce_denominator : w.scal, w.row_loss, w.logits));
+    if (int rc = vocab_ce_chunked(st, SB, Vp, H, hout, hld, P->deep_w, P->deep_b, w.tgt_tm, w.ldV, w.logits, d->label_smoothing,
+                                  d->ignore_index, ce_denominator ? ce_denominator : w.scal, w.row_loss, G->deep_w, G->deep_b,
+                                  w.dHout, w.cs_scratch)) return rc;
     API_CK(reduce_sum(st, w.row_loss, SB, w.scal + 1));
     if (reg) API_CK(attn_regulariser(st, B, S, L, d->reg_weight, w.ALPHA, w.R, w.scal + 2, w.reg_scratch));
     API_CK(finalize_loss(st, w.scal + 1, reg ? w.scal + 2 : nullptr, w.scal, loss_out));
     if (alphas_out)
       API_CK(cudaMemcpyAsync(alphas_out, w.ALPHA, sizeof(float) * (size_t)B * S * L, cudaMemcpyDeviceToDevice, st));
-    // vocab backward: dW_o = dlogits^T H ; db_o = colsum(dlogits) ; dH = dlogits W_o
-    API_CK(gemm_f32(st, true, false, Vp, H, SB, 1.f, w.logits, w.ldV, hout, hld, G->deep_w, H, nullptr, nullptr, false, ACT_NONE));
-    API_CK(col_sum(st, w.logits, SB, Vp, w.ldV, G->deep_b, false, w.cs_scratch));
-    API_CK(gemm_f32(st, false, false, SB, H, Vp, 1.f, w.logits, w.ldV, P->deep_w, H, w.dHout, H, nullptr, nullptr, false, ACT_NONE));
   }
   if (phase & 2) return attn_bwd_core(d, P, feat, nullptr, reg ? w.R : nullptr, G, dfeat, w, st);
   return 0;

@@ -38,7 +38,7 @@ LstmWs lstm_layout(const alexcap_dims* d, void* base, bool with_logits) {
   const bool drop = d->dropout_p > 0.f;
   w.MASK = drop ? a.take<float>(S * B * H) : nullptr;
   w.Hd = drop ? a.take<float>(S * B * H) : nullptr;
-  w.logits = with_logits ? a.take<float>(S * B * w.ldV) : nullptr;
+  w.logits = with_logits ? a.take<float>((int64_t)vocab_chunk_rows((int)(S * B), w.ldV) * w.ldV) : nullptr;   // ONE chunk
   w.row_loss = a.take<float>(S * B);
   w.scal = a.take<float>(64);
   w.dHout = a.take<float>(S * B * H);
@@ -185,15 +185,12 @@ int alexcap_lstm_train_fused(const alexcap_dims* d, const alexcap_lstm_params* P
   const int B = d->B, H = d->H, Vp = d->Vp, S = d->S, SB = S * B;
   if (int rc = lstm_fwd_core(d, P, feat, gt, drop_mask, w, st)) return rc;
   const float* hout = top_out(d, w);
-  API_CK(gemm_f32(st, false, true, SB, Vp, H, 1.f, hout, H, P->out_w, H, w.logits, w.ldV, P->out_b, nullptr, false, ACT_NONE));
   API_CK(count_valid(st, w.tgt_tm, SB, d->ignore_index, w.scal));
-  API_CK(ce_rows(st, w.logits, w.tgt_tm, SB, Vp, w.ldV, d->label_smoothing, d->ignore_index,
-                 ce_denominator ? ce_denominator : w.scal, w.row_loss, w.logits));
+  if (int rc = vocab_ce_chunked(st, SB, Vp, H, hout, H, P->out_w, P->out_b, w.tgt_tm, w.ldV, w.logits, d->label_smoothing,
+                                d->ignore_index, ce_denominator ? ce_denominator : w.scal, w.row_loss, G->out_w, G->out_b,
+                                w.dHout, w.cs_scratch)) return rc;
   API_CK(reduce_sum(st, w.row_loss, SB, w.scal + 1));
   API_CK(finalize_loss(st, w.scal + 1, nullptr, w.scal, loss_out));
-  API_CK(gemm_f32(st, false, false, SB, H, Vp, 1.f, w.logits, w.ldV, P->out_w, H, w.dHout, H, nullptr, nullptr, false, ACT_NONE));
-  API_CK(gemm_f32(st, true, false, Vp, H, SB, 1.f, w.logits, w.ldV, hout, H, G->out_w, H, nullptr, nullptr, false, ACT_NONE));
-  API_CK(col_sum(st, w.logits, SB, Vp, w.ldV, G->out_b, false, w.cs_scratch));
   return lstm_bwd_core(d, P, feat, G, dfeat, w, st);
 }
 

@@ -1,6 +1,7 @@
 // api_util.h -- error reporting and workspace carving shared by the C-ABI translation units.
 #pragma once
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "../../include/alexcap.h"
@@ -59,6 +60,40 @@ struct DtypeScope {
   }
   ~DtypeScope() { gemm_engine() = saved; }
 };
+
+// ---- vocabulary projection + CustomCrossEntropyLoss + vocabulary backward, chunked over rows (north_star item 4).
+// The logits exist only as a workspace chunk of `vocab_chunk_rows` rows: the projection GEMM produces it, the one-pass CE
+// kernel turns it into its gradient in place, the two backward GEMMs consume it, and the next chunk overwrites it -- the
+// caller never sees logits and the workspace is bounded (ALEXCAP_VOCAB_CHUNK_MB, default 4096 MB).  Measured on B200 at
+// cfg2: chunks small enough to stay L2-resident (24 MB: 5 chunks) make the step 9 % SLOWER -- the K = chunk-rows dW_o
+// GEMMs and their read-modify-write of dW_o cost more than the ~0.4 GB of HBM traffic they save -- so the default keeps
+// one chunk whenever it fits the budget.
+inline int vocab_chunk_rows(int SB, int64_t ldV) {
+  static const int64_t mb = [] { const char* v = getenv("ALEXCAP_VOCAB_CHUNK_MB"); return (v && *v) ? atoll(v) : 4096ll; }();
+  int64_t r = (mb << 20) / (ldV * 4);
+  r = r / 128 * 128;
+  if (r < 128) r = 128;
+  return r > SB ? SB : (int)r;
+}
+inline int vocab_ce_chunked(cudaStream_t st, int SB, int Vp, int H, const float* hout, int64_t hld, const float* Wo,
+                            const float* bo, const int32_t* tgt_tm, int64_t ldV, float* logits_chunk, float eps,
+                            int ignore_index, const float* denom, float* row_loss, float* dWo, float* dbo, float* dHout,
+                            float* cs_scratch) {
+  const int RC = vocab_chunk_rows(SB, ldV);
+  for (int r0 = 0; r0 < SB; r0 += RC) {
+    const int rows = SB - r0 < RC ? SB - r0 : RC;
+    const float* h = hout + (int64_t)r0 * hld;
+    // logits = h W_o^T + b_o  (AttentionLanguageModule.py:79 / LanguageModule.py:106)
+    API_CK(gemm_f32(st, false, true, rows, Vp, H, 1.f, h, hld, Wo, H, logits_chunk, ldV, bo, nullptr, false, ACT_NONE));
+    API_CK(ce_rows(st, logits_chunk, tgt_tm + r0, rows, Vp, ldV, eps, ignore_index, denom, row_loss + r0, logits_chunk));
+    // dW_o += dlogits^T h ; db_o += colsum(dlogits) ; dH = dlogits W_o
+    API_CK(gemm_f32(st, true, false, Vp, H, rows, 1.f, logits_chunk, ldV, h, hld, dWo, H, nullptr, nullptr, r0 > 0, ACT_NONE));
+    API_CK(col_sum(st, logits_chunk, rows, Vp, ldV, dbo, r0 > 0, cs_scratch));
+    API_CK(gemm_f32(st, false, false, rows, H, Vp, 1.f, logits_chunk, ldV, Wo, H, dHout + (int64_t)r0 * H, H, nullptr, nullptr,
+                    false, ACT_NONE));
+  }
+  return 0;
+}
 
 // Decoding must reproduce the reference's token ids exactly (fp32): never run it on a reduced-precision engine.
 struct ExactScope {

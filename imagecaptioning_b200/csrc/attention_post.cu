@@ -3,13 +3,24 @@
 // attention regulariser (AlexCap/LSTMwAttentionModel.py:70-71).
 #include "common.cuh"
 #include "kernels.h"
+#include "pipe.cuh"
 
 namespace alexcap {
 
 // ------------------------------------------------------------------------------------------ hoisted dWs
 // dWs[b,l,:] = w_v * sum_t de[b,t,l] * (1 - tanh^2(Ws[b,l,:] + q_t[b,:])) : one read of Ws, one write of dWs,
 // instead of a read-modify-write of the [B,L,H] accumulator on every reverse step.
-constexpr int DWS_ROWS = 4;
+// S tanh per element make this kernel MUFU-bound, so the exponential is factored: with r = 1/(1 + e^{2z}),
+// 1 - tanh^2 z = 4 r (1 - r) and e^{2(w+q)} = e^{2w} e^{2q}: e^{2w} is computed once per element, e^{2q_t} once per
+// (t, column) and shared by the DWS_ROWS rows a thread owns -- 1 + 1/DWS_ROWS MUFU per (element, t) instead of 2.
+// (exponents clamped to +-60 so the product of the two factors cannot overflow or hit 0 * inf)
+constexpr int DWS_ROWS = 8;
+__device__ __forceinline__ float4 exp2c4(const float4 x) {
+  float4 y;
+  y.x = ex2_ftz(fminf(fmaxf(TANH_C * x.x, -60.f), 60.f)); y.y = ex2_ftz(fminf(fmaxf(TANH_C * x.y, -60.f), 60.f));
+  y.z = ex2_ftz(fminf(fmaxf(TANH_C * x.z, -60.f), 60.f)); y.w = ex2_ftz(fminf(fmaxf(TANH_C * x.w, -60.f), 60.f));
+  return y;
+}
 __global__ void __launch_bounds__(256) attn_dws_kernel(int L, int H, int S, int B, const float* __restrict__ Ws,
                                                        const float* __restrict__ q, int64_t q_ld,
                                                        const float* __restrict__ wv, const float* __restrict__ de,
@@ -17,27 +28,28 @@ __global__ void __launch_bounds__(256) attn_dws_kernel(int L, int H, int S, int 
   const int b = blockIdx.y, l0 = blockIdx.x * DWS_ROWS, H4 = H >> 2;
   const float* deb = de + (int64_t)b * S * L;
   for (int c = threadIdx.x; c < H4; c += blockDim.x) {
-    const float4 v = __ldg(reinterpret_cast<const float4*>(wv) + c);
-    float4 w[DWS_ROWS], acc[DWS_ROWS];
+    float4 ew[DWS_ROWS], acc[DWS_ROWS];
 #pragma unroll
     for (int r = 0; r < DWS_ROWS; ++r) {
       const int l = l0 + r;
-      w[r] = (l < L) ? ldg4(reinterpret_cast<const float4*>(Ws) + ((int64_t)b * L + l) * H4 + c) : f4_zero();
+      ew[r] = exp2c4((l < L) ? ldg4(reinterpret_cast<const float4*>(Ws) + ((int64_t)b * L + l) * H4 + c) : f4_zero());
       acc[r] = f4_zero();
     }
     for (int t = 0; t < S; ++t) {
-      const float4 qt = __ldg(reinterpret_cast<const float4*>(q + ((int64_t)t * B + b) * q_ld) + c);
+      const float4 eq = exp2c4(__ldg(reinterpret_cast<const float4*>(q + ((int64_t)t * B + b) * q_ld) + c));
 #pragma unroll
       for (int r = 0; r < DWS_ROWS; ++r) {
         const int l = l0 + r;
         const float d = (l < L) ? __ldg(deb + (int64_t)t * L + l) : 0.f;
-        float a;
-        a = tanhf(w[r].x + qt.x); acc[r].x = fmaf(d, 1.f - a * a, acc[r].x);
-        a = tanhf(w[r].y + qt.y); acc[r].y = fmaf(d, 1.f - a * a, acc[r].y);
-        a = tanhf(w[r].z + qt.z); acc[r].z = fmaf(d, 1.f - a * a, acc[r].z);
-        a = tanhf(w[r].w + qt.w); acc[r].w = fmaf(d, 1.f - a * a, acc[r].w);
+        float rr;
+        rr = rcp_ftz(fmaf(ew[r].x, eq.x, 1.f)); acc[r].x = fmaf(d, fmaf(-rr, rr, rr), acc[r].x);
+        rr = rcp_ftz(fmaf(ew[r].y, eq.y, 1.f)); acc[r].y = fmaf(d, fmaf(-rr, rr, rr), acc[r].y);
+        rr = rcp_ftz(fmaf(ew[r].z, eq.z, 1.f)); acc[r].z = fmaf(d, fmaf(-rr, rr, rr), acc[r].z);
+        rr = rcp_ftz(fmaf(ew[r].w, eq.w, 1.f)); acc[r].w = fmaf(d, fmaf(-rr, rr, rr), acc[r].w);
       }
     }
+    float4 v = __ldg(reinterpret_cast<const float4*>(wv) + c);
+    v = make_float4(4.f * v.x, 4.f * v.y, 4.f * v.z, 4.f * v.w);
 #pragma unroll
     for (int r = 0; r < DWS_ROWS; ++r) {
       const int l = l0 + r;

@@ -103,9 +103,14 @@ __global__ void __launch_bounds__(256) col_sum_part_kernel(const float* __restri
   const int s = blockIdx.y;
   const int rows_per = (M + CS_SPLIT - 1) / CS_SPLIT;
   const int m0 = s * rows_per, m1 = min(M, m0 + rows_per);
-  float acc = 0.f;
-  for (int m = m0; m < m1; ++m) acc += __ldg(X + (int64_t)m * ld + n);
-  part[(int64_t)s * N + n] = acc;
+  float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;     // four independent chains: loads of several rows in flight
+  int m = m0;
+  for (; m + 3 < m1; m += 4) {
+    a0 += __ldg(X + (int64_t)m * ld + n); a1 += __ldg(X + (int64_t)(m + 1) * ld + n);
+    a2 += __ldg(X + (int64_t)(m + 2) * ld + n); a3 += __ldg(X + (int64_t)(m + 3) * ld + n);
+  }
+  for (; m < m1; ++m) a0 += __ldg(X + (int64_t)m * ld + n);
+  part[(int64_t)s * N + n] = (a0 + a1) + (a2 + a3);
 }
 __global__ void __launch_bounds__(256) col_sum_final_kernel(const float* __restrict__ part, int N, float* __restrict__ out,
                                                             int accumulate) {
