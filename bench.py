@@ -185,6 +185,29 @@ def dominant_kernel_roofline(c, dev, pk):
                      'bytes, see profiles/)' % (2 * B * L * max(H, D) * 4 / 1e6))
 
 
+def gemm_roofline(c, dev, pk):
+    """The GEMM group's kernel (tc::gemm_tc_kernel: 55 % of the step's kernel time, profiles/) on the largest GEMM of the
+    step, the vocabulary projection [S*B, H] x [V', H]^T, timed alone from a CUDA graph.  `achieved` counts the ALGORITHMIC
+    2MNK; the fp32 engines issue three tensor-core MMAs per product (bf16x3 / 3xTF32), so frac is against the measured
+    bf16 burst peak with that factor stated, not hidden."""
+    from imagecaptioning_b200 import functional as F_
+    M, N, K = (c['T'] + 1) * c['B'], (c['V'] + 3 + 3) // 4 * 4, c['H']
+    g = torch.Generator(device='cpu').manual_seed(2)
+    A = torch.randn(M, K, generator=g).to(dev)
+    W = torch.randn(N, K, generator=g).to(dev)
+    C = torch.empty(M, N, device=dev)
+    bf16 = c['dtype'] == 'bf16'
+    eng = 100 if bf16 else 200
+    ms = time_graph_events(lambda: F_.gemm(A, W, transa=False, transb=True, out=C, engine=eng), 8, 6)
+    tf = 2.0 * M * N * K / (ms * 1e-3) / 1e12
+    return dict(kernel='tc::gemm_tc_kernel', bound='tensor', achieved=round(tf, 1), peak=pk['bf16'], unit='TFLOP/s',
+                frac=round(tf / pk['bf16'], 4), traffic=None, ms_per_launch=round(ms, 5), shape=[M, N, K],
+                mma_per_product=1 if bf16 else 3, issued_frac=round((1 if bf16 else 3) * tf / pk['bf16'], 4),
+                peak_source=pk['src'],
+                note='fp32 operands are converted to bf16 (hi, lo) pairs in shared memory by the kernel; shared-memory '
+                     'bandwidth (TMA write + converter read/write + MMA operand reads), not the tensor pipe, bounds it')
+
+
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` captures (profiles/)
 NCU_TRAFFIC = {}
 _t = os.path.join(ROOT, 'profiles', 'ncu_traffic.json')
@@ -360,6 +383,7 @@ def main():
                                   'tcgen05 bf16 operands, fp32 accumulate (2e-2 parity)')
         if c['model'] == 'LSTMwAttentionModel':
             line['roofline'] = dominant_kernel_roofline(c, dev, pk)
+            line['roofline_gemm'] = gemm_roofline(c, dev, pk)
         if world == 1 and not args.no_cpu_baseline:
             cb, _, _ = time_cpu_port(c, steps=3, warmup=1, budget_s=25.0)
             line['cpu_baseline'] = cb
