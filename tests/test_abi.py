@@ -52,7 +52,7 @@ def test_bad_arguments_are_reported_not_swallowed():
     d.D = 4
     rc = lib.alexcap_attn_train_fused(C.byref(d), C.byref(P), None, None, C.byref(P), None, None, None, None, None, None, 0, None)
     assert rc == -1 and b'NULL' in lib.alexcap_last_error()
-    d.dtype = 1
+    d.dtype = 7                                                              # neither ALEXCAP_F32 nor ALEXCAP_BF16
     rc = lib.alexcap_attn_forward(C.byref(d), C.byref(P), None, None, None, None, None, None, 0, None)
     assert rc == -2
 
