@@ -185,6 +185,42 @@ def dominant_kernel_roofline(c, dev, pk):
                      'bytes, see profiles/)' % (2 * B * L * max(H, D) * 4 / 1e6))
 
 
+def optimizer_step_timing(model, step, dev, iters=20):
+    """SURVEY.md section 8(f) rank 1 (the step right after the hot path): clip_grad_norm_(1) + Adam.step() over the
+    decoder's parameters -- FusedClipAdam (alexcap_clip_adam_step, 3 launches) next to stock torch on the same device.
+    Informational: it is not part of `value`/`e2e` (BASELINE.json's metric is the fwd+bwd step)."""
+    import copy
+    from imagecaptioning_b200.optim import FusedClipAdam
+    ps = list(model.parameters())
+    order = {id(p): i for i, p in enumerate(step._params)}
+    grads = [step._grads[order[id(p)]] for p in ps]
+    saved = [p.detach().clone() for p in ps]
+    fused = FusedClipAdam(ps, lr=1e-4, weight_decay=1e-6, max_norm=1.0)
+    ref_ps = [torch.nn.Parameter(p.detach().clone()) for p in ps]
+    ref = torch.optim.Adam(ref_ps, lr=1e-4, weight_decay=1e-6)
+    for q, g in zip(ref_ps, grads):
+        q.grad = g.clone()
+
+    def t(fn):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(iters):
+            fn()
+        b.record(); torch.cuda.synchronize()
+        return a.elapsed_time(b) / iters
+
+    ms_f = t(lambda: fused.step(grads=grads))
+    ms_t = t(lambda: (torch.nn.utils.clip_grad_norm_(ref_ps, 1.0), ref.step()))
+    with torch.no_grad():
+        for p, s0 in zip(ps, saved):
+            p.copy_(s0)
+    return dict(what='clip_grad_norm_(1) + Adam.step() on %d tensors / %.1f M parameters' % (len(ps), sum(p.numel() for p in ps) / 1e6),
+                fused_ms=round(ms_f, 4), torch_ms=round(ms_t, 4), launches_fused=3)
+
+
 def gemm_roofline(c, dev, pk):
     """The GEMM group's kernel (tc::gemm_tc_kernel: 55 % of the step's kernel time, profiles/) on the largest GEMM of the
     step, the vocabulary projection [S*B, H] x [V', H]^T, timed alone from a CUDA graph.  `achieved` counts the ALGORITHMIC
@@ -384,6 +420,8 @@ def main():
         if c['model'] == 'LSTMwAttentionModel':
             line['roofline'] = dominant_kernel_roofline(c, dev, pk)
             line['roofline_gemm'] = gemm_roofline(c, dev, pk)
+        if world == 1 and c['model'] == 'LSTMwAttentionModel':
+            line['next_row_optimizer'] = optimizer_step_timing(model, step, dev)
         if world == 1 and not args.no_cpu_baseline:
             cb, _, _ = time_cpu_port(c, steps=3, warmup=1, budget_s=25.0)
             line['cpu_baseline'] = cb

@@ -10,6 +10,7 @@ from . import build as _build
 
 ALEXCAP_MAX_LAYERS = 8
 F32, BF16 = 0, 1
+OPT_MAX_TENSORS = 48      # ALEXCAP_OPT_MAX_TENSORS (include/alexcap.h)
 
 
 class Dims(C.Structure):
@@ -53,6 +54,9 @@ PROTOTYPES = {
     'alexcap_get_gemm_engine': (C.c_int, []),
     'alexcap_attn_workspace_bytes': (_SZ, [_DP]),
     'alexcap_attn_train_fused': (C.c_int, [_DP, _AP, _P, _P, _AP, _P, _P, _P, _P, _P, _P, _SZ, _P]),
+    'alexcap_clip_adam_scratch_floats': (C.c_size_t, []),
+    'alexcap_clip_adam_step': (C.c_int, [C.c_int32, _P, _P, _P, _P, _P, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float,
+                                         C.c_float, C.c_int64, _P, _P, _P]),
     'alexcap_attn_train_phase': (C.c_int, [_DP, _AP, _P, _P, _AP, _P, _P, _P, _P, _P, _P, _SZ, C.c_int32, _P]),
     'alexcap_attn_forward': (C.c_int, [_DP, _AP, _P, _P, _P, _P, _P, _P, _SZ, _P]),
     'alexcap_attn_backward': (C.c_int, [_DP, _AP, _P, _P, _P, _AP, _P, _P, _SZ, _P]),

@@ -195,6 +195,23 @@ ALEXCAP_API size_t alexcap_lstm_decode_workspace_bytes(const alexcap_dims* dims)
 ALEXCAP_API int alexcap_lstm_decode_greedy(const alexcap_dims* dims, const alexcap_lstm_params* params, const float* feat,
                                int64_t* ids, void* workspace, size_t workspace_bytes, void* stream);
 
+/* ------------------------------------------------------------------ optimizer step ----------
+ * Global-norm gradient clipping + Adam over ALL parameter tensors in three launches.  Replaces, with identical arithmetic,
+ * AlexCapModel.clip_gradient (AlexCap/LSTMModel.py:50-51 = torch.nn.utils.clip_grad_norm_(params, max_norm), called from
+ * train_LSTM.py:86-87 / train_LSTMwAttention.py:87-88) followed by optim.step() of torch.optim.Adam(params, lr, betas, eps,
+ * weight_decay) (train_LSTMwAttention.py:60, :109).  The learning rate is passed per call, so the reference's LambdaLR
+ * warm-up/cosine schedule (train_LSTMwAttention.py:58-76) keeps driving it from the host.
+ *   params / grads / exp_avg / exp_avg_sq: HOST arrays of n_tensors device pointers (fp32, numel[i] elements each)
+ *   max_norm <= 0: no clipping.  step: 1-based Adam step count (bias correction).  grads are scaled in place like
+ *   clip_grad_norm_ does.  norm_out (device, 1 float) or NULL: the total gradient norm BEFORE clipping.
+ *   scratch: device buffer of alexcap_clip_adam_scratch_floats() floats. */
+#define ALEXCAP_OPT_MAX_TENSORS 48
+ALEXCAP_API size_t alexcap_clip_adam_scratch_floats(void);
+ALEXCAP_API int alexcap_clip_adam_step(int32_t n_tensors, float* const* params, float* const* grads, float* const* exp_avg,
+                           float* const* exp_avg_sq, const int64_t* numel, float max_norm, float lr, float beta1,
+                           float beta2, float eps, float weight_decay, int64_t step, float* norm_out, float* scratch,
+                           void* stream);
+
 /* ------------------------------------------------------------------ kernel-level entry points ----------
  * The building blocks, exported so the parity tests can pin each kernel on its own.
  * C[M,N] = act(alpha * op(A) op(B) + bias[N] + bias2[N]) (+ C if accumulate), fp32 SIMT or tensor-core path.
