@@ -189,7 +189,6 @@ def optimizer_step_timing(model, step, dev, iters=20):
     """SURVEY.md section 8(f) rank 1 (the step right after the hot path): clip_grad_norm_(1) + Adam.step() over the
     decoder's parameters -- FusedClipAdam (alexcap_clip_adam_step, 3 launches) next to stock torch on the same device.
     Informational: it is not part of `value`/`e2e` (BASELINE.json's metric is the fwd+bwd step)."""
-    import copy
     from imagecaptioning_b200.optim import FusedClipAdam
     ps = list(model.parameters())
     order = {id(p): i for i, p in enumerate(step._params)}

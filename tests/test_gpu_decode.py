@@ -84,3 +84,70 @@ def test_decode_sequence_strings():
     assert dec.decode_sequence(torch.tensor([[6, 1, 2, 7, 3]])) == ['SOS w1 w2']
     assert dec.decode_sequence([6, 1, 2, 0]) == ['w1 w2']
     assert dec.decode_sequence(torch.tensor([[[1, 2, 7], [3, 0, 0]]])) == [['w1 w2', 'w3']]
+
+
+def test_config4_greedy_and_beam_batch_1024():
+    """BASELINE.json configs[3] at FULL size: greedy / beam-5 decoding of 1024 images (L=196, D=H=E=512, V=10000,
+    T_max=20) in fp32.  Token ids must equal the fp64 oracle's on a 32-image sample wherever the oracle's own top-1/top-2
+    logit margin makes the argmax well defined (> 1e-4; random weights give some near-ties that no fp32 run can pin)."""
+    import time
+    cfg = dict(B=1024, L=196, D=512, H=512, E=512, V=10000, T=20)
+    p = random_attn_params(cfg, seed=31, dtype=torch.float32, scale=1.0)
+    feat, _ = synth_inputs(cfg['B'], cfg['L'], cfg['D'], cfg['V'], cfg['T'], seed=8)
+    dec_full = build_decoder(cfg, p).eval()                      # END never wins: all 21 steps run (timing only)
+    dec_full.use_beam = False
+    # make END win for some images and not others: bias it to about the typical max logit of the random model
+    with torch.no_grad():
+        m = feat[:64].mean(1)
+        h0 = torch.tanh(m @ p['init_h.weight'].T + p['init_h.bias'])
+        top = (h0 @ p['deep_output.weight'].T + p['deep_output.bias']).max(1).values
+        p['deep_output.bias'][cfg['V'] + 2] += float(top.median())
+    dec = build_decoder(cfg, p).eval()
+    dec.use_beam = False
+    fd = feat.to(DEV)
+    ids, alphas = dec(fd, torch.empty(0, device=DEV))            # warm-up (allocations, attributes)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    ids, alphas = dec(fd, torch.empty(0, device=DEV))
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    print(f'\ncfg4 greedy decode: {cfg["B"] / dt:.0f} captions/s ({dt * 1e3:.1f} ms, rows stop at END)')
+    dec_full(fd, torch.empty(0, device=DEV))
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    ids_full, _ = dec_full(fd, torch.empty(0, device=DEV))
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    print(f'cfg4 greedy decode, all 21 steps: {cfg["B"] / dt:.0f} captions/s ({dt * 1e3:.1f} ms)')
+    assert int((ids_full == cfg['V'] + 2).sum()) == 0
+    assert ids.shape == (cfg['B'], cfg['T'] + 1) and float((alphas.sum(2)[:, 0] - 1).abs().max()) < 1e-4
+    sample = torch.arange(0, cfg['B'], 32)
+    p64 = {k: v.double() for k, v in p.items()}
+    rid, _, margins = R.attn_greedy(p64, feat[sample].double(), cfg['V'], cfg['T'])
+    end = cfg['V'] + 2
+    checked = 0
+    for j, b in enumerate(sample.tolist()):
+        ref, got = rid[j].tolist(), ids[b].cpu().tolist()
+        n = ref.index(end) + 1 if end in ref else len(ref)
+        well_defined = bool((margins[j, :n] > 1e-4).all())
+        if well_defined:
+            checked += 1
+            assert got[:n] == ref[:n], (b, got[:n], ref[:n])
+    assert checked >= len(sample) // 2
+    # beam-5 over the same 1024 images: runs batched, one sentence per image, ends with END where a beam completed
+    t0 = time.perf_counter()
+    bids, _ = dec.caption(fd, 5)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    print(f'cfg4 beam-5 decode: {cfg["B"] / dt:.0f} captions/s ({dt * 1e3:.1f} ms)')
+    lens = dec.last_beam_lens.cpu()
+    done = lens > 0
+    print(f'cfg4 beam-5: {int(done.sum())} of {cfg["B"]} images completed a beam; greedy rows checked: {checked}')
+    for b in torch.nonzero(done).flatten()[:64].tolist():
+        assert int(bids[b, int(lens[b]) - 1]) == end
+    for b in (0, 341, 682, 1023):                                  # exact vs the per-image oracle beam search
+        try:
+            ref, _ = R.attn_beam(p64, feat[b:b + 1].double(), cfg['V'], cfg['T'], 5)
+        except ValueError:
+            ref = []
+        assert bids[b, :int(lens[b])].cpu().tolist() == ref
