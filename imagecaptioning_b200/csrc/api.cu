@@ -45,6 +45,7 @@ struct AttnWs {
   float *logits, *row_loss, *scal;   // scal: [0]=n_valid [1]=ce_sum [2]=reg
   float *dHout, *dh_next, *dc, *dgctx, *R, *dwv_part, *dWs, *dEmbIn, *dh0, *dc0, *dm;
   float *cs_scratch, *reg_scratch;
+  uint8_t* arena; size_t arena_bytes;   // bf16 hi/lo operand copies of the big GEMMs (training layout only)
   int64_t ldV;
   size_t bytes;
 };
@@ -92,6 +93,12 @@ AttnWs attn_layout(const alexcap_dims* d, void* base, bool with_logits) {
   if (W5 > maxn) maxn = W5;
   w.cs_scratch = a.take<float>(64 * maxn);
   w.reg_scratch = a.take<float>(256);
+  w.arena = nullptr; w.arena_bytes = 0;
+  if (with_logits) {
+    w.arena_bytes = split_arena_bytes(B, L, D, H, E, Vp, S, vocab_chunk_rows((int)(S * B), w.ldV));
+    a.off = (a.off + 1023) & ~size_t(1023);
+    w.arena = reinterpret_cast<uint8_t*>(a.take<char>(w.arena_bytes));
+  }
   w.bytes = a.off + 256;
   return w;
 }
@@ -276,6 +283,7 @@ static int attn_train_phases(const alexcap_dims* d, const alexcap_attn_params* P
   if (!gt || !G || !loss_out) return fail(ALEXCAP_E_BADARG, "NULL gt / grads / loss_out");
   if (phase < 1 || phase > 3) return fail(ALEXCAP_E_BADARG, "phase must be 1, 2 or 3");
   w = attn_layout(d, workspace, true);
+  ArenaScope arena_scope(w.arena, w.arena_bytes);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int B = d->B, D = d->D, H = d->H, Vp = d->Vp, S = d->S, L = d->L, SB = S * B;
   const int64_t DH = D + H;
@@ -401,6 +409,24 @@ int alexcap_gemm_f32(int32_t transa, int32_t transb, int32_t M, int32_t N, int32
     // engine 1 = 3xTF32, heuristic split-K; 2..99 = 3xTF32 with split-K forced to `engine` (tests);
     // 100 = bf16 operands / fp32 accumulate, heuristic split-K; 100 + s = bf16 with split-K forced to s
     // 200 (+s) = bf16x3 (hi/lo bf16 pairs, three kind::f16 MMAs)
+    // 300 (+s) = bf16x3 over operands pre-split in HBM (gemm_ps.cu), 400 (+s) = bf16 pre-split; the copies live in a
+    // process-lifetime arena grown on demand (this entry point is the test / micro-benchmark hook: not capturable when it grows)
+    if (engine >= 300) {
+      static SplitArena arena;
+      const size_t need = ((size_t)M * (K + 8) + (size_t)N * (K + 8) + (size_t)K * (M + N + 16)) * 4 + (1 << 16);
+      if (arena.bytes < need) {
+        API_CK(cudaDeviceSynchronize());
+        if (arena.base) API_CK(cudaFree(arena.base));
+        arena.base = nullptr; arena.bytes = 0;
+        API_CK(cudaMalloc(reinterpret_cast<void**>(&arena.base), need));
+        arena.bytes = need;
+      }
+      arena.used = 0; arena.n = 0;
+      const int np = engine >= 400 ? 1 : 3;
+      API_CK(gemm_ps_f32(st, transa != 0, transb != 0, M, N, K, alpha, A, lda, B, ldb, C, ldc, bias, bias2, accumulate != 0, act,
+                         engine >= 400 ? engine - 400 : engine - 300, np, &arena));
+      return 0;
+    }
     const int mode = engine >= 200 ? 2 : engine >= 100 ? 1 : 0;
     const int force = engine >= 200 ? engine - 200 : engine >= 100 ? engine - 100 : (engine >= 2 ? engine : 0);
     API_CK(gemm_tc_f32(st, transa != 0, transb != 0, M, N, K, alpha, A, lda, B, ldb, C, ldc, bias, bias2, accumulate != 0, act,

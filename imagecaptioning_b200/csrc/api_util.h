@@ -61,6 +61,25 @@ struct DtypeScope {
   ~DtypeScope() { gemm_engine() = saved; }
 };
 
+// Big GEMMs of the call may keep bf16 hi/lo copies of their operands in this slice of the caller's workspace (gemm_ps.cu);
+// a copy is reused by every later GEMM of the call that reads the same matrix (feat, W_o, dlogits, dgates, ...).
+struct ArenaScope {
+  SplitArena arena;
+  SplitArena* saved;
+  ArenaScope(void* base, size_t bytes) : saved(split_arena()) {
+    arena.base = static_cast<uint8_t*>(base); arena.bytes = bytes;
+    split_arena() = base ? &arena : nullptr;
+  }
+  ~ArenaScope() { split_arena() = saved; }
+};
+// bytes that hold every operand copy one attention / LSTM training step can ask for
+inline size_t split_arena_bytes(int64_t B, int64_t L, int64_t D, int64_t H, int64_t E, int64_t Vp, int64_t S, int64_t chunk_rows) {
+  const int64_t W5 = 5 * H + D, DH = D + H;
+  const int64_t act = B * L * (D + H) + 2 * S * B * (W5 + DH + E + 5 * H) + chunk_rows * (Vp + 8) + S * B * H;
+  const int64_t wts = Vp * H + 2 * (4 * H * (E + D) + 4 * H * DH + (H + D) * H + W5 * H + H * D + 4 * H * H);
+  return (size_t)(act + wts) * 4 + (size_t)SplitArena::MAX_ENTRIES * 2048 + (1 << 20);
+}
+
 // ---- vocabulary projection + CustomCrossEntropyLoss + vocabulary backward, chunked over rows (north_star item 4).
 // The logits exist only as a workspace chunk of `vocab_chunk_rows` rows: the projection GEMM produces it, the one-pass CE
 // kernel turns it into its gradient in place, the two backward GEMMs consume it, and the next chunk overwrites it -- the
@@ -85,12 +104,15 @@ inline int vocab_ce_chunked(cudaStream_t st, int SB, int Vp, int H, const float*
     const float* h = hout + (int64_t)r0 * hld;
     // logits = h W_o^T + b_o  (AttentionLanguageModule.py:79 / LanguageModule.py:106)
     API_CK(gemm_f32(st, false, true, rows, Vp, H, 1.f, h, hld, Wo, H, logits_chunk, ldV, bo, nullptr, false, ACT_NONE));
+    SplitArena* arena = split_arena();
+    const size_t mark = arena ? arena->used : 0;      // the chunk buffer is rewritten per chunk: drop its bf16 copy afterwards
     API_CK(ce_rows(st, logits_chunk, tgt_tm + r0, rows, Vp, ldV, eps, ignore_index, denom, row_loss + r0, logits_chunk));
     // dW_o += dlogits^T h ; db_o += colsum(dlogits) ; dH = dlogits W_o
     API_CK(gemm_f32(st, true, false, Vp, H, rows, 1.f, logits_chunk, ldV, h, hld, dWo, H, nullptr, nullptr, r0 > 0, ACT_NONE));
     API_CK(col_sum(st, logits_chunk, rows, Vp, ldV, dbo, r0 > 0, cs_scratch));
     API_CK(gemm_f32(st, false, false, rows, H, Vp, 1.f, logits_chunk, ldV, Wo, H, dHout + (int64_t)r0 * H, H, nullptr, nullptr,
                     false, ACT_NONE));
+    if (arena && RC < SB) split_arena_release(arena, mark);
   }
   return 0;
 }

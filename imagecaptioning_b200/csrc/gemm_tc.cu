@@ -22,6 +22,7 @@
 
 #include "common.cuh"
 #include "kernels.h"
+#include "tc_ptx.cuh"
 
 namespace alexcap {
 
@@ -34,7 +35,6 @@ constexpr int CONV_WARPS = 16;                // hi/lo splitter + epilogue warps
 constexpr int CONV_THREADS = CONV_WARPS * 32;
 constexpr int TMA_WARP = CONV_WARPS, MMA_WARP = CONV_WARPS + 1;
 constexpr int NUM_THREADS = (CONV_WARPS + 2) * 32;
-constexpr uint32_t SPIN_LIMIT = 1u << 27;
 
 struct Params {
   float* C; const float* bias; const float* bias2;
@@ -46,67 +46,6 @@ struct Params {
 // of 4 k-rows); one K=8 MMA consumes 8 k-rows = 1024 bytes.
 constexpr uint32_t MN_LBO = 4096, MN_SBO = 512, MN_KSTEP = 1024;
 
-// ------------------------------------------------------------------------------------------------ PTX helpers
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-      "selp.u32 %0, 1, 0, p;\n\t}"
-      : "=r"(ok)
-      : "r"(smem_u32(bar)), "r"(parity)
-      : "memory");
-  return ok != 0;
-}
-// Bounded wait: a protocol bug must trap, not hang the GPU box.
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  uint32_t spins = 0;
-  while (!mbar_try_wait(bar, parity)) {
-    if (++spins > SPIN_LIMIT) __trap();
-  }
-}
-__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-      ::"r"(smem_u32(smem_dst)), "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar))
-      : "memory");
-}
-__device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-
-__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accum) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
-      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accum)
-      : "memory");
-}
-__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accum) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accum)
-      : "memory");
-}
-__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {      // round to nearest even
-  uint32_t r;
-  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
-  return r;
-}
 // fp32 tile [ROWS][32 k] as TMA delivered it -> bf16 tile, k-chunk-major core matrices: (r, k) at (k/8)*ROWS*16 + r*16 + (k%8)*2.
 // K-major source: 128-byte rows, 16-byte chunk c of row r stored at chunk c ^ (r & 7) (SWIZZLE_128B).
 // MN-major source: boxes of {32 mn, 32 k}, un-swizzled: (k, mn) at (mn/32)*4096 + k*128 + (mn%32)*4.
@@ -139,27 +78,12 @@ __device__ __forceinline__ void convert_bf16(const uint8_t* src, uint8_t* dst, u
     *reinterpret_cast<uint4*>(dst + pch * (ROWS * 16) + r * 16) = o;
   }
 }
-__device__ __forceinline__ void umma_commit(uint64_t* bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-
 // fp32 -> (hi, lo) with both parts exactly representable in TF32 (low 13 mantissa bits zero), round-to-nearest at both
 // levels so the residual error (~2^-22 |x|) is unbiased; the tensor core would otherwise TRUNCATE the low bits.
 __device__ __forceinline__ void split_tf32(uint32_t x, uint32_t& hi, uint32_t& lo) {
   hi = (x + 0x1000u) & 0xffffe000u;
   const float r = __uint_as_float(x) - __uint_as_float(hi);      // exact in fp32
   lo = (__float_as_uint(r) + 0x1000u) & 0xffffe000u;
-}
-
-// UMMA shared-memory descriptor, 128-byte swizzle (cute::UMMA::SmemDescriptor bit layout).
-__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout_type = 2) {
-  uint64_t d = 0;
-  d |= (uint64_t)((saddr & 0x3FFFF) >> 4);            // start address, bits [0,14)
-  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;   // leading-dimension byte offset, bits [16,30)
-  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;   // stride-dimension byte offset, bits [32,46)
-  d |= (uint64_t)1 << 46;                             // descriptor version (Blackwell)
-  d |= (uint64_t)layout_type << 61;                   // 2 = SWIZZLE_128B, 1 = SWIZZLE_128B_BASE32B
-  return d;
 }
 
 // ------------------------------------------------------------------------------------------------ kernel
@@ -382,24 +306,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 }
 
 // ------------------------------------------------------------------------------------------------ host side
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn get_encode() {
-  static EncodeTiledFn fn = nullptr;
-  static bool tried = false;
-  if (!tried) {
-    tried = true;
-    void* ptr = nullptr;
-    cudaDriverEntryPointQueryResult qres;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
-        qres == cudaDriverEntryPointSuccess)
-      fn = reinterpret_cast<EncodeTiledFn>(ptr);
-  }
-  return fn;
-}
-
 // 2-D fp32 tensor map: inner (contiguous) extent `inner`, outer extent `outer`, row pitch ld floats, box {32, box_outer}.
 static bool make_map(CUtensorMap* map, const float* base, int64_t inner, int64_t outer, int64_t ld, int box_outer,
                      bool mn_major, bool plain = false) {
@@ -444,6 +350,12 @@ cudaError_t gemm_tc_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, 
   using namespace tc;
   if (M <= 0 || N <= 0 || K <= 0) return cudaSuccess;
   if (!gemm_tc_supported(M, N, K, A, lda, B, ldb, C)) return cudaErrorNotSupported;
+  if (mode >= 1 && force_splits == 0 && split_arena() && gemm_ps_wanted(M, N, K)) {
+    // big GEMM inside a training step: split the operands once in HBM, feed the tensor pipe by TMA alone (gemm_ps.cu)
+    const cudaError_t e = gemm_ps_f32(st, ta, tb, M, N, K, alpha, A, lda, B, ldb, C, ldc, bias, bias2, accumulate, act, 0,
+                                      mode == 2 ? 3 : 1, split_arena());
+    if (e != cudaErrorMemoryAllocation) return e;       // arena full: convert in the kernel instead
+  }
   const bool a_mn = ta;        // transa: A stored [K,M] -> M contiguous
   const bool b_mn = !tb;       // transb=0: B stored [K,N] -> N contiguous
   const int num_kb = ceil_div(K, BK);

@@ -19,6 +19,22 @@ cudaError_t gemm_simt_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K
 cudaError_t gemm_tc_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, float alpha,
                         const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
                         const float* bias, const float* bias2, bool accumulate, int act, int force_splits, int mode = 0);
+// Pre-split engine (gemm_ps.cu): operands split once in HBM into bf16 hi (+ lo) copies that live in a bump arena (cached
+// per source pointer until released), then a persistent TMA -> tcgen05 kernel.  nprod: 1 = bf16, 3 = bf16x3.
+// Returns cudaErrorMemoryAllocation when the arena cannot hold the copies (the caller falls back to gemm_tc_f32).
+struct SplitArena {
+  static constexpr int MAX_ENTRIES = 256;
+  struct Entry { const float* src; int rows, cols; int64_t ld, ldo; uint16_t* hi; uint16_t* lo; size_t end; };
+  uint8_t* base = nullptr; size_t bytes = 0, used = 0;
+  Entry e[MAX_ENTRIES]; int n = 0;
+};
+SplitArena*& split_arena();                       // the arena big GEMMs of the current call may use (nullptr: none)
+void split_arena_release(SplitArena* a, size_t mark);   // forget every copy made after `mark` (= a->used at that time)
+bool gemm_ps_wanted(int M, int N, int K);
+cudaError_t gemm_ps_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, float alpha,
+                        const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
+                        const float* bias, const float* bias2, bool accumulate, int act, int force_splits, int nprod,
+                        SplitArena* arena);
 bool gemm_tc_supported(int M, int N, int K, const float* A, int64_t lda, const float* B, int64_t ldb, const float* C);
 int& gemm_engine();
 

@@ -31,10 +31,10 @@ for name, ta, tb, M, N, K in shapes:
     B = torch.randn((N, K) if tb else (K, N), device=dev)
     C = torch.empty(M, N, device=dev)
     row = []
-    engines = [0, 1, 100, 200]
+    engines = [1, 100, 200, 300, 400]
     for eng in engines:
         us = t(lambda: F_.gemm(A, B, transa=ta, transb=tb, out=C, engine=eng))
         row.append(f'e{eng}:{us:7.1f}us')
     tf = 2.0 * M * N * K / 1e12
-    us1 = float(row[1].split(':')[1][:-2]); us2 = float(row[2].split(':')[1][:-2])
-    print(f'{name} M={M} N={N} K={K}  ' + ' '.join(row) + f'   3xTF32 {tf / (us1 * 1e-6):6.1f} TF/s  bf16 {tf / (us2 * 1e-6):6.1f} TF/s  bf16x3 {tf / (float(row[3].split(":")[1][:-2]) * 1e-6):6.1f} TF/s')
+    us = [float(r.split(':')[1][:-2]) for r in row]
+    print(f'{name} M={M} N={N} K={K}  ' + ' '.join(row) + '   TF/s: ' + ' '.join(f'e{e}:{tf / (u * 1e-6):6.1f}' for e, u in zip(engines, us)))

@@ -97,3 +97,61 @@ def test_gemm_bf16_engine_layouts(F_, ta, tb, M, N, K):
     assert rel_err(out, ref + bias.double()) < 2e-5, rel_err(out, ref + bias.double())
     out = F_.gemm(A.to(DEV), B.to(DEV), transa=ta, transb=tb, M=M, N=N, K=K, lda=A.shape[1], ldb=B.shape[1], engine=103)
     assert rel_err(out, ref) < 2e-5            # split-K forced to 3
+
+
+# ---------------------------------------------------------------------------------------------- pre-split engine (gemm_ps.cu)
+PS_SHAPES = [(128, 128, 64), (256, 256, 256), (37, 53, 29), (130, 200, 100), (384, 1000, 520), (2176, 515, 96),
+             (2300, 1100, 200), (1, 7, 3)]
+
+
+@pytest.mark.parametrize('ta,tb', [(False, True), (False, False), (True, False), (True, True)])
+@pytest.mark.parametrize('M,N,K', PS_SHAPES)
+def test_gemm_presplit_bf16_layouts(F_, ta, tb, M, N, K):
+    """Persistent TMA -> tcgen05 kernel over operands split in HBM, bf16 mode: the fp64 product of the bf16-ROUNDED operands
+    up to fp32 accumulation error, for every operand-major combination (pins the TMA boxes and UMMA descriptors; 2300x1100
+    gives 162 tiles > 148 CTAs, so some CTAs run two work items through both TMEM accumulators)."""
+    g = torch.Generator().manual_seed(M * 1000 + N + K + 11)
+    pad_a = (-M) % 4 if ta else (-K) % 4
+    pad_b = (-K) % 4 if tb else (-N) % 4
+    A, B, _ = _mk(ta, tb, M, N, K, g, pad_a, pad_b)
+    Av = (A[:, :M] if ta else A[:, :K]).bfloat16().double()
+    Bv = (B[:, :K] if tb else B[:, :N]).bfloat16().double()
+    ref = (Av.T if ta else Av) @ (Bv.T if tb else Bv)
+    bias = torch.randn(N, generator=g)
+    out = F_.gemm(A.to(DEV), B.to(DEV), transa=ta, transb=tb, M=M, N=N, K=K, lda=A.shape[1], ldb=B.shape[1],
+                  bias=bias.to(DEV), engine=400)
+    assert rel_err(out, ref + bias.double()) < 2e-5, rel_err(out, ref + bias.double())
+    if K >= 128:
+        out = F_.gemm(A.to(DEV), B.to(DEV), transa=ta, transb=tb, M=M, N=N, K=K, lda=A.shape[1], ldb=B.shape[1], engine=402)
+        assert rel_err(out, ref) < 2e-5            # split-K forced to 2
+
+
+@pytest.mark.parametrize('ta,tb', [(False, True), (False, False), (True, False), (True, True)])
+@pytest.mark.parametrize('M,N,K', PS_SHAPES)
+def test_gemm_presplit_bf16x3_is_fp32_grade(F_, ta, tb, M, N, K):
+    g = torch.Generator().manual_seed(M * 1000 + N + K + 13)
+    pad_a = (-M) % 4 if ta else (-K) % 4
+    pad_b = (-K) % 4 if tb else (-N) % 4
+    A, B, ref = _mk(ta, tb, M, N, K, g, pad_a, pad_b)
+    C0 = torch.randn(M, N, generator=g)
+    Cd = C0.to(DEV)
+    F_.gemm(A.to(DEV), B.to(DEV), transa=ta, transb=tb, M=M, N=N, K=K, lda=A.shape[1], ldb=B.shape[1], out=Cd,
+            accumulate=True, alpha=0.5, engine=300)
+    assert rel_err(Cd, 0.5 * ref + C0.double()) < 2e-5
+    if K >= 192:
+        out = F_.gemm(A.to(DEV), B.to(DEV), transa=ta, transb=tb, M=M, N=N, K=K, lda=A.shape[1], ldb=B.shape[1], engine=303)
+        assert rel_err(out, ref) < 2e-5
+
+
+def test_gemm_presplit_epilogues_and_long_k(F_):
+    g = torch.Generator().manual_seed(21)
+    M, N, K = 300, 200, 4100
+    A, B, ref = _mk(False, True, M, N, K, g)
+    b1, b2 = torch.randn(N, generator=g), torch.randn(N, generator=g)
+    out = F_.gemm(A.to(DEV), B.to(DEV), bias=b1.to(DEV), bias2=b2.to(DEV), act=1, alpha=0.01, engine=300)
+    assert rel_err(out, torch.tanh(0.01 * ref + b1.double() + b2.double())) < 1e-4   # |z| up to ~5, output scale 1
+    out = F_.gemm(A.to(DEV), B.to(DEV), act=2, engine=300)
+    assert rel_err(out, ref.clamp_min(0)) < 2e-5
+    out = F_.gemm(A.to(DEV), B.to(DEV), engine=300)
+    e3, e1 = rel_err(out, ref), rel_err(F_.gemm(A.to(DEV), B.to(DEV), engine=400), ref)
+    assert e3 < 5e-6 and e1 > 100 * e3, (e3, e1)
