@@ -16,6 +16,7 @@ struct LstmWs {
   float *enc_bm, *In0;
   float *G[ALEXCAP_MAX_LAYERS], *Hs[ALEXCAP_MAX_LAYERS], *Cs[ALEXCAP_MAX_LAYERS];
   float *MASK, *Hd, *logits, *row_loss, *scal, *dHout, *dA, *dB, *dh_next, *dc, *dpre_bm, *cs_scratch;
+  uint8_t* arena; size_t arena_bytes;   // bf16 hi/lo operand copies of the big GEMMs (training layout only)
   int64_t ldV;
   size_t bytes;
 };
@@ -51,6 +52,15 @@ LstmWs lstm_layout(const alexcap_dims* d, void* base, bool with_logits) {
   int64_t maxn = Vp > 4 * H ? Vp : 4 * H;
   if (E > maxn) maxn = E;
   w.cs_scratch = a.take<float>(64 * maxn);
+  w.arena = nullptr; w.arena_bytes = 0;
+  if (with_logits) {
+    const int64_t I = E > H ? E : H, D = d->D;
+    const int64_t el = B * L * (D + E) + E * D + LT * B * E + nl * (2 * LT * B * 4 * H + 2 * (LT + 1) * B * H + 4 * H * (I + H) + 4 * H * H) +
+                       S * B * H + Vp * H + (int64_t)vocab_chunk_rows((int)(S * B), w.ldV) * (Vp + 8);
+    w.arena_bytes = (size_t)el * 4 + (size_t)SplitArena::MAX_ENTRIES * 2048 + (1 << 20);
+    a.off = (a.off + 1023) & ~size_t(1023);
+    w.arena = reinterpret_cast<uint8_t*>(a.take<char>(w.arena_bytes));
+  }
   w.bytes = a.off + 256;
   return w;
 }
@@ -181,6 +191,7 @@ int alexcap_lstm_train_fused(const alexcap_dims* d, const alexcap_lstm_params* P
   if (int rc = check_lstm_args(d, P, feat, workspace, workspace_bytes, w.bytes)) return rc;
   if (!gt || !G || !loss_out) return fail(ALEXCAP_E_BADARG, "NULL gt / grads / loss_out");
   w = lstm_layout(d, workspace, true);
+  ArenaScope arena_scope(w.arena, w.arena_bytes);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int B = d->B, H = d->H, Vp = d->Vp, S = d->S, SB = S * B;
   if (int rc = lstm_fwd_core(d, P, feat, gt, drop_mask, w, st)) return rc;

@@ -392,7 +392,8 @@ cudaError_t gemm_ps_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, 
   if (e == cudaSuccess) e = get_split(st, arena, B, tb ? N : K, tb ? K : N, ldb, with_lo, &sb);
   if (e != cudaSuccess) { split_arena_release(arena, mark); return e; }
 
-  constexpr int BN = 128;
+  static const int bn_env = [] { const char* v = getenv("ALEXCAP_PS_BN"); return v ? atoi(v) : 0; }();
+  const int BN = (bn_env == 128 || bn_env == 256) ? bn_env : ((N >= 1024 && (int64_t)ceil_div(M, BM) * ceil_div(N, 256) >= 296) ? 256 : 128);
   const int num_kb = ceil_div(K, BK);
   const int tiles_m = ceil_div(M, BM), tiles_n = ceil_div(N, BN);
   const int tiles = tiles_m * tiles_n;
@@ -429,15 +430,19 @@ cudaError_t gemm_ps_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, 
   int nsm = 148;
   { int dev = 0; if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev); }
   const int grid = p.n_items < nsm ? p.n_items : nsm;
-#define PS_DISPATCH(NP_)                                                                   \
+#define PS_DISPATCH(BN_, NP_)                                                              \
   do {                                                                                     \
-    if (!a_mn && !b_mn) return launch<BN, false, false, NP_>(st, maps, p, grid);           \
-    if (!a_mn && b_mn) return launch<BN, false, true, NP_>(st, maps, p, grid);             \
-    if (a_mn && b_mn) return launch<BN, true, true, NP_>(st, maps, p, grid);               \
-    return launch<BN, true, false, NP_>(st, maps, p, grid);                                \
+    if (!a_mn && !b_mn) return launch<BN_, false, false, NP_>(st, maps, p, grid);          \
+    if (!a_mn && b_mn) return launch<BN_, false, true, NP_>(st, maps, p, grid);            \
+    if (a_mn && b_mn) return launch<BN_, true, true, NP_>(st, maps, p, grid);              \
+    return launch<BN_, true, false, NP_>(st, maps, p, grid);                               \
   } while (0)
-  if (with_lo) PS_DISPATCH(3);
-  PS_DISPATCH(1);
+  if (BN == 256) {
+    if (with_lo) PS_DISPATCH(256, 3);
+    PS_DISPATCH(256, 1);
+  }
+  if (with_lo) PS_DISPATCH(128, 3);
+  PS_DISPATCH(128, 1);
 #undef PS_DISPATCH
 }
 

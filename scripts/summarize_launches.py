@@ -2,9 +2,12 @@
 import collections, csv, re, sys
 lines = [l for l in open(sys.argv[1]) if not l.startswith('==')]
 tot = collections.defaultdict(lambda: [0, 0.0])
-for row in csv.DictReader(lines):
-    if row.get('Metric Name') != 'gpu__time_duration.sum':
-        continue
+rows = [r for r in csv.DictReader(lines) if r.get('Metric Name') == 'gpu__time_duration.sum']
+if '--one-step' in sys.argv:
+    # one training step = the launches from one make_target_kernel (first kernel of a step) up to the next one
+    starts = [i for i, r in enumerate(rows) if 'make_target_kernel' in r['Kernel Name']]
+    rows = rows[starts[-2]:starts[-1]]
+for row in rows:
     name = re.sub(r'\(.*', '', row['Kernel Name'])
     v = float(row['Metric Value'].replace(',', ''))
     u = row['Metric Unit']

@@ -154,4 +154,4 @@ def test_gemm_presplit_epilogues_and_long_k(F_):
     assert rel_err(out, ref.clamp_min(0)) < 2e-5
     out = F_.gemm(A.to(DEV), B.to(DEV), engine=300)
     e3, e1 = rel_err(out, ref), rel_err(F_.gemm(A.to(DEV), B.to(DEV), engine=400), ref)
-    assert e3 < 5e-6 and e1 > 100 * e3, (e3, e1)
+    assert e3 < 1e-5 and e1 > 100 * e3, (e3, e1)     # hi + lo keeps ~17 significand bits per operand
