@@ -32,14 +32,15 @@ cudaError_t make_target(cudaStream_t st, const int32_t* gt, int B, int T, int st
 }
 
 // mean over regions (AttentionLanguageModule.py:117): one CTA per image, D/4 float4 columns x row groups
-__global__ void __launch_bounds__(256) mean_L_kernel(const float* __restrict__ feat, int L, int D, float* __restrict__ m) {
-  __shared__ float4 red[256];
+constexpr int MEAN_THREADS = 1024;     // one CTA per image: 32 warps x 8 loads in flight keep the SM's HBM share busy
+__global__ void __launch_bounds__(MEAN_THREADS) mean_L_kernel(const float* __restrict__ feat, int L, int D, float* __restrict__ m) {
+  __shared__ float4 red[MEAN_THREADS];
   const int b = blockIdx.x, D4 = D >> 2, tid = threadIdx.x;
   const float4* fb = reinterpret_cast<const float4*>(feat) + (int64_t)b * L * D4;
-  const bool wide = D4 >= 256;
-  const int G = wide ? 1 : 256 / D4;
+  const bool wide = D4 >= MEAN_THREADS;
+  const int G = wide ? 1 : MEAN_THREADS / D4;
   const float inv = 1.f / (float)L;
-  for (int c0 = 0; c0 < D4; c0 += 256) {
+  for (int c0 = 0; c0 < D4; c0 += MEAN_THREADS) {
     const int c = wide ? c0 + tid : tid % D4;
     const int g = wide ? 0 : tid / D4;
     float4 acc = f4_zero();
@@ -58,7 +59,7 @@ __global__ void __launch_bounds__(256) mean_L_kernel(const float* __restrict__ f
 }
 cudaError_t mean_over_L(cudaStream_t st, const float* feat, int B, int L, int D, float* m) {
   if (D & 3) return cudaErrorInvalidValue;
-  ALEXCAP_NOTE_LAUNCH(); mean_L_kernel<<<B, 256, 0, st>>>(feat, L, D, m);
+  ALEXCAP_NOTE_LAUNCH(); mean_L_kernel<<<B, MEAN_THREADS, 0, st>>>(feat, L, D, m);
   return cudaGetLastError();
 }
 
