@@ -175,11 +175,11 @@ def dominant_kernel_roofline(c, dev, pk):
     ach = w['attn_fwd_bytes_per_launch'] / (ms_f * 1e-3) / 1e9
     ach_b = w['attn_bwd_bytes_per_launch'] / (ms_b * 1e-3) / 1e9
     return dict(kernel='attn_fwd_stream_kernel', bound='hbm', achieved=round(ach, 1), peak=pk['hbm'], unit='GB/s',
-                frac=round(ach / pk['hbm'], 4), traffic=NCU_TRAFFIC.get('attn_fwd'), ms_per_launch=round(ms_f, 5),
+                frac=round(ach / pk['hbm'], 4), traffic=NCU_TRAFFIC.get('attn_fwd') if c is CONFIGS['cfg2'] else None, ms_per_launch=round(ms_f, 5),
                 algorithmic_bytes_per_launch=w['attn_fwd_bytes_per_launch'], peak_source=pk['src'],
                 backward=dict(kernel='attn_bwd_stream_kernel', achieved=round(ach_b, 1), frac=round(ach_b / pk['hbm'], 4),
                               ms_per_launch=round(ms_b, 5), algorithmic_bytes_per_launch=w['attn_bwd_bytes_per_launch'],
-                              traffic=NCU_TRAFFIC.get('attn_bwd')),
+                              traffic=NCU_TRAFFIC.get('attn_bwd') if c is CONFIGS['cfg2'] else None),
                 note='Ws+feat = %.0f MB per launch, re-read by each of the 2*S launches of a step; with a 126 MB L2 part '
                      'of it can hit L2 between consecutive launches (ncu, cache flushed: dram__bytes_read = algorithmic '
                      'bytes, see profiles/)' % (2 * B * L * max(H, D) * 4 / 1e6))
@@ -240,7 +240,8 @@ def gemm_roofline(c, dev, pk):
     ms_conv = time_graph_events(lambda: F_.gemm(A, W, transa=False, transb=True, out=C, engine=100 if bf16 else 200), 8, 6)
     tf = 2.0 * M * N * K / (ms * 1e-3) / 1e12
     return dict(kernel='ps::gemm_ps_kernel', bound='tensor', achieved=round(tf, 1), peak=pk['bf16'], unit='TFLOP/s',
-                frac=round(tf / pk['bf16'], 4), traffic=None, ms_per_launch=round(ms, 5), shape=[M, N, K],
+                frac=round(tf / pk['bf16'], 4), traffic=NCU_TRAFFIC.get('gemm_ps_logits') if (c is CONFIGS['cfg2']) else None,
+                ms_per_launch=round(ms, 5), shape=[M, N, K],
                 mma_per_product=1 if bf16 else 3, issued_frac=round((1 if bf16 else 3) * tf / pk['bf16'], 4),
                 with_split_ms=round(ms_split, 5), convert_in_kernel_ms=round(ms_conv, 5), peak_source=pk['src'],
                 note='operands pre-split into bf16 hi/lo copies in HBM, kernel = TMA -> smem -> tcgen05.mma only; bound by '

@@ -9,5 +9,5 @@ run() {  # name regex skip count
 run attn_fwd 'attn_fwd_stream_kernel' 20 1
 run attn_bwd 'attn_bwd_stream_kernel' 20 1
 run gemm_step 'gemm_tc_kernel' 20 2      # the two per-step forward GEMMs (query, gates)
-run gemm_big 'gemm_tc_kernel' 2 3        # Ws projection, embedding->gates, (first per-step)
+run gemm_ps 'gemm_ps_kernel' 12 5        # one step's big GEMMs: Ws projection, embedding->gates, vocabulary projection, dW_o
 run attn_dws 'attn_dws_kernel' 1 1

@@ -27,10 +27,14 @@ for rep in sorted(glob.glob(os.path.join(root, 'gpurun_out', tag + '_*.ncu-rep')
         rd = to_bytes(row[hdr.index('dram__bytes_read.sum')], units[hdr.index('dram__bytes_read.sum')])
         wr = to_bytes(row[hdr.index('dram__bytes_write.sum')], units[hdr.index('dram__bytes_write.sum')])
         out.append(f'    dram read+write per launch: {(rd + wr) / 1e6:.1f} MB')
+        if 'gemm_ps_kernel' in name and wr > traffic.get('_ps_wr', 0):      # the vocabulary projection writes the most (logits)
+            traffic['_ps_wr'] = wr
+            traffic['gemm_ps_logits'] = int(rd + wr)
         for key in ('attn_fwd', 'attn_bwd'):
             if key + '_stream' in name:
                 traffic[key] = int(rd + wr)
 open(os.path.join(root, 'profiles', tag + '_ncu_summary.txt'), 'w').write('\n'.join(out) + '\n')
+traffic.pop('_ps_wr', None)
 if traffic:
     json.dump(traffic, open(os.path.join(root, 'profiles', 'ncu_traffic.json'), 'w'))
 print('\n'.join(out[:60]))
