@@ -432,7 +432,13 @@ def main():
             line['cpu_baseline'] = cb
         print(json.dumps(line), flush=True)
     if dist:
-        dist.destroy_process_group()
+        # the whole-step CUDA graphs hold captured NCCL kernels: drop them before the communicator, and do not let the
+        # communicator's teardown outlive the measurement (every rank has finished its timed region by the barrier)
+        reducer.close()
+        torch.cuda.synchronize()
+        dist.barrier()
+        sys.stdout.flush(); sys.stderr.flush()
+        os._exit(0)
 
 
 if __name__ == '__main__':

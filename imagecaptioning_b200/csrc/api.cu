@@ -151,12 +151,16 @@ int attn_fwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
 
 // ------------------------------------------------------------------------------------------ attention backward core
 // dHout [S*B,H] (time-major) = d loss / d (h_t before dropout is applied => masked inside if dropout is on).
+// part bit 1: the reverse-time chain, then lstm.* and embedding gradients (the largest tensors after deep_output);
+// part bit 2: every remaining gradient (attention.*, f_beta, init_*, dfeat).  3 = everything.
 int attn_bwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const float* feat,
                   const float* dalphas, const float* reg_r, const alexcap_attn_params* G, float* dfeat,
-                  AttnWs& w, cudaStream_t st) {
+                  AttnWs& w, cudaStream_t st, int part = 3) {
   const int B = d->B, L = d->L, D = d->D, H = d->H, E = d->E, S = d->S;
   const int64_t DH = D + H, W5 = 5 * (int64_t)H + D, HD = H + D;
   const bool need_dfeat = d->need_dfeat && dfeat;
+  const int SB = S * B;
+  if (part & 1) {
   // Wback = [W_hh ; W_U ; W_beta]  ((4H + H + D) x H): dh_{t-1} = [dgates | dq | dbpre] Wback in one GEMM
   API_CK(cudaMemcpyAsync(w.Wback, P->lstm_w_hh, sizeof(float) * 4 * H * H, cudaMemcpyDeviceToDevice, st));
   API_CK(cudaMemcpyAsync(w.Wback + (int64_t)4 * H * H, P->att_U_w, sizeof(float) * H * H, cudaMemcpyDeviceToDevice, st));
@@ -187,12 +191,6 @@ int attn_bwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
     API_CK(gemm_f32(st, false, false, B, H, (int)W5, 1.f, g, W5, w.Wback, H, dhn, H, nullptr, nullptr, true, ACT_NONE));
   }
 
-  const int SB = S * B;
-  // attention.W : dWs in one pass, then one K = B*L GEMM
-  API_CK(attn_dws(st, B, L, H, S, w.Ws, w.QB, HD, P->att_v_w, w.DE, w.dWs));
-  API_CK(gemm_f32(st, true, false, H, D, B * L, 1.f, w.dWs, H, feat, D, G->att_W_w, D, nullptr, nullptr, false, ACT_NONE));
-  if (need_dfeat)
-    API_CK(gemm_f32(st, false, false, B * L, D, H, 1.f, w.dWs, H, P->att_W_w, D, dfeat, D, nullptr, nullptr, true, ACT_NONE));
   // lstm weights: dW = dgates_all^T [EmbIn | gctx | h_prev], K = S*B
   API_CK(gemm_f32(st, true, false, 4 * H, E, SB, 1.f, w.DGQ, W5, w.EmbIn, E, G->lstm_w_ih, E + D, nullptr, nullptr, false, ACT_NONE));
   API_CK(gemm_f32(st, true, false, 4 * H, D, SB, 1.f, w.DGQ, W5, w.XH, DH, G->lstm_w_ih + E, E + D, nullptr, nullptr, false, ACT_NONE));
@@ -203,6 +201,14 @@ int attn_bwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
   API_CK(gemm_f32(st, false, false, SB, E, 4 * H, 1.f, w.DGQ, W5, P->lstm_w_ih, E + D, w.dEmbIn, E, nullptr, nullptr, false, ACT_NONE));
   API_CK(fill_f32(st, G->emb_w, (int64_t)d->Vp * E, 0.f));
   API_CK(scatter_add_rows(st, w.dEmbIn, E, w.in_tm, SB, E, G->emb_w));
+  }   // part & 1
+  if (!(part & 2)) return 0;
+
+  // attention.W : dWs in one pass, then one K = B*L GEMM
+  API_CK(attn_dws(st, B, L, H, S, w.Ws, w.QB, HD, P->att_v_w, w.DE, w.dWs));
+  API_CK(gemm_f32(st, true, false, H, D, B * L, 1.f, w.dWs, H, feat, D, G->att_W_w, D, nullptr, nullptr, false, ACT_NONE));
+  if (need_dfeat)
+    API_CK(gemm_f32(st, false, false, B * L, D, H, 1.f, w.dWs, H, P->att_W_w, D, dfeat, D, nullptr, nullptr, true, ACT_NONE));
   // attention.U, f_beta
   API_CK(gemm_f32(st, true, false, H, H, SB, 1.f, w.DGQ + 4 * H, W5, w.XH + D, DH, G->att_U_w, H, nullptr, nullptr, false, ACT_NONE));
   API_CK(gemm_f32(st, true, false, D, H, SB, 1.f, w.DGQ + 5 * H, W5, w.XH + D, DH, G->f_beta_w, H, nullptr, nullptr, false, ACT_NONE));
@@ -272,6 +278,8 @@ size_t alexcap_attn_workspace_bytes(const alexcap_dims* d) {
 
 // phase bit 1: forward + loss + vocabulary backward (deep_output.{weight,bias} gradients final afterwards);
 // phase bit 2: reverse-time chain + every other weight gradient.  3 = the whole step.
+// phase 4 / phase 8 are the two halves of bit 2: 4 = chain + lstm.* and embedding gradients, 8 = all remaining gradients
+// (so a data-parallel caller can all-reduce the lstm/embedding bucket while the rest is still being computed).
 static int attn_train_phases(const alexcap_dims* d, const alexcap_attn_params* P, const float* feat, const int32_t* gt,
                              const alexcap_attn_params* G, float* dfeat, float* loss_out, float* alphas_out,
                              const float* drop_mask, const float* ce_denominator, void* workspace,
@@ -281,9 +289,19 @@ static int attn_train_phases(const alexcap_dims* d, const alexcap_attn_params* P
   AttnWs w = attn_layout(d, nullptr, true);
   if (int rc = check_attn_args(d, P, feat, workspace, workspace_bytes, w.bytes)) return rc;
   if (!gt || !G || !loss_out) return fail(ALEXCAP_E_BADARG, "NULL gt / grads / loss_out");
-  if (phase < 1 || phase > 3) return fail(ALEXCAP_E_BADARG, "phase must be 1, 2 or 3");
+  if (phase != 1 && phase != 2 && phase != 3 && phase != 4 && phase != 8)
+    return fail(ALEXCAP_E_BADARG, "phase must be 1, 2, 3 (= 1|2), 4 or 8 (the halves of 2)");
   w = attn_layout(d, workspace, true);
-  ArenaScope arena_scope(w.arena, w.arena_bytes);
+  // phases 2 / 4 / 8 continue the step phase 1 started (same arguments and workspace): feat, W_W, dgates ... stay split
+  // -- but only what the EARLIER phases made: a repeated phase 4 (say) must not find the copies of its previous run.
+  static thread_local SplitArena step_arena;
+  static thread_local size_t mark_after_1 = 0, mark_after_4 = 0;
+  ArenaScope arena_scope(w.arena, w.arena_bytes, &step_arena, (phase & 1) != 0);
+  if (!(phase & 1) && step_arena.base) {
+    size_t mark = (phase == 8) ? mark_after_4 : mark_after_1;
+    if (mark > step_arena.used) mark = step_arena.used;
+    split_arena_release(&step_arena, mark);
+  }
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int B = d->B, D = d->D, H = d->H, Vp = d->Vp, S = d->S, L = d->L, SB = S * B;
   const int64_t DH = D + H;
@@ -302,9 +320,13 @@ static int attn_train_phases(const alexcap_dims* d, const alexcap_attn_params* P
     API_CK(finalize_loss(st, w.scal + 1, reg ? w.scal + 2 : nullptr, w.scal, loss_out));
     if (alphas_out)
       API_CK(cudaMemcpyAsync(alphas_out, w.ALPHA, sizeof(float) * (size_t)B * S * L, cudaMemcpyDeviceToDevice, st));
+    mark_after_1 = mark_after_4 = step_arena.used;
   }
-  if (phase & 2) return attn_bwd_core(d, P, feat, nullptr, reg ? w.R : nullptr, G, dfeat, w, st);
-  return 0;
+  int rc = 0;
+  if (phase & 2) rc = attn_bwd_core(d, P, feat, nullptr, reg ? w.R : nullptr, G, dfeat, w, st, 3);
+  else if (phase & 12) rc = attn_bwd_core(d, P, feat, nullptr, reg ? w.R : nullptr, G, dfeat, w, st, phase == 4 ? 1 : 2);
+  if (phase == 4) mark_after_4 = step_arena.used;
+  return rc;
 }
 
 int alexcap_attn_train_fused(const alexcap_dims* d, const alexcap_attn_params* P, const float* feat, const int32_t* gt,

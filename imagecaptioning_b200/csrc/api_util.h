@@ -70,6 +70,14 @@ struct ArenaScope {
     arena.base = static_cast<uint8_t*>(base); arena.bytes = bytes;
     split_arena() = base ? &arena : nullptr;
   }
+  // A training step run as several phase calls keeps its copies from one call to the next: `keep` is the bookkeeping of
+  // the previous call on this thread; it is reused when it describes the same arena memory and `fresh` is false.
+  ArenaScope(void* base, size_t bytes, SplitArena* keep, bool fresh) : saved(split_arena()) {
+    if (fresh || keep->base != static_cast<uint8_t*>(base) || keep->bytes != bytes) {
+      keep->base = static_cast<uint8_t*>(base); keep->bytes = bytes; keep->used = 0; keep->n = 0;
+    }
+    split_arena() = base ? keep : nullptr;
+  }
   ~ArenaScope() { split_arena() = saved; }
 };
 // bytes that hold every operand copy one attention / LSTM training step can ask for

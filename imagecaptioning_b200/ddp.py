@@ -4,11 +4,14 @@ The reference is single-GPU (AlexCap/LSTM_opts.py:12-13); data parallelism is ne
 Every caption/image pair is independent, so the batch is sharded by rank with parameters replicated and the ONLY
 exchange is the gradient all-reduce.  DecoderTrainStep keeps all gradients in one flat fp32
 buffer laid out in gradient-finalisation order, so buckets are contiguous slices (no flatten/unflatten copies):
-    bucket 0  deep_output.{weight,bias}   final after the vocab/CE backward, BEFORE the reverse-time chain starts
-    bucket 1+ everything else             final after the chain
-`allreduce()` averages the whole buffer; `allreduce_bucket(i)` lets a caller overlap bucket 0 with the chain.
+    group 0  deep_output.{weight,bias}   final after the vocab/CE backward, BEFORE the reverse-time chain starts (phase 1)
+    group 1  lstm.*, embedding           final right after the chain (phase 4)
+    group 2  everything else             final at the end (phase 8)
+`allreduce()` averages the whole buffer; `step_overlapped()` all-reduces group g on a side stream while phase g+1 runs.
 """
 from __future__ import annotations
+
+import os
 
 import torch
 import torch.distributed as dist
@@ -18,6 +21,14 @@ class GradAllReducer:
     def __init__(self, step, world_size: int, group=None):
         self.step, self.world, self.group = step, world_size, group
         self.side = torch.cuda.Stream() if torch.cuda.is_available() else None
+        self._graphs = {}            # input set -> CUDA graph of the whole data-parallel step (kernels + NCCL)
+        self._graph_ok = os.environ.get('ALEXCAP_DDP_GRAPH', '1') != '0'
+
+    def close(self):
+        """Destroy the captured whole-step graphs (they reference the NCCL communicator): call before
+        dist.destroy_process_group()."""
+        torch.cuda.synchronize()
+        self._graphs.clear()
 
     def buckets(self):
         return self.step.grad_buckets()
@@ -30,35 +41,57 @@ class GradAllReducer:
             if not b.is_cuda:           # gloo (CPU tests) has no AVG
                 b.div_(self.world)
 
-    def _reduce(self, b):
+    def _reduce(self, b, gi=None):
+        if gi is not None and str(gi) in os.environ.get('ALEXCAP_DDP_SKIP', ''):     # timing experiments only
+            return
         dist.all_reduce(b, op=dist.ReduceOp.AVG if b.is_cuda else dist.ReduceOp.SUM, group=self.group)
         if not b.is_cuda:               # gloo (CPU tests) has no AVG
             b.div_(self.world)
 
     def step_overlapped(self):
-        """One data-parallel training step with the first gradient bucket (deep_output.*: ~1/3 of the bytes, final
-        after the vocabulary backward) all-reduced on a side stream WHILE the reverse-time chain runs; the remaining
-        buckets follow the chain on the main stream.  Returns the loss tensor."""
+        """One data-parallel training step: group 0 (deep_output.*) is all-reduced on a side stream WHILE the reverse-time
+        chain runs, group 1 (lstm.*, embedding) WHILE the remaining gradients are computed; only the small last group
+        is exposed.  Returns the loss tensor."""
         step = self.step
         if self.world <= 1 or not step.is_attn:
             loss = step.run_resident()
             self.allreduce()
             return loss
+        if self._graph_ok and step.use_cuda_graph and step._dims.dropout_p == 0:
+            # the whole step -- three phase launches, the side-stream fork / join and the NCCL all-reduces -- as ONE graph
+            key = step._cur
+            if key in self._graphs:
+                self._graphs[key].replay()
+                return step._loss
+            loss = self._run_phases(step, graphs=False)      # this call's step, eagerly (also warms up NCCL and the kernels)
+            try:
+                torch.cuda.synchronize()
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    self._run_phases(step, graphs=False)
+                self._graphs[key] = g
+            except Exception as e:                            # capture of the collectives not supported here: phase graphs
+                self._graph_ok = False
+                print(f'[imagecaptioning_b200.ddp] whole-step graph capture failed ({type(e).__name__}: {e}); '
+                      'falling back to per-phase graphs', flush=True)
+            return loss
+        return self._run_phases(step, graphs=True)
+
+    def _run_phases(self, step, graphs):
         main = torch.cuda.current_stream()
-        step.run_resident(phase=1)
-        ready = torch.cuda.Event()
-        ready.record(main)
-        bks = self.buckets()
-        self.side.wait_event(ready)
-        with torch.cuda.stream(self.side):
-            self._reduce(bks[0])
-            done = torch.cuda.Event()
-            done.record(self.side)
-        loss = step.run_resident(phase=2)
-        for b in bks[1:]:
-            self._reduce(b)
-        main.wait_event(done)
-        return loss
+        groups = step.grad_groups()
+        run = step.run_resident if graphs else (lambda phase: step._launch(phase))
+        for gi, (phase, g) in enumerate(((1, groups[0]), (4, groups[1]))):
+            run(phase=phase)
+            self.side.wait_stream(main)
+            with torch.cuda.stream(self.side):
+                if g.numel():
+                    self._reduce(g, gi)
+        run(phase=8)
+        if groups[2].numel():
+            self._reduce(groups[2], 2)
+        main.wait_stream(self.side)
+        return step._loss
 
     def global_ce_denominator(self, n_valid_local: torch.Tensor) -> torch.Tensor:
         """N_valid_global / world: with it as the CE divisor on every rank, the AVERAGED gradient equals the

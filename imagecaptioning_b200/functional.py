@@ -163,7 +163,8 @@ def attn_workspace_bytes(dims: Dims) -> int:
 
 def attn_train_fused(dims, params, feat, gt, grads, ws, dfeat=None, loss_out=None, alphas_out=None, drop_mask=None,
                      ce_denominator=None, phase=3):
-    """phase 3: the whole step.  phase 1 (forward + loss + vocab backward) then phase 2 (reverse chain + the other
+    """phase 3: the whole step.  phase 2 may itself be run as 4 (chain + lstm/embedding gradients) then 8 (the rest).
+    phase 1 (forward + loss + vocab backward) then phase 2 (reverse chain + the other
     weight gradients) is the same step in two calls (data-parallel overlap of the first gradient bucket)."""
     lib = ensure_device(feat.device)
     _req(feat, gt, dfeat, loss_out, alphas_out, drop_mask, ce_denominator, ws)

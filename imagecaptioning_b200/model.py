@@ -57,18 +57,22 @@ class DecoderTrainStep:
         for p in self._params:
             if p.dtype != torch.float32 or not p.is_contiguous() or p.device != dev:
                 raise F_._lib.AlexcapError('parameters must be contiguous float32 tensors on the features device')
-        # one flat fp32 gradient buffer, slices 16-byte aligned, vocab projection first (it is final first)
-        order = sorted(range(len(self._params)), key=lambda i: 0 if self._is_vocab(i) else 1)
+        # one flat fp32 gradient buffer, slices 16-byte aligned, in gradient-finalisation order: vocab projection (final
+        # after phase 1), then lstm.* / embedding (final after phase 4), then everything else
+        order = sorted(range(len(self._params)), key=self._group)
         sizes = [(self._params[i].numel() + 3) // 4 * 4 for i in order]
         self._flat_grads = torch.zeros(sum(sizes), dtype=torch.float32, device=dev)
         self._grads = [None] * len(self._params)
         off = 0
         self._vocab_elems = 0
+        self._group_end = [0, 0, 0]
         for i, n in zip(order, sizes):
             self._grads[i] = self._flat_grads[off:off + self._params[i].numel()].view_as(self._params[i])
             off += n
             if self._is_vocab(i):
                 self._vocab_elems = off
+            for gi in range(self._group(i), 3):
+                self._group_end[gi] = off
         self._dims = self.llm._dims(feat, gt, need_dfeat=self.need_dfeat)
         nbytes = F_.attn_workspace_bytes(self._dims) if self.is_attn else F_.lstm_workspace_bytes(self._dims)
         self._ws = F_.workspace(nbytes, dev)
@@ -89,14 +93,14 @@ class DecoderTrainStep:
 
     def _launch(self, phase=3):
         d = self._dims
-        if d.dropout_p > 0 and phase != 2:   # fresh mask every step (Philox counter advances)
+        if d.dropout_p > 0 and phase in (1, 3):   # fresh mask every step (Philox counter advances)
             d.offset += 1 << 32
         mask = self.llm._drop_mask_override
         if self.is_attn:
             F_.attn_train_fused(d, self._params, self._feat, self._gt, self._grads, self._ws, dfeat=self.dfeat,
                                 loss_out=self._loss, alphas_out=self._alphas, drop_mask=mask,
                                 ce_denominator=self.ce_denominator, phase=phase)
-        elif phase == 2:
+        elif phase in (2, 4, 8):
             return                               # plain LSTM: one call does the whole step (phase 1)
         else:
             P = self.llm._struct(self._params)
@@ -106,7 +110,8 @@ class DecoderTrainStep:
 
     def run_resident(self, phase=3):
         """One step on the inputs already staged in the static device buffers (bench: inputs resident in HBM).
-        phase=1 then phase=2 run the same step in two launches (see GradAllReducer.step_overlapped)."""
+        phase=1 then phase=2 -- or 1, 4, 8 (the two halves of 2) -- run the same step in several launches (see
+        GradAllReducer.step_overlapped)."""
         if self.use_cuda_graph and self._dims.dropout_p == 0:
             key = (self._cur, phase)
             if key not in self._graphs:
@@ -119,8 +124,9 @@ class DecoderTrainStep:
                 with torch.cuda.graph(g):
                     self._launch(phase)
                 self._graphs[key] = g
-                if phase == 2:               # the warm-up consumed phase 1's saved state (gates -> dgates in place)
-                    self._launch(1)
+                # the warm-up consumed the saved state of the earlier phases (gates -> dgates in place, accumulations)
+                for prev in {2: (1,), 4: (1,), 8: (1, 4)}.get(phase, ()):
+                    self._launch(prev)
             self._graphs[key].replay()
         else:
             self._launch(phase)
@@ -204,6 +210,21 @@ class DecoderTrainStep:
     def _is_vocab(self, i):
         names = F_._lib.ATTN_STATE_NAMES if self.is_attn else self.llm.param_names()
         return names[i].startswith('deep_output.') or names[i].startswith('rnn.linear.')
+
+    def _group(self, i):
+        """0: vocab projection, 1: lstm.* and embedding (attention model), 2: the rest."""
+        if self._is_vocab(i):
+            return 0
+        if self.is_attn:
+            n = F_._lib.ATTN_STATE_NAMES[i]
+            if n.startswith('lstm.') or n.startswith('embedding.'):
+                return 1
+        return 2
+
+    def grad_groups(self):
+        """The flat gradient buffer as contiguous slices in finalisation order (attention model: after phase 1 / 4 / 8)."""
+        e = self._group_end
+        return [self._flat_grads[:e[0]], self._flat_grads[e[0]:e[1]], self._flat_grads[e[1]:e[2]]]
 
     def grad_buckets(self, bucket_elems: int = 8 << 20):
         """Contiguous slices of the flat gradient buffer: [vocab projection] + ~32 MB chunks of the rest."""

@@ -1,6 +1,5 @@
-set -x
-python bench.py --steps 50 --warmup 10 > gpurun_out/r1g_bench.json 2> gpurun_out/r1g_bench.err; tail -2 gpurun_out/r1g_bench.err
-python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/r1g_bench_ref.json 2> gpurun_out/r1g_bench_ref.err; tail -2 gpurun_out/r1g_bench_ref.err
-ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/r1g_launches.csv python bench.py --steps 1 --warmup 3 --no-graph --no-cpu-baseline > gpurun_out/r1g_ncu_launch.log 2>&1
-bash scripts/ncu_capture.sh r1g
-ls -la gpurun_out/r1g_*
+N=$1
+s=$(date +%s)
+timeout 150 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus $N --steps 50 --warmup 10 > gpurun_out/r2y_n$N.json 2> gpurun_out/r2y_n$N.err < /dev/null
+echo "exit code $? after $(( $(date +%s) - s )) s"
+tail -3 gpurun_out/r2y_n$N.err; cut -c50-260 gpurun_out/r2y_n$N.json; grep -o '"e2e": {[^}]*}' gpurun_out/r2y_n$N.json

@@ -219,6 +219,46 @@ def test_two_phase_step_equals_fused(graph):
         assert torch.equal(b.grad_buckets()[0], vocab)               # phase 2 does not touch bucket 0
 
 
+@pytest.mark.parametrize('graph', [False, True])
+@pytest.mark.parametrize('need_dfeat', [False, True])
+def test_three_phase_step_equals_fused(graph, need_dfeat):
+    """Phases 1, 4, 8 (phase 2 split in two so that the lstm/embedding gradient group can be all-reduced while the
+    remaining gradients are computed) == the fused step; each gradient group is final after its phase."""
+    from imagecaptioning_b200.model import DecoderTrainStep
+    cfg = dict(V=60, E=16, D=32, H=32, T=6)
+    dec = build_decoder(cfg, random_attn_params(cfg, seed=4, dtype=torch.float32))
+    f, g = synth_inputs(5, 9, cfg['D'], cfg['V'], cfg['T'], seed=2)
+    a = DecoderTrainStep(dec, need_dfeat=need_dfeat)
+    a.stage(f.to(DEV), g.to(DEV))
+    want_loss = a.run_resident().clone()
+    want = a._flat_grads.clone()
+    want_dfeat = a.dfeat.clone() if need_dfeat else None
+    b = DecoderTrainStep(dec, use_cuda_graph=graph, need_dfeat=need_dfeat)
+    b.stage(f.to(DEV), g.to(DEV))
+    e = None
+    for it in range(2):
+        b._flat_grads.zero_()
+        b.run_resident(phase=1)
+        e = b._group_end
+        assert 0 < e[0] < e[1] < e[2] == want.numel()
+        g0 = b.grad_groups()[0].clone()
+        assert rel_err(g0, want[:e[0]]) < 1e-5
+        b.run_resident(phase=4)
+        g1 = b.grad_groups()[1].clone()
+        assert rel_err(g1, want[e[0]:e[1]]) < 1e-5                  # lstm.* and embedding final after phase 4
+        assert float(b.grad_groups()[2].abs().max()) == 0.0          # ... and nothing of the last group written yet
+        b.run_resident(phase=8)
+        assert rel_err(b._loss, want_loss) < 1e-6
+        assert rel_err(b._flat_grads, want) < 1e-5
+        if it == 1:     # (creating a phase's CUDA graph in iteration 0 re-runs the earlier phases: atomics reorder sums)
+            assert torch.equal(b.grad_groups()[0], g0) and torch.equal(b.grad_groups()[1], g1)
+        if need_dfeat:
+            assert rel_err(b.dfeat, want_dfeat) < 1e-5
+    names = b.grads_by_name()
+    assert names['lstm.weight_ih'].data_ptr() >= b._flat_grads.data_ptr() + 4 * e[0]
+    assert names['attention.U.weight'].data_ptr() >= b._flat_grads.data_ptr() + 4 * e[1]
+
+
 BF16_TOL = 2e-2     # BASELINE.json north_star: 2e-2 relative for the bf16 configs
 
 
