@@ -94,7 +94,10 @@ ALEXCAP_API unsigned long long alexcap_launch_count(void);
  * in 3xTF32 (operands split into tf32 hi/lo in shared memory, ~2^-21; the decode entry points always use it: exact token
  * ids); 2 = tcgen05 bf16 operands / fp32 accumulate (what dims.dtype = ALEXCAP_BF16 selects for the duration of a call);
  * 3 = tcgen05 bf16x3 (operands split into bf16 hi/lo pairs, three kind::f16 MMAs, ~2^-17: 1e-5-level gradients, 1.3x
- * faster than engine 1).  Calls whose operands TMA cannot map (ld % 4 != 0) use engine 0.  Process-wide. */
+ * faster than engine 1).  Inside the training entry points the LARGE GEMMs of engines 2 and 3 (M >= 256, >= 1 GFLOP) run on
+ * the pre-split path: each fp32 operand is split once into bf16 hi (+ lo) copies in the workspace and a persistent
+ * TMA -> tcgen05 kernel consumes them (gemm_ps.cu; ALEXCAP_GEMM_PRESPLIT=0 disables).
+ * Calls whose operands TMA cannot map (ld % 4 != 0) use engine 0.  Process-wide. */
 ALEXCAP_API int alexcap_set_gemm_engine(int engine);
 ALEXCAP_API int alexcap_get_gemm_engine(void);
 
@@ -122,7 +125,9 @@ ALEXCAP_API int alexcap_attn_train_fused(const alexcap_dims* dims, const alexcap
 /* The same step in two calls, so that a data-parallel caller can start the all-reduce of the vocabulary-projection
  * gradients (the largest tensors, final after phase 1) while phase 2 runs (the reference is
  * single-GPU and has no counterpart).  phase 1: forward + loss + vocab backward; phase 2: reverse-time chain and all
- * other weight gradients (same arguments and workspace as phase 1); phase 3: both (== alexcap_attn_train_fused). */
+ * other weight gradients (same arguments and workspace as phase 1); phase 3: both (== alexcap_attn_train_fused).
+ * Phase 2 may itself be run as phase 4 (reverse-time chain, then the lstm.* and embedding gradients) followed by phase 8
+ * (all remaining gradients), so that the second-largest gradient group can be exchanged while phase 8 runs. */
 ALEXCAP_API int alexcap_attn_train_phase(const alexcap_dims* dims, const alexcap_attn_params* params,
                              const float* feat, const int32_t* gt,
                              const alexcap_attn_params* grads, float* dfeat,
@@ -217,7 +222,9 @@ ALEXCAP_API int alexcap_clip_adam_step(int32_t n_tensors, float* const* params, 
  * C[M,N] = act(alpha * op(A) op(B) + bias[N] + bias2[N]) (+ C if accumulate), fp32 SIMT or tensor-core path.
  *   transa=0: A is [M,K] (lda);  transa=1: A is stored [K,M] (lda).   transb=0: B is [K,N];  transb=1: B is [N,K].
  *   act: 0 none, 1 tanh, 2 relu.   engine: 0 = fp32 CUDA-core tiles, 1 = tcgen05 3xTF32, 100 = tcgen05 bf16, 200 = tcgen05 bf16x3,
- *   n >= 2 = tcgen05 with split-K forced to n. */
+ *   n in 2..99 = tcgen05 3xTF32 with split-K forced to n (100 + n, 200 + n likewise);
+ *   300 (+n) = bf16x3 over operands pre-split in HBM (persistent kernel), 400 (+n) = bf16 pre-split; 500 / 600 = the same two
+ *   but reusing the previous call's operand copies when the pointers match (times the GEMM kernel alone; test hook). */
 ALEXCAP_API int alexcap_gemm_f32(int32_t transa, int32_t transb, int32_t M, int32_t N, int32_t K, float alpha,
                      const float* A, int64_t lda, const float* B, int64_t ldb,
                      float* C, int64_t ldc, const float* bias, const float* bias2,
