@@ -1,5 +1,1 @@
-N=$1
-s=$(date +%s)
-timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus $N --steps 50 --warmup 10 > gpurun_out/r1h_n$N.json 2> gpurun_out/r1h_n$N.err < /dev/null
-echo "exit code $? after $(( $(date +%s) - s )) s"
-cut -c50-260 gpurun_out/r1h_n$N.json
+timeout 600 python -m pytest tests/test_gpu_train.py -m gpu -x -q -k "large_batch" 2>&1 < /dev/null | grep -E "^E  |passed|failed" | cut -c1-250 | head

@@ -283,3 +283,28 @@ def test_attn_train_bf16_vs_oracle_fp64(shape):
     assert float(l32) != float(loss)
     from imagecaptioning_b200 import functional as F_
     assert F_.get_gemm_engine() != 2               # the scoped override was restored
+
+
+@pytest.mark.parametrize('dtype', ['f32', 'bf16'])
+def test_attn_large_batch_per_step_presplit_vs_oracle_fp64(dtype):
+    """B >= 256 (configs 3 and 5): the PER-STEP gates / dh GEMMs are large enough for the pre-split GEMM path too, with the
+    weight copies cached across the S steps and one activation copy per step in the workspace arena."""
+    from imagecaptioning_b200.model import DecoderTrainStep
+    cfg = dict(B=384, L=5, D=512, H=512, E=64, V=300, T=3)
+    p = random_attn_params(cfg, seed=21, dtype=torch.float32)
+    feat, gt = synth_inputs(cfg['B'], cfg['L'], cfg['D'], cfg['V'], cfg['T'], seed=6)
+    ref = R.attn_train_step({k: v.double() for k, v in p.items()}, feat.double(), gt, cfg['V'], need_dfeat=True)
+    dec = build_decoder(cfg, p)
+    dec.compute_dtype = dtype
+    tol = TOL if dtype == 'f32' else BF16_TOL
+    for graph in (False, True):
+        for q in dec.parameters():
+            q.grad = None
+        step = DecoderTrainStep(dec, need_dfeat=True, use_cuda_graph=graph)
+        for _ in range(2):
+            for q in dec.parameters():
+                q.grad = None
+            loss = step.forward_train(feat.to(DEV), gt.to(DEV))
+        assert abs(float(loss) - float(ref['loss'])) < tol * float(ref['loss'])
+        _check_grads({k: q.grad for k, q in dec.named_parameters()}, ref['grads'], tol=tol)
+        assert rel_err(step.dfeat, ref['dfeat']) < tol
