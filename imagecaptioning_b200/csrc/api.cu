@@ -134,10 +134,10 @@ int attn_fwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
     float* xh = w.XH + (int64_t)t * B * DH;
     float* qb = w.QB + (int64_t)t * B * HD;
     float* g = w.DGQ + (int64_t)t * B * W5;
-    API_CK(gemm_f32(st, false, true, B, H + D, H, 1.f, xh + D, DH, w.Wub, H, qb, HD, w.bub, nullptr, true, ACT_NONE));
+    { WeightBScope wb; API_CK(gemm_f32(st, false, true, B, H + D, H, 1.f, xh + D, DH, w.Wub, H, qb, HD, w.bub, nullptr, true, ACT_NONE)); }
     API_CK(attn_step_fwd(st, B, L, D, H, w.Ws, feat, qb, HD, qb + H, HD, P->att_v_w, w.ALPHA + (int64_t)t * L,
                          (int64_t)S * L, w.CTX + (int64_t)t * B * D, w.BETA + (int64_t)t * B * D, xh, DH));
-    API_CK(gemm_f32(st, false, true, B, 4 * H, D + H, 1.f, xh, DH, w.Wcat, DH, g, W5, nullptr, nullptr, true, ACT_NONE));
+    { WeightBScope wb; API_CK(gemm_f32(st, false, true, B, 4 * H, D + H, 1.f, xh, DH, w.Wcat, DH, g, W5, nullptr, nullptr, true, ACT_NONE)); }
     API_CK(lstm_pointwise_fwd(st, B, H, g, W5, w.Call + (int64_t)t * B * H, w.Call + (int64_t)(t + 1) * B * H,
                               xh + (int64_t)B * DH + D, DH, nullptr, 0));
   }
@@ -180,15 +180,15 @@ int attn_bwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
                               w.dHout + (int64_t)t * B * H, H, w.MASK ? w.MASK + (int64_t)t * B * H : nullptr,
                               (t == S - 1) ? nullptr : dhn + (int64_t)B * H, H, w.dc));
     // d gctx = dgates W_ih[:, E:]
-    API_CK(gemm_f32(st, false, false, B, D, 4 * H, 1.f, g, W5, P->lstm_w_ih + E, E + D, dgc, D, nullptr, nullptr,
-                    true, ACT_NONE));
+    { WeightBScope wb; API_CK(gemm_f32(st, false, false, B, D, 4 * H, 1.f, g, W5, P->lstm_w_ih + E, E + D, dgc, D, nullptr, nullptr,
+                    true, ACT_NONE)); }
     API_CK(attn_step_bwd(st, B, L, D, H, w.Ws, feat, qb, HD, P->att_v_w, w.ALPHA + (int64_t)t * L, (int64_t)S * L,
                          w.CTX + (int64_t)t * B * D, w.BETA + (int64_t)t * B * D, dgc, D,
                          dalphas ? dalphas + (int64_t)t * L : nullptr, (int64_t)S * L, reg_r,
                          g + 4 * H, W5, g + 5 * H, W5, w.DE + (int64_t)t * L, (int64_t)S * L, w.dwv_part,
                          need_dfeat ? dfeat : nullptr));
     // dh_{t-1} = [dgates | dq | dbpre] [W_hh ; W_U ; W_beta]
-    API_CK(gemm_f32(st, false, false, B, H, (int)W5, 1.f, g, W5, w.Wback, H, dhn, H, nullptr, nullptr, true, ACT_NONE));
+    { WeightBScope wb; API_CK(gemm_f32(st, false, false, B, H, (int)W5, 1.f, g, W5, w.Wback, H, dhn, H, nullptr, nullptr, true, ACT_NONE)); }
   }
 
   // lstm weights: dW = dgates_all^T [EmbIn | gctx | h_prev], K = S*B

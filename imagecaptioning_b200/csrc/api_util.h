@@ -125,6 +125,14 @@ inline int vocab_ce_chunked(cudaStream_t st, int SB, int Vp, int H, const float*
   return 0;
 }
 
+// Per-step GEMMs of the time loop: B = weights (or their concatenations built at the start of the call, many kernels and at
+// least one fully-ordered node earlier), so the GEMM kernel may prefetch its B tiles before griddepcontrol.wait.
+struct WeightBScope {
+  bool saved;
+  WeightBScope() : saved(gemm_b_is_weight()) { gemm_b_is_weight() = true; }
+  ~WeightBScope() { gemm_b_is_weight() = saved; }
+};
+
 // Decoding must reproduce the reference's token ids exactly (fp32): never run it on a reduced-precision engine.
 struct ExactScope {
   int saved;

@@ -209,6 +209,10 @@ static cudaError_t launch_cfg(cudaStream_t st, bool ta, bool tb, const GemmP& p)
   return cudaGetLastError();
 }
 
+bool& gemm_b_is_weight() {
+  static thread_local bool on = false;
+  return on;
+}
 int& gemm_engine() {
   // 0 = fp32 CUDA-core tiles; 1 = tcgen05 3xTF32 (2^-21: decoding always uses it); 2 = tcgen05 bf16 (mixed precision);
   // 3 = tcgen05 bf16x3 (hi/lo bf16 pairs, 2^-17, 1.3x faster than 3xTF32: the training default).  Per-call fallback to

@@ -40,6 +40,7 @@ struct Params {
   float* C; const float* bias; const float* bias2;
   int M, N, K; int64_t ldc; float alpha; int accumulate, act;
   int kb_per_split, num_kb;
+  int b_const;     // B was written long before the previous kernel (weights): its first tiles may be fetched before pdl_wait
 };
 // MN-major fp32/tf32 tiles (probed on B200, scripts/debug_tc_mn.py): boxes of {32 mn, 32 k} = 32 rows of 128 bytes,
 // TMA swizzle 128B_ATOM_32B, UMMA layout SWIZZLE_128B_BASE32B: LBO = 4096 (next 32-wide mn block), SBO = 512 (next group
@@ -132,6 +133,22 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   pdl_trigger();      // the next kernel in the stream may start its own prologue
+  // Weight operand (per-step GEMMs): the B tiles of the first ring pass do not depend on the previous kernel, so their
+  // L2 -> smem latency is put under the previous kernel's tail as well; the A tiles follow after the wait.
+  const int npre = p.b_const ? min(nkb, STAGES) : 0;
+  if (npre > 0 && warp == TMA_WARP && lane == 0) {
+    for (int i = 0; i < npre; ++i) {
+      uint8_t* sb = smem + i * STAGE_BYTES + 2 * A_BYTES;
+      mbar_expect_tx(&full_bar[i], A_BYTES + B_BYTES);
+      const int k0 = (kb0 + i) * BK;
+      if (B_MN) {
+#pragma unroll
+        for (int j = 0; j < BN / 32; ++j) tma_load_2d(sb + j * 4096, &tmB, n0 + 32 * j, k0, &full_bar[i]);
+      } else {
+        tma_load_2d(sb, &tmB, k0, n0, &full_bar[i]);
+      }
+    }
+  }
   pdl_wait();         // everything above overlapped the previous kernel's tail; its results are visible from here on
 
   if (warp == TMA_WARP) {
@@ -140,9 +157,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       for (int i = 0; i < nkb; ++i) {
         const int s = i % STAGES;
         const uint32_t ph = (i / STAGES) & 1;
-        mbar_wait(&empty_bar[s], ph ^ 1);
+        const bool pre = i < npre;                       // B tile already in flight, barrier already armed
+        if (!pre) {
+          mbar_wait(&empty_bar[s], ph ^ 1);
+          mbar_expect_tx(&full_bar[s], A_BYTES + B_BYTES);
+        }
         uint8_t* st = smem + s * STAGE_BYTES;
-        mbar_expect_tx(&full_bar[s], A_BYTES + B_BYTES);
         const int k0 = (kb0 + i) * BK;
         if (A_MN) {
 #pragma unroll
@@ -151,6 +171,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           tma_load_2d(st, &tmA, k0, m0, &full_bar[s]);
         }
         uint8_t* sb = st + 2 * A_BYTES;
+        if (pre) continue;
         if (B_MN) {
 #pragma unroll
           for (int j = 0; j < BN / 32; ++j) tma_load_2d(sb + j * 4096, &tmB, n0 + 32 * j, k0, &full_bar[s]);
@@ -360,14 +381,18 @@ cudaError_t gemm_tc_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, 
   const bool b_mn = !tb;       // transb=0: B stored [K,N] -> N contiguous
   const int num_kb = ceil_div(K, BK);
   const int tiles128 = ceil_div(M, BM) * ceil_div(N, 128);
-  const int BN = (tiles128 >= 120 || N > 64 * 1024) ? 128 : 64;
+  static const int bn_env = [] { const char* v = getenv("ALEXCAP_TC_BN"); return v ? atoi(v) : 0; }();
+  static const int minkb_env = [] { const char* v = getenv("ALEXCAP_TC_MINKB"); return v ? atoi(v) : 2; }();
+  const int BN = (bn_env == 64 || bn_env == 128) ? bn_env : (tiles128 >= 120 || N > 64 * 1024 || (int64_t)N * K >= (1 << 20)) ? 128 : 64;
+  // (latency-bound M = 128 GEMMs, measured in a PDL chain: the wide tile halves the A-tile re-reads from L2 once the weight
+  //  matrix is >= 4 MB; two k-blocks per split are enough -- scripts/bench_gemm.py --small)
   const int tiles = ceil_div(M, BM) * ceil_div(N, BN);
   // split-K (fp32 red.add into C) when the output grid alone cannot fill 148 SMs; no split with an activation
   int splits = 1;
   if (force_splits > 0) splits = force_splits;
   else if (act == ACT_NONE && tiles < 100) {
     splits = 148 / tiles;
-    const int max_by_k = num_kb / 4 > 0 ? num_kb / 4 : 1;     // keep >= 4 k-blocks per CTA
+    const int max_by_k = num_kb / minkb_env > 0 ? num_kb / minkb_env : 1;     // keep >= 2 k-blocks per CTA
     if (splits > max_by_k) splits = max_by_k;
     if (splits < 1) splits = 1;
   }
@@ -385,6 +410,7 @@ cudaError_t gemm_tc_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, 
   Params p;
   p.C = C; p.bias = bias; p.bias2 = bias2; p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.alpha = alpha;
   p.accumulate = accumulate ? 1 : 0; p.act = act; p.kb_per_split = kb_per; p.num_kb = num_kb;
+  p.b_const = (gemm_b_is_weight() && pdl_enabled()) ? 1 : 0;
   dim3 grid(ceil_div(N, BN), ceil_div(M, BM), splits);
 #define TC_DISPATCH(BN_, MODE_)                                                                 \
   do {                                                                                          \

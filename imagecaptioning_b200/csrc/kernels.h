@@ -37,6 +37,9 @@ cudaError_t gemm_ps_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, 
                         SplitArena* arena);
 bool gemm_tc_supported(int M, int N, int K, const float* A, int64_t lda, const float* B, int64_t ldb, const float* C);
 int& gemm_engine();
+// Hint for the calls made while it is true: the B operand holds weights that were final before the PREVIOUS kernel of the
+// stream started, so the kernel may fetch B tiles ahead of its programmatic-dependent-launch wait (api.cu: WeightBScope).
+bool& gemm_b_is_weight();
 
 // ---- attention (attention.cu)
 cudaError_t attn_step_fwd(cudaStream_t st, int B, int L, int D, int H, const float* Ws, const float* feat,

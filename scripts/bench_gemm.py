@@ -26,7 +26,7 @@ def t(fn, it=30):
     for _ in range(max(it // 10, 1)): g.replay()
     e.record(); torch.cuda.synchronize()
     return s.elapsed_time(e) / (max(it // 10, 1) * 10) * 1e3
-for name, ta, tb, M, N, K in shapes:
+for name, ta, tb, M, N, K in ([] if '--small' in sys.argv else shapes):
     A = torch.randn((K, M) if ta else (M, K), device=dev)
     B = torch.randn((N, K) if tb else (K, N), device=dev)
     C = torch.empty(M, N, device=dev)
@@ -38,3 +38,16 @@ for name, ta, tb, M, N, K in shapes:
     tf = 2.0 * M * N * K / 1e12
     us = [float(r.split(':')[1][:-2]) for r in row]
     print(f'{name} M={M} N={N} K={K}  ' + ' '.join(row) + '   TF/s: ' + ' '.join(f'e{e}:{tf / (u * 1e-6):6.1f}' for e, u in zip(engines, us)))
+
+print('--- per-step GEMMs as they run inside the step: accumulate into a pre-zeroed C (no memset node), PDL-chained launches')
+for name, ta, tb, M, N, K in shapes[:4]:
+    A = torch.randn((K, M) if ta else (M, K), device=dev)
+    B = torch.randn((N, K) if tb else (K, N), device=dev)
+    C = torch.zeros(M, N, device=dev)
+    row = []
+    for eng in (1, 100, 200, 500):
+        if eng == 500:
+            F_.gemm(A, B, transa=ta, transb=tb, out=C, engine=300)
+        us = t(lambda: F_.gemm(A, B, transa=ta, transb=tb, out=C, accumulate=True, engine=eng))
+        row.append(f'e{eng}:{us:6.2f}us')
+    print(f'{name} M={M} N={N} K={K}  ' + ' '.join(row))
