@@ -57,6 +57,8 @@ PROTOTYPES = {
     'alexcap_clip_adam_scratch_floats': (C.c_size_t, []),
     'alexcap_clip_adam_step': (C.c_int, [C.c_int32, _P, _P, _P, _P, _P, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float,
                                          C.c_float, C.c_int64, _P, _P, _P]),
+    'alexcap_features_from_nchw': (C.c_int, [C.c_int32, C.c_int32, C.c_int32, _P, _P, _P]),
+    'alexcap_dfeat_to_nchw': (C.c_int, [C.c_int32, C.c_int32, C.c_int32, _P, _P, C.c_int32, _P]),
     'alexcap_attn_train_phase': (C.c_int, [_DP, _AP, _P, _P, _AP, _P, _P, _P, _P, _P, _P, _SZ, C.c_int32, _P]),
     'alexcap_attn_forward': (C.c_int, [_DP, _AP, _P, _P, _P, _P, _P, _P, _SZ, _P]),
     'alexcap_attn_backward': (C.c_int, [_DP, _AP, _P, _P, _P, _AP, _P, _P, _SZ, _P]),

@@ -77,6 +77,37 @@ def workspace(nbytes: int, device) -> torch.Tensor:
 
 
 # ------------------------------------------------------------------------------------------------ kernels
+def features_from_nchw(nchw: torch.Tensor, out: torch.Tensor = None) -> torch.Tensor:
+    """[B, D, h, w] CNN output -> the decoder's [B, h*w, D] grid (LSTMwAttentionModel.py:64-66) in one transposing pass."""
+    lib = ensure_device(nchw.device)
+    if nchw.dim() != 4 or nchw.dtype != torch.float32 or not nchw.is_contiguous():
+        raise _lib.AlexcapError('features_from_nchw takes a contiguous float32 [B, D, h, w] tensor')
+    B, D, L = nchw.shape[0], nchw.shape[1], nchw.shape[2] * nchw.shape[3]
+    if out is None:
+        out = torch.empty(B, L, D, dtype=torch.float32, device=nchw.device)
+    if tuple(out.shape) != (B, L, D) or not out.is_contiguous() or out.dtype != torch.float32:
+        raise _lib.AlexcapError('features_from_nchw: out must be a contiguous float32 [B, h*w, D] tensor')
+    check(lib.alexcap_features_from_nchw(B, D, L, _ptr(nchw), _ptr(out), _stream()), 'alexcap_features_from_nchw')
+    return out
+
+
+def dfeat_to_nchw(dfeat: torch.Tensor, hw, out: torch.Tensor = None, accumulate: bool = False) -> torch.Tensor:
+    """Gradient w.r.t. the [B, L, D] grid -> [B, D, h, w] (what autograd would hand the CNN); accumulate adds into `out`."""
+    lib = ensure_device(dfeat.device)
+    B, L, D = dfeat.shape
+    h, w = hw
+    if h * w != L or dfeat.dtype != torch.float32 or not dfeat.is_contiguous():
+        raise _lib.AlexcapError('dfeat_to_nchw takes a contiguous float32 [B, h*w, D] tensor')
+    if out is None:
+        if accumulate:
+            raise _lib.AlexcapError('dfeat_to_nchw: accumulate needs an existing out tensor')
+        out = torch.empty(B, D, h, w, dtype=torch.float32, device=dfeat.device)
+    if tuple(out.shape) != (B, D, h, w) or not out.is_contiguous() or out.dtype != torch.float32:
+        raise _lib.AlexcapError('dfeat_to_nchw: out must be a contiguous float32 [B, D, h, w] tensor')
+    check(lib.alexcap_dfeat_to_nchw(B, D, L, _ptr(dfeat), _ptr(out), int(accumulate), _stream()), 'alexcap_dfeat_to_nchw')
+    return out
+
+
 def gemm(A, B, transa=False, transb=True, M=None, N=None, K=None, lda=None, ldb=None, out=None, ldc=None, bias=None,
          bias2=None, accumulate=False, act=0, alpha=1.0, engine=0):
     """C = act(alpha*op(A)op(B) + bias + bias2) (+C).  Shapes default from 2-D contiguous A, B."""

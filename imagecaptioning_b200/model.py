@@ -146,6 +146,41 @@ class DecoderTrainStep:
         self._feat.copy_(feat, non_blocking=True)
         self._gt.copy_(gt, non_blocking=True)
 
+    def stage_nchw(self, cnn_out, gt_labels):
+        """Stage one batch from the backbone's NCHW output [B, D, h, w] (device tensor): replaces the reference's
+        permute(0, 2, 3, 1).view(B, -1, C) (LSTMwAttentionModel.py:64-66) AND the staging copy by one transposing pass
+        into the static feature buffer.  Follow with run_resident() / forward_train_nchw()."""
+        if not cnn_out.is_cuda:
+            raise F_._lib.AlexcapError('stage_nchw takes the CNN output on the CUDA device')
+        x = cnn_out.detach()
+        if x.dtype != torch.float32:
+            x = x.float()
+        x = x.contiguous()
+        B, D, h, w = x.shape
+        gt = gt_labels if gt_labels.dtype == torch.int32 else gt_labels.to(torch.int32)
+        self._prepare(torch.empty(B, h * w, D, dtype=torch.float32, device='meta'), gt, x.device)
+        F_.features_from_nchw(x, out=self._feat)
+        self._gt.copy_(gt, non_blocking=True)
+        self._hw = (h, w)
+
+    def forward_train_nchw(self, cnn_out, gt_labels):
+        """forward_train on the backbone's NCHW output.  With need_dfeat=True, `dfeat_nchw()` afterwards returns the
+        gradient w.r.t. `cnn_out` in its own layout (the fine-tune phase, train_LSTMwAttention.py:51-55)."""
+        self.stage_nchw(cnn_out, gt_labels)
+        loss4 = self.run_resident()
+        for p, g in zip(self._params, self._grads):
+            if p.requires_grad:
+                if p.grad is None:
+                    p.grad = g.clone()
+                else:
+                    p.grad.add_(g)
+        return loss4[0]
+
+    def dfeat_nchw(self, out=None, accumulate=False):
+        if self.dfeat is None:
+            raise F_._lib.AlexcapError('dfeat_nchw needs DecoderTrainStep(need_dfeat=True)')
+        return F_.dfeat_to_nchw(self.dfeat, self._hw, out=out, accumulate=accumulate)
+
     def prefetch(self, features, gt_labels):
         """Start the H2D copy of the NEXT batch (pinned host tensors) into the idle input buffer set on a side stream,
         so that it overlaps the step running on the current set.  Pair with swap()+run_resident()."""

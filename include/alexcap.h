@@ -217,6 +217,15 @@ ALEXCAP_API int alexcap_clip_adam_step(int32_t n_tensors, float* const* params, 
                            float beta2, float eps, float weight_decay, int64_t step, float* norm_out, float* scratch,
                            void* stream);
 
+/* The CNN hand-off either side of the path.  The backbone's output is NCHW [B, D, h, w];
+ * the reference makes the decoder's grid with permute(0, 2, 3, 1).view(B, -1, C) (AlexCap/LSTMwAttentionModel.py:64-66,
+ * :79-80).  alexcap_features_from_nchw writes feat[b, l, d] = nchw[b, d, l] (L = h*w) in one pass -- e.g. straight into
+ * the buffer passed as `feat` to the training entry points; alexcap_dfeat_to_nchw is the way back for the gradient of the
+ * fine-tune phase (train_LSTMwAttention.py:51-55): dnchw[b, d, l] (+)= dfeat[b, l, d]. */
+ALEXCAP_API int alexcap_features_from_nchw(int32_t B, int32_t D, int32_t L, const float* nchw, float* feat, void* stream);
+ALEXCAP_API int alexcap_dfeat_to_nchw(int32_t B, int32_t D, int32_t L, const float* dfeat, float* dnchw, int32_t accumulate,
+                          void* stream);
+
 /* ------------------------------------------------------------------ kernel-level entry points ----------
  * The building blocks, exported so the parity tests can pin each kernel on its own.
  * C[M,N] = act(alpha * op(A) op(B) + bias[N] + bias2[N]) (+ C if accumulate), fp32 SIMT or tensor-core path.

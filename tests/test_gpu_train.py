@@ -308,3 +308,36 @@ def test_attn_large_batch_per_step_presplit_vs_oracle_fp64(dtype):
         assert abs(float(loss) - float(ref['loss'])) < tol * float(ref['loss'])
         _check_grads({k: q.grad for k, q in dec.named_parameters()}, ref['grads'], tol=tol)
         assert rel_err(step.dfeat, ref['dfeat']) < tol
+
+
+def test_nchw_handoff_matches_permute_view():
+    """the CNN output [B, D, h, w] goes into the step by ONE transposing pass (bit-exact with the
+    reference's permute(0, 2, 3, 1).view(B, -1, C), LSTMwAttentionModel.py:64-66) and the grid gradient comes back NCHW."""
+    from imagecaptioning_b200 import functional as F_
+    from imagecaptioning_b200.model import DecoderTrainStep
+    g = torch.Generator().manual_seed(3)
+    for (B, D, h, w) in [(3, 40, 7, 7), (2, 33, 5, 9), (4, 64, 1, 1)]:
+        x = torch.randn(B, D, h, w, generator=g).to(DEV)
+        want = x.permute(0, 2, 3, 1).reshape(B, -1, D)
+        assert torch.equal(F_.features_from_nchw(x), want)
+        d = torch.randn(B, h * w, D, generator=g).to(DEV)
+        back = F_.dfeat_to_nchw(d, (h, w))
+        assert torch.equal(back, d.view(B, h, w, D).permute(0, 3, 1, 2).contiguous())
+        acc = back.clone()
+        F_.dfeat_to_nchw(d, (h, w), out=acc, accumulate=True)
+        assert torch.equal(acc, 2 * back)
+    cfg = dict(V=60, E=16, D=32, H=32, T=6)
+    p = random_attn_params(cfg, seed=4, dtype=torch.float32)
+    feat, gt = synth_inputs(5, 12, cfg['D'], cfg['V'], cfg['T'], seed=2)
+    nchw = feat.view(5, 3, 4, cfg['D']).permute(0, 3, 1, 2).contiguous().to(DEV)       # what a CNN would hand over
+    dec_a, dec_b = build_decoder(cfg, p), build_decoder(cfg, p)
+    a = DecoderTrainStep(dec_a, need_dfeat=True)
+    la = a.forward_train(feat.to(DEV), gt.to(DEV))
+    b = DecoderTrainStep(dec_b, need_dfeat=True)
+    lb = b.forward_train_nchw(nchw, gt.to(DEV))
+    assert rel_err(lb, la) < 1e-6
+    for (k, qa), (_, qb) in zip(dec_a.named_parameters(), dec_b.named_parameters()):
+        assert rel_err(qb.grad, qa.grad) < 1e-5 or k == 'attention.v.bias', k
+    assert rel_err(b.dfeat_nchw(), a.dfeat.view(5, 3, 4, cfg['D']).permute(0, 3, 1, 2)) < 1e-5
+    ref = R.attn_train_step({k: v.double() for k, v in p.items()}, feat.double(), gt, cfg['V'], need_dfeat=True)
+    assert rel_err(b.dfeat_nchw(), ref['dfeat'].view(5, 3, 4, cfg['D']).permute(0, 3, 1, 2)) < TOL
