@@ -16,6 +16,7 @@
 //     publishes (max, sum, unnormalised context) [backward: partial sums that are LINEAR in the softmax-backward
 //     scalar], bumps the image's counter, and the CTA that arrives last finalises the image.  No CTA ever waits for
 //     another one.
+#include <stdio.h>
 #include <stdlib.h>
 
 #include <mutex>
@@ -44,6 +45,25 @@ constexpr int SA_THREADS = SA_CTHREADS + 32;        // + one producer warp
 constexpr int SA_MAX_NST = 16;
 constexpr int SA_NC = 2;                            // float4 column chunks per consumer thread (fwd): D <= 4*256*SA_NC
 
+// Fraction of the streamed Ws / feat lines loaded with an L2 evict_last policy (ALEXCAP_ATT_L2_FRAC, 0 = plain loads).
+float l2_fraction() {
+  static const float f = [] {
+    const char* v = getenv("ALEXCAP_ATT_L2_FRAC");
+    const float x = (v && *v) ? (float)atof(v) : 0.f;
+    if (x > 0.f) {        // evict_last lines live in the persisting set-aside of L2: size it (ALEXCAP_ATT_L2_MB, default = max)
+      int dev = 0, maxb = 0;
+      cudaGetDevice(&dev);
+      cudaDeviceGetAttribute(&maxb, cudaDevAttrMaxPersistingL2CacheSize, dev);
+      const char* mb = getenv("ALEXCAP_ATT_L2_MB");
+      size_t want = (mb && *mb) ? (size_t)atoll(mb) << 20 : (size_t)maxb;
+      if (want > (size_t)maxb) want = (size_t)maxb;
+      cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want);
+      fprintf(stderr, "[alexcap] persisting L2 set-aside %zu MB (max %d MB)\n", want >> 20, maxb >> 20);
+    }
+    return x;
+  }();
+  return f < 0.f ? 0.f : (f > 1.f ? 1.f : f);
+}
 int env_int(const char* name, int dflt) {
   const char* v = getenv(name);
   return (v && *v) ? atoi(v) : dflt;
@@ -152,6 +172,7 @@ struct Cursor {
 };
 struct Ring {
   float* base; uint64_t* full; uint64_t* empty; int NST, stage_floats;
+  uint64_t policy = 0; bool hinted = false;      // L2 eviction policy of the streamed rows (producer thread only)
   __device__ __forceinline__ float* stage(const Cursor& c) const { return base + (int64_t)c.s * stage_floats; }
   __device__ __forceinline__ void wait_full(const Cursor& c) const { pipe::mbar_wait(&full[c.s], c.ph); }
   __device__ __forceinline__ void release(const Cursor& c) const { pipe::mbar_arrive(&empty[c.s]); }
@@ -162,6 +183,10 @@ struct Ring {
   }
   __device__ __forceinline__ void copy(const Cursor& c, int dst_float_off, const float* src, uint32_t bytes) const {
     pipe::bulk_g2s(base + (int64_t)c.s * stage_floats + dst_float_off, src, bytes, &full[c.s]);
+  }
+  __device__ __forceinline__ void copy_rows(const Cursor& c, const float* src, uint32_t bytes) const {
+    if (hinted) pipe::bulk_g2s_hint(base + (int64_t)c.s * stage_floats, src, bytes, &full[c.s], policy);
+    else pipe::bulk_g2s(base + (int64_t)c.s * stage_floats, src, bytes, &full[c.s]);
   }
 };
 
@@ -196,7 +221,7 @@ __device__ __forceinline__ void produce(const Ring& ring, int64_t row0, int64_t 
         const int rows = min(R, nl - r0);
         const uint32_t bytes = (uint32_t)rows * (uint32_t)n * 4u;
         ring.begin(k, bytes);
-        ring.copy(k, 0, X + (src_row + r0) * n, bytes);
+        ring.copy_rows(k, X + (src_row + r0) * n, bytes);
       }
     }
     lo = hi;
@@ -215,6 +240,7 @@ struct SAttnFwdP {
   const float* wv; float* alpha; int64_t alpha_ld; float* ctx; float* beta; float* gctx; int64_t gctx_ld;
   float* scratch; unsigned* counters;
   int B, L, D, H, rpi, rp, R, NST, stage_floats, maxseg, seg_pad, slot_floats, dry;
+  float l2_frac;
 };
 
 // Scratch slot of (CTA c, its j-th segment): [0]=local max, [1]=local sum, [4 .. 4+D) unnormalised partial context.
@@ -253,6 +279,7 @@ __global__ void __launch_bounds__(SA_THREADS, 1) attn_fwd_stream_kernel(const SA
       hd.p[0] = a.q; hd.ld[0] = a.q_ld; hd.n[0] = a.H;
       hd.p[1] = a.bpre; hd.ld[1] = a.bpre_ld; hd.n[1] = D;
       hd.count = 2;
+      if (a.l2_frac > 0.f) { ring.policy = pipe::l2_policy_evict_last(a.l2_frac); ring.hinted = true; }
       produce(ring, row0, row1, L, R, a.rpi, hd, a.Ws, a.H, a.feat, D);
     }
     return;
@@ -499,7 +526,7 @@ cudaError_t attn_step_fwd_stream(cudaStream_t st, int B, int L, int D, int H, co
   ACK(get_scratch((size_t)g.nCTA * g.maxseg * slot_floats, (size_t)B, &scratch, &counters));
   SAttnFwdP a{Ws, feat, q, q_ld, bpre, bpre_ld, wv, alpha, alpha_ld, ctx, beta, gctx, gctx_ld, scratch, counters,
               B, L, D, H, rows_per_image < 1 ? 1 : rows_per_image, g.rp, g.R, g.NST, g.stage_floats, g.maxseg, seg_pad,
-              slot_floats, env_int("ALEXCAP_ATT_DRY", 0)};
+              slot_floats, env_int("ALEXCAP_ATT_DRY", 0), l2_fraction()};
   const size_t smem = (size_t)g.NST * g.stage_floats * 4 + fwd_fixed_smem(D, seg_pad, g.maxseg);
   const int nj = ceil_div(H, 128);
 #define LAUNCH_FWD(NJ)                                                                      \
@@ -539,6 +566,7 @@ struct SAttnBwdP {
   float* dq; int64_t dq_ld; float* dbpre; int64_t dbpre_ld; float* de; int64_t de_ld; float* dwv_part; float* dfeat;
   float* scratch; unsigned* counters;
   int B, L, D, H, rp, R, NST, stage_floats, maxseg, seg_pad, rp_pad, slot_floats;
+  float l2_frac;
 };
 
 // Scratch slot: [0] = partial dot, [1] = ref_s, [4 + i*H .. ) i = 0..3 : X1, X2, Y1, Y2.
@@ -584,6 +612,7 @@ __global__ void __launch_bounds__(SA_THREADS, 1) attn_bwd_stream_kernel(const SA
       hd.p[3] = a.ctx; hd.ld[3] = D; hd.n[3] = D;
       hd.p[4] = a.Ws; hd.ld[4] = (int64_t)L * H; hd.n[4] = H;          // Ws[b,0,:]: the reference row of pass D
       hd.count = 5;
+      if (a.l2_frac > 0.f) { ring.policy = pipe::l2_policy_evict_last(a.l2_frac); ring.hinted = true; }
       produce(ring, row0, row1, L, R, 1, hd, a.feat, D, a.Ws, H);     // feat pieces, then Ws pieces
     }
     return;
@@ -845,7 +874,7 @@ cudaError_t attn_step_bwd_stream(cudaStream_t st, int B, int L, int D, int H, co
   ACK(get_scratch((size_t)g.nCTA * g.maxseg * slot_floats, (size_t)B, &scratch, &counters));
   SAttnBwdP a{Ws, feat, q, q_ld, wv, alpha, alpha_ld, ctx, beta, dgctx, dgctx_ld, dalpha_ext, ext_ld, reg_r,
               dq, dq_ld, dbpre, dbpre_ld, de, de_ld, dwv_part, dfeat, scratch, counters,
-              B, L, D, H, g.rp, g.R, g.NST, g.stage_floats, g.maxseg, seg_pad, rp_pad, slot_floats};
+              B, L, D, H, g.rp, g.R, g.NST, g.stage_floats, g.maxseg, seg_pad, rp_pad, slot_floats, l2_fraction()};
   const size_t smem = (size_t)g.NST * g.stage_floats * 4 + bwd_fixed_smem(D, H, seg_pad, rp_pad, g.maxseg);
   if (g.rp % L == 0) {
     ACK(set_smem(attn_bwd_stream_kernel<true>, smem));

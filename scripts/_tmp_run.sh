@@ -1,1 +1,3 @@
-timeout 600 python -m pytest tests/test_gpu_train.py -m gpu -x -q -k "nchw" 2>&1 < /dev/null | grep -E "^E  |passed|failed" | cut -c1-250 | head
+for f in 0 0.45 0.6 0.75; do
+echo "frac=$f: $(ALEXCAP_ATT_L2_FRAC=$f timeout 200 python bench.py --steps 30 --warmup 5 --no-cpu-baseline 2>/dev/null < /dev/null | cut -c50-175)"
+done
