@@ -205,7 +205,16 @@ int attn_bwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
   if (!(part & 2)) return 0;
 
   // attention.W : dWs in one pass, then one K = B*L GEMM
-  API_CK(attn_dws(st, B, L, H, S, w.Ws, w.QB, HD, P->att_v_w, w.DE, w.dWs));
+  {
+    // the only readers of dWs are the dW_W (and dfeat) GEMMs: when they run on the pre-split path the kernel writes the
+    // bf16 copies itself and the fp32 matrix is never materialised
+    uint16_t *d_hi = nullptr, *d_lo = nullptr;
+    int64_t d_ld = 0;
+    SplitArena* arena = split_arena();
+    const bool direct = arena && gemm_engine() >= 2 && gemm_ps_wanted(H, D, B * L) && (!need_dfeat || gemm_ps_wanted(B * L, D, H)) &&
+                        split_arena_reserve(arena, w.dWs, B * L, H, H, gemm_engine() == 3, &d_hi, &d_lo, &d_ld);
+    API_CK(attn_dws(st, B, L, H, S, w.Ws, w.QB, HD, P->att_v_w, w.DE, direct ? nullptr : w.dWs, d_hi, d_lo, d_ld));
+  }
   API_CK(gemm_f32(st, true, false, H, D, B * L, 1.f, w.dWs, H, feat, D, G->att_W_w, D, nullptr, nullptr, false, ACT_NONE));
   if (need_dfeat)
     API_CK(gemm_f32(st, false, false, B * L, D, H, 1.f, w.dWs, H, P->att_W_w, D, dfeat, D, nullptr, nullptr, true, ACT_NONE));

@@ -24,7 +24,8 @@ __device__ __forceinline__ float4 exp2c4(const float4 x) {
 __global__ void __launch_bounds__(256) attn_dws_kernel(int L, int H, int S, int B, const float* __restrict__ Ws,
                                                        const float* __restrict__ q, int64_t q_ld,
                                                        const float* __restrict__ wv, const float* __restrict__ de,
-                                                       float* __restrict__ dWs) {
+                                                       float* __restrict__ dWs, uint16_t* __restrict__ d_hi,
+                                                       uint16_t* __restrict__ d_lo, int64_t d_ld) {
   const int b = blockIdx.y, l0 = blockIdx.x * DWS_ROWS, H4 = H >> 2;
   const float* deb = de + (int64_t)b * S * L;
   for (int c = threadIdx.x; c < H4; c += blockDim.x) {
@@ -53,19 +54,32 @@ __global__ void __launch_bounds__(256) attn_dws_kernel(int L, int H, int S, int 
 #pragma unroll
     for (int r = 0; r < DWS_ROWS; ++r) {
       const int l = l0 + r;
-      if (l < L)
-        reinterpret_cast<float4*>(dWs)[((int64_t)b * L + l) * H4 + c] =
-            make_float4(v.x * acc[r].x, v.y * acc[r].y, v.z * acc[r].z, v.w * acc[r].w);
+      if (l >= L) continue;
+      const float4 o = make_float4(v.x * acc[r].x, v.y * acc[r].y, v.z * acc[r].z, v.w * acc[r].w);
+      if (dWs) reinterpret_cast<float4*>(dWs)[((int64_t)b * L + l) * H4 + c] = o;
+      if (d_hi) {              // bf16 hi (+ lo residual) copies for the pre-split dW_W / dfeat GEMMs: no fp32 round trip
+        uint2 h;
+        asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(h.x) : "f"(o.y), "f"(o.x));
+        asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(h.y) : "f"(o.w), "f"(o.z));
+        const int64_t at = ((int64_t)b * L + l) * d_ld + 4 * c;
+        *reinterpret_cast<uint2*>(d_hi + at) = h;
+        if (d_lo) {
+          uint2 lo2;
+          asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(lo2.x) : "f"(o.y - __uint_as_float(h.x & 0xffff0000u)), "f"(o.x - __uint_as_float(h.x << 16)));
+          asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(lo2.y) : "f"(o.w - __uint_as_float(h.y & 0xffff0000u)), "f"(o.z - __uint_as_float(h.y << 16)));
+          *reinterpret_cast<uint2*>(d_lo + at) = lo2;
+        }
+      }
     }
   }
 }
 
 cudaError_t attn_dws(cudaStream_t st, int B, int L, int H, int S, const float* Ws, const float* q, int64_t q_ld,
-                     const float* wv, const float* de, float* dWs) {
-  if ((H & 3) || (q_ld & 3)) return cudaErrorInvalidValue;
+                     const float* wv, const float* de, float* dWs, uint16_t* d_hi, uint16_t* d_lo, int64_t d_ld) {
+  if ((H & 3) || (q_ld & 3) || (d_hi && (d_ld & 3))) return cudaErrorInvalidValue;
   dim3 grid(ceil_div(L, DWS_ROWS), B);
   const int threads = (H / 4 >= 256) ? 256 : ((H / 4 + 31) / 32) * 32;
-  ALEXCAP_NOTE_LAUNCH(); attn_dws_kernel<<<grid, threads, 0, st>>>(L, H, S, B, Ws, q, q_ld, wv, de, dWs);
+  ALEXCAP_NOTE_LAUNCH(); attn_dws_kernel<<<grid, threads, 0, st>>>(L, H, S, B, Ws, q, q_ld, wv, de, dWs, d_hi, d_lo, d_ld);
   return cudaGetLastError();
 }
 

@@ -26,15 +26,20 @@ __global__ void __launch_bounds__(CE_THREADS) ce_rows_kernel(const float* __rest
                                                              const int32_t* __restrict__ tgt, int C, int64_t ld,
                                                              float eps, int ignore_index,
                                                              const float* __restrict__ denom,
-                                                             float* __restrict__ row_loss, float* dlogits) {
+                                                             float* __restrict__ row_loss, float* dlogits,
+                                                             uint16_t* __restrict__ dl_hi, uint16_t* __restrict__ dl_lo,
+                                                             int64_t dl_ld) {
   __shared__ float scratch[40];
   const int row = blockIdx.x;
   const float* x = logits + (int64_t)row * ld;
   float* dx = dlogits ? dlogits + (int64_t)row * ld : nullptr;
   const int y = tgt[row];
+  uint32_t* hi2 = dl_hi ? reinterpret_cast<uint32_t*>(dl_hi + (int64_t)row * dl_ld) : nullptr;   // bf16 pairs (dl_ld even)
+  uint32_t* lo2 = dl_lo ? reinterpret_cast<uint32_t*>(dl_lo + (int64_t)row * dl_ld) : nullptr;
   if (y == ignore_index) {   // ignored row: no loss, zero gradient
     if (threadIdx.x == 0) row_loss[row] = 0.f;
     if (dx) for (int c = threadIdx.x; c < C; c += CE_THREADS) dx[c] = 0.f;
+    if (hi2) for (int c = threadIdx.x; 2 * c < C; c += CE_THREADS) { hi2[c] = 0u; if (lo2) lo2[c] = 0u; }
     return;
   }
   const float xy = x[y];   // read before any (possibly aliasing) gradient write
@@ -56,8 +61,26 @@ __global__ void __launch_bounds__(CE_THREADS) ce_rows_kernel(const float* __rest
     const float smooth = lse - sx / (float)C;
     row_loss[row] = ((1.f - eps) * nll + eps * smooth) * inv_d;
   }
-  if (dx) {
-    const float u = eps / (float)C;
+  const float u = eps / (float)C;
+  if (hi2) {                 // two columns per thread: packed bf16 pairs, 4-byte stores
+    for (int c = 2 * threadIdx.x; c < C; c += 2 * CE_THREADS) {
+      float g0 = expf(x[c] - lse) - u, g1 = (c + 1 < C) ? expf(x[c + 1] - lse) - u : 0.f;
+      if (c == y) g0 -= (1.f - eps);
+      if (c + 1 == y) g1 -= (1.f - eps);
+      g0 *= inv_d; g1 *= inv_d;
+      if (c + 1 >= C) g1 = 0.f;
+      uint32_t h;
+      asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(h) : "f"(g1), "f"(g0));
+      hi2[c >> 1] = h;
+      if (lo2) {
+        uint32_t l;
+        const float r0 = g0 - __uint_as_float(h << 16), r1 = g1 - __uint_as_float(h & 0xffff0000u);
+        asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(l) : "f"(r1), "f"(r0));
+        lo2[c >> 1] = l;
+      }
+      if (dx) { dx[c] = g0; if (c + 1 < C) dx[c + 1] = g1; }
+    }
+  } else if (dx) {
     for (int c = threadIdx.x; c < C; c += CE_THREADS) {
       float g = expf(x[c] - lse) - u;
       if (c == y) g -= (1.f - eps);
@@ -67,9 +90,12 @@ __global__ void __launch_bounds__(CE_THREADS) ce_rows_kernel(const float* __rest
 }
 
 cudaError_t ce_rows(cudaStream_t st, const float* logits, const int32_t* tgt, int N, int C, int64_t ld, float eps,
-                    int ignore_index, const float* denom, float* row_loss, float* dlogits) {
+                    int ignore_index, const float* denom, float* row_loss, float* dlogits, uint16_t* dl_hi, uint16_t* dl_lo,
+                    int64_t dl_ld) {
   if (N <= 0) return cudaSuccess;
-  ALEXCAP_NOTE_LAUNCH(); ce_rows_kernel<<<N, CE_THREADS, 0, st>>>(logits, tgt, C, ld, eps, ignore_index, denom, row_loss, dlogits);
+  if (dl_hi && (dl_ld & 1)) return cudaErrorInvalidValue;
+  ALEXCAP_NOTE_LAUNCH();
+  ce_rows_kernel<<<N, CE_THREADS, 0, st>>>(logits, tgt, C, ld, eps, ignore_index, denom, row_loss, dlogits, dl_hi, dl_lo, dl_ld);
   return cudaGetLastError();
 }
 

@@ -343,7 +343,7 @@ static cudaError_t get_split(cudaStream_t st, SplitArena* a, const float* X, int
   const size_t need = one * (with_lo ? 2 : 1);
   if (!a->base || a->used + need > a->bytes || a->n >= SplitArena::MAX_ENTRIES) return cudaErrorMemoryAllocation;
   SplitArena::Entry& e = a->e[a->n];
-  e.src = X; e.rows = rows; e.cols = cols; e.ld = ld; e.ldo = ldo;
+  e.src = X; e.rows = rows; e.cols = cols; e.ld = ld; e.ldo = ldo; e.produced = false;
   e.hi = reinterpret_cast<uint16_t*>(a->base + a->used);
   e.lo = with_lo ? reinterpret_cast<uint16_t*>(a->base + a->used + one) : nullptr;
   a->used += need;
@@ -370,6 +370,33 @@ SplitArena*& split_arena() {
 void split_arena_release(SplitArena* a, size_t mark) {
   while (a->n > 0 && a->e[a->n - 1].end > mark) a->n--;
   a->used = mark;
+}
+
+// Entry for a matrix whose PRODUCER writes the bf16 copies itself (CE kernel -> dlogits, attn_dws -> dWs): same key as the
+// fp32 matrix would have had, no split pass.  False when the arena cannot hold it (the producer then writes fp32 as before).
+bool split_arena_reserve(SplitArena* a, const float* key, int rows, int cols, int64_t ld, bool with_lo, uint16_t** hi,
+                         uint16_t** lo, int64_t* ldo_out) {
+  if (!a || !a->base || a->n >= SplitArena::MAX_ENTRIES) return false;
+  const int64_t ldo = ((int64_t)cols + 7) & ~int64_t(7);
+  const size_t one = (((size_t)rows * ldo * 2) + 1023) & ~size_t(1023);
+  const size_t need = one * (with_lo ? 2 : 1);
+  if (a->used + need > a->bytes) return false;
+  SplitArena::Entry& e = a->e[a->n];
+  e.src = key; e.rows = rows; e.cols = cols; e.ld = ld; e.ldo = ldo; e.produced = true;
+  e.hi = reinterpret_cast<uint16_t*>(a->base + a->used);
+  e.lo = with_lo ? reinterpret_cast<uint16_t*>(a->base + a->used + one) : nullptr;
+  a->used += need;
+  e.end = a->used;
+  a->n++;
+  *hi = e.hi; *lo = e.lo; *ldo_out = ldo;
+  return true;
+}
+
+bool split_arena_is_produced(const SplitArena* a, const float* p) {
+  if (!a) return false;
+  for (int i = 0; i < a->n; ++i)
+    if (a->e[i].src == p && a->e[i].produced) return true;
+  return false;
 }
 
 bool gemm_ps_wanted(int M, int N, int K) {

@@ -229,6 +229,8 @@ cudaError_t gemm_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, flo
   if (gemm_engine() >= 1 && gemm_tc_supported(M, N, K, A, lda, B, ldb, C))
     return gemm_tc_f32(st, ta, tb, M, N, K, alpha, A, lda, B, ldb, C, ldc, bias, bias2, accumulate, act, 0,
                        gemm_engine() == 2 ? 1 : gemm_engine() == 3 ? 2 : 0);
+  // an operand that exists only as producer-written bf16 copies cannot be read as fp32: loud, never silent garbage
+  if (split_arena_is_produced(split_arena(), A) || split_arena_is_produced(split_arena(), B)) return cudaErrorInvalidValue;
   return gemm_simt_f32(st, ta, tb, M, N, K, alpha, A, lda, B, ldb, C, ldc, bias, bias2, accumulate, act);
 }
 

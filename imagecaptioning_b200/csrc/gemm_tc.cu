@@ -377,6 +377,8 @@ cudaError_t gemm_tc_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, 
                                       mode == 2 ? 3 : 1, split_arena());
     if (e != cudaErrorMemoryAllocation) return e;       // arena full: convert in the kernel instead
   }
+  // an operand whose bf16 copies were written directly by its producer has no fp32 data to convert: fail loudly
+  if (split_arena_is_produced(split_arena(), A) || split_arena_is_produced(split_arena(), B)) return cudaErrorInvalidValue;
   const bool a_mn = ta;        // transa: A stored [K,M] -> M contiguous
   const bool b_mn = !tb;       // transb=0: B stored [K,N] -> N contiguous
   const int num_kb = ceil_div(K, BK);

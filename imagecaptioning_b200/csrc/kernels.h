@@ -24,13 +24,17 @@ cudaError_t gemm_tc_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, 
 // Returns cudaErrorMemoryAllocation when the arena cannot hold the copies (the caller falls back to gemm_tc_f32).
 struct SplitArena {
   static constexpr int MAX_ENTRIES = 256;
-  struct Entry { const float* src; int rows, cols; int64_t ld, ldo; uint16_t* hi; uint16_t* lo; size_t end; };
+  struct Entry { const float* src; int rows, cols; int64_t ld, ldo; uint16_t* hi; uint16_t* lo; size_t end; bool produced; };
   uint8_t* base = nullptr; size_t bytes = 0, used = 0;
   Entry e[MAX_ENTRIES]; int n = 0;
 };
 SplitArena*& split_arena();                       // the arena big GEMMs of the current call may use (nullptr: none)
 void split_arena_release(SplitArena* a, size_t mark);   // forget every copy made after `mark` (= a->used at that time)
 bool gemm_ps_wanted(int M, int N, int K);
+// true when `p` is the key of copies written directly by their producer: the fp32 matrix behind it does NOT hold the data
+bool split_arena_is_produced(const SplitArena* a, const float* p);
+bool split_arena_reserve(SplitArena* a, const float* key, int rows, int cols, int64_t ld, bool with_lo, uint16_t** hi,
+                         uint16_t** lo, int64_t* ldo_out);
 cudaError_t gemm_ps_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, float alpha,
                         const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
                         const float* bias, const float* bias2, bool accumulate, int act, int force_splits, int nprod,
@@ -69,7 +73,8 @@ cudaError_t attn_step_bwd_stream(cudaStream_t st, int B, int L, int D, int H, co
 // dWs[b,l,h] = wv[h] * sum_t de[b,t,l] * (1 - tanh^2(Ws[b,l,h] + q[t,b,h]));  q: [S][B] rows of stride q_ld,
 // de: [B][S][L].
 cudaError_t attn_dws(cudaStream_t st, int B, int L, int H, int S, const float* Ws, const float* q, int64_t q_ld,
-                     const float* wv, const float* de, float* dWs);
+                     const float* wv, const float* de, float* dWs, uint16_t* d_hi = nullptr, uint16_t* d_lo = nullptr,
+                     int64_t d_ld = 0);    // d_hi / d_lo: bf16 copies [B*L, d_ld] written as well as / instead of dWs (may be NULL)
 // resid = 1 - sum_t alpha[b,t,l]; r[b,l] = -2*w*resid/(B*L); loss_reg = w*mean(resid^2) -> *loss_reg
 cudaError_t attn_regulariser(cudaStream_t st, int B, int S, int L, float weight, const float* alphas, float* r,
                              float* loss_reg, float* scratch);
@@ -88,8 +93,13 @@ cudaError_t lstm_pointwise_bwd(cudaStream_t st, int B, int H, float* gates, int6
 // ---- loss (ce_loss.cu)
 cudaError_t count_valid(cudaStream_t st, const int32_t* tgt, int N, int ignore_index, float* n_valid_out);
 // per-row masked label-smoothed CE; denom (device float) = divisor; row_loss[N]; dlogits may alias logits.
+// out[n] (+)= sum_m (hi[m, n] + lo[m, n]) over bf16 pair copies (lo may be NULL)
+cudaError_t col_sum_bf16(cudaStream_t st, const uint16_t* hi, const uint16_t* lo, int M, int N, int64_t ld, float* out,
+                         bool accumulate, float* scratch);
 cudaError_t ce_rows(cudaStream_t st, const float* logits, const int32_t* tgt, int N, int C, int64_t ld, float eps,
-                    int ignore_index, const float* denom, float* row_loss, float* dlogits);
+                    int ignore_index, const float* denom, float* row_loss, float* dlogits,
+                    uint16_t* dl_hi = nullptr, uint16_t* dl_lo = nullptr, int64_t dl_ld = 0);
+// (dl_hi / dl_lo: the gradient is ALSO/INSTEAD written as bf16 hi (+ lo residual) copies [N, dl_ld] for the pre-split GEMMs)
 // out[0] = sum(x[0..n)) (deterministic single-block tree)
 cudaError_t reduce_sum(cudaStream_t st, const float* x, int n, float* out, float* scratch = nullptr);
 

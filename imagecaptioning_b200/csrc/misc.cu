@@ -131,6 +131,37 @@ cudaError_t col_sum(cudaStream_t st, const float* X, int M, int N, int64_t ld, f
   return cudaGetLastError();
 }
 
+// the same over bf16 (hi, lo) pair copies: thread = two adjacent columns (one 4-byte load per copy and row)
+__global__ void __launch_bounds__(256) col_sum_bf16_part_kernel(const uint16_t* __restrict__ hi, const uint16_t* __restrict__ lo,
+                                                                int M, int N, int64_t ld, float* __restrict__ part) {
+  const int n = 2 * (blockIdx.x * blockDim.x + threadIdx.x);
+  if (n >= N) return;
+  const int s = blockIdx.y;
+  const int rows_per = (M + CS_SPLIT - 1) / CS_SPLIT;
+  const int m0 = s * rows_per, m1 = min(M, m0 + rows_per);
+  float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
+  for (int m = m0; m < m1; ++m) {
+    const uint32_t h = __ldg(reinterpret_cast<const uint32_t*>(hi + (int64_t)m * ld + n));
+    a0 += __uint_as_float(h << 16); a1 += __uint_as_float(h & 0xffff0000u);
+    if (lo) {
+      const uint32_t l = __ldg(reinterpret_cast<const uint32_t*>(lo + (int64_t)m * ld + n));
+      b0 += __uint_as_float(l << 16); b1 += __uint_as_float(l & 0xffff0000u);
+    }
+  }
+  part[(int64_t)s * N + n] = a0 + b0;
+  if (n + 1 < N) part[(int64_t)s * N + n + 1] = a1 + b1;
+}
+cudaError_t col_sum_bf16(cudaStream_t st, const uint16_t* hi, const uint16_t* lo, int M, int N, int64_t ld, float* out,
+                         bool accumulate, float* scratch) {
+  if (N <= 0) return cudaSuccess;
+  if (ld & 1) return cudaErrorInvalidValue;
+  dim3 grid(ceil_div(ceil_div(N, 2), 256), CS_SPLIT);
+  ALEXCAP_NOTE_LAUNCH(); col_sum_bf16_part_kernel<<<grid, 256, 0, st>>>(hi, lo, M, N, ld, scratch);
+  ALEXCAP_LAUNCH_CHECK();
+  ALEXCAP_NOTE_LAUNCH(); col_sum_final_kernel<<<ceil_div(N, 256), 256, 0, st>>>(scratch, N, out, accumulate ? 1 : 0);
+  return cudaGetLastError();
+}
+
 __global__ void __launch_bounds__(256) tanh_bwd_kernel(int rows, int cols, const float* __restrict__ dy, int64_t dy_ld,
                                                        const float* __restrict__ t, int64_t t_ld, float* __restrict__ out,
                                                        int64_t out_ld) {
