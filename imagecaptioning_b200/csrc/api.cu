@@ -86,8 +86,8 @@ AttnWs attn_layout(const alexcap_dims* d, void* base, bool with_logits) {
   w.dwv_part = a.take<float>(B * H);
   w.dWs = a.take<float>(B * L * H);
   w.dEmbIn = a.take<float>(S * B * E);
-  w.dh0 = a.take<float>(B * H);
-  w.dc0 = a.take<float>(B * H);
+  w.dh0 = a.take<float>(2 * B * H);      // [B, 2H] = [dh0 | dc0]: one column-sum pass gives both init biases
+  w.dc0 = w.dh0 ? w.dh0 + H : nullptr;
   w.dm = a.take<float>(B * D);
   int64_t maxn = Vp;
   if (W5 > maxn) maxn = W5;
@@ -195,7 +195,9 @@ int attn_bwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
   API_CK(gemm_f32(st, true, false, 4 * H, E, SB, 1.f, w.DGQ, W5, w.EmbIn, E, G->lstm_w_ih, E + D, nullptr, nullptr, false, ACT_NONE));
   API_CK(gemm_f32(st, true, false, 4 * H, D, SB, 1.f, w.DGQ, W5, w.XH, DH, G->lstm_w_ih + E, E + D, nullptr, nullptr, false, ACT_NONE));
   API_CK(gemm_f32(st, true, false, 4 * H, H, SB, 1.f, w.DGQ, W5, w.XH + D, DH, G->lstm_w_hh, H, nullptr, nullptr, false, ACT_NONE));
-  API_CK(col_sum(st, w.DGQ, SB, 4 * H, W5, G->lstm_b_ih, false, w.cs_scratch));
+  // bias gradients = column sums of [dgates | dq | dbpre] (all final after the chain): lstm.bias_*, attention.U.bias, f_beta.bias
+  // in ONE pass over DGQ
+  API_CK(col_sum3(st, w.DGQ, SB, W5, G->lstm_b_ih, 4 * H, G->att_U_b, H, G->f_beta_b, D, w.cs_scratch));
   API_CK(cudaMemcpyAsync(G->lstm_b_hh, G->lstm_b_ih, sizeof(float) * 4 * H, cudaMemcpyDeviceToDevice, st));
   // embedding: d EmbIn = dgates_all W_ih[:, :E], scatter-add by input token (row 0 / pad included: no padding_idx)
   API_CK(gemm_f32(st, false, false, SB, E, 4 * H, 1.f, w.DGQ, W5, P->lstm_w_ih, E + D, w.dEmbIn, E, nullptr, nullptr, false, ACT_NONE));
@@ -221,24 +223,22 @@ int attn_bwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
   // attention.U, f_beta
   API_CK(gemm_f32(st, true, false, H, H, SB, 1.f, w.DGQ + 4 * H, W5, w.XH + D, DH, G->att_U_w, H, nullptr, nullptr, false, ACT_NONE));
   API_CK(gemm_f32(st, true, false, D, H, SB, 1.f, w.DGQ + 5 * H, W5, w.XH + D, DH, G->f_beta_w, H, nullptr, nullptr, false, ACT_NONE));
-  API_CK(col_sum(st, w.DGQ + 4 * H, SB, H, W5, G->att_U_b, false, w.cs_scratch));
   // d b_W = sum_{b,l} dWs = sum_{b,t,l} dz = sum_{b,t} dq = d b_U: the same number; taken from the dq path, whose sums are
   // formed without the cancellation that a column sum of dWs would re-introduce (see attention_stream.cu, pass D)
   API_CK(cudaMemcpyAsync(G->att_W_b, G->att_U_b, sizeof(float) * H, cudaMemcpyDeviceToDevice, st));
-  API_CK(col_sum(st, w.DGQ + 5 * H, SB, D, W5, G->f_beta_b, false, w.cs_scratch));
   // attention.v
   API_CK(col_sum(st, w.dwv_part, B, H, H, G->att_v_w, false, w.cs_scratch));
   API_CK(reduce_sum(st, w.DE, B * S * L, G->att_v_b, w.reg_scratch));
   // init_h / init_c (AttentionLanguageModule.py:116-125)
-  API_CK(tanh_bwd(st, B, H, w.dh_next, H, w.XH + D, DH, w.dh0, H));
-  API_CK(tanh_bwd(st, B, H, w.dc, H, w.Call, H, w.dc0, H));
-  API_CK(gemm_f32(st, true, false, H, D, B, 1.f, w.dh0, H, w.m, D, G->init_h_w, D, nullptr, nullptr, false, ACT_NONE));
-  API_CK(gemm_f32(st, true, false, H, D, B, 1.f, w.dc0, H, w.m, D, G->init_c_w, D, nullptr, nullptr, false, ACT_NONE));
-  API_CK(col_sum(st, w.dh0, B, H, H, G->init_h_b, false, w.cs_scratch));
-  API_CK(col_sum(st, w.dc0, B, H, H, G->init_c_b, false, w.cs_scratch));
+  const int64_t H2 = 2 * (int64_t)H;
+  API_CK(tanh_bwd(st, B, H, w.dh_next, H, w.XH + D, DH, w.dh0, H2));
+  API_CK(tanh_bwd(st, B, H, w.dc, H, w.Call, H, w.dc0, H2));
+  API_CK(gemm_f32(st, true, false, H, D, B, 1.f, w.dh0, H2, w.m, D, G->init_h_w, D, nullptr, nullptr, false, ACT_NONE));
+  API_CK(gemm_f32(st, true, false, H, D, B, 1.f, w.dc0, H2, w.m, D, G->init_c_w, D, nullptr, nullptr, false, ACT_NONE));
+  API_CK(col_sum3(st, w.dh0, B, H2, G->init_h_b, H, G->init_c_b, H, nullptr, 0, w.cs_scratch));
   if (need_dfeat) {
-    API_CK(gemm_f32(st, false, false, B, D, H, 1.f, w.dh0, H, P->init_h_w, D, w.dm, D, nullptr, nullptr, false, ACT_NONE));
-    API_CK(gemm_f32(st, false, false, B, D, H, 1.f, w.dc0, H, P->init_c_w, D, w.dm, D, nullptr, nullptr, true, ACT_NONE));
+    API_CK(gemm_f32(st, false, false, B, D, H, 1.f, w.dh0, H2, P->init_h_w, D, w.dm, D, nullptr, nullptr, false, ACT_NONE));
+    API_CK(gemm_f32(st, false, false, B, D, H, 1.f, w.dc0, H2, P->init_c_w, D, w.dm, D, nullptr, nullptr, true, ACT_NONE));
     API_CK(add_broadcast_L(st, B, L, D, w.dm, 1.f / (float)L, dfeat));
   }
   return 0;

@@ -93,6 +93,9 @@ cudaError_t lstm_pointwise_bwd(cudaStream_t st, int B, int H, float* gates, int6
 // ---- loss (ce_loss.cu)
 cudaError_t count_valid(cudaStream_t st, const int32_t* tgt, int N, int ignore_index, float* n_valid_out);
 // per-row masked label-smoothed CE; denom (device float) = divisor; row_loss[N]; dlogits may alias logits.
+// column sums of X[M, n0+n1+n2] written to three destinations by column range (n1 / n2 may be 0)
+cudaError_t col_sum3(cudaStream_t st, const float* X, int M, int64_t ld, float* o0, int n0, float* o1, int n1, float* o2, int n2,
+                     float* scratch);
 // out[n] (+)= sum_m (hi[m, n] + lo[m, n]) over bf16 pair copies (lo may be NULL)
 cudaError_t col_sum_bf16(cudaStream_t st, const uint16_t* hi, const uint16_t* lo, int M, int N, int64_t ld, float* out,
                          bool accumulate, float* scratch);

@@ -131,6 +131,28 @@ cudaError_t col_sum(cudaStream_t st, const float* X, int M, int N, int64_t ld, f
   return cudaGetLastError();
 }
 
+// column sums of ONE matrix whose column ranges [0,n0) [n0,n0+n1) [n0+n1,n0+n1+n2) are different bias gradients
+__global__ void __launch_bounds__(256) col_sum_final3_kernel(const float* __restrict__ part, int N, float* __restrict__ o0, int n0,
+                                                             float* __restrict__ o1, int n1, float* __restrict__ o2) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  float acc = 0.f;
+  for (int s = 0; s < CS_SPLIT; ++s) acc += part[(int64_t)s * N + n];
+  if (n < n0) o0[n] = acc;
+  else if (n < n0 + n1) o1[n - n0] = acc;
+  else o2[n - n0 - n1] = acc;
+}
+cudaError_t col_sum3(cudaStream_t st, const float* X, int M, int64_t ld, float* o0, int n0, float* o1, int n1, float* o2, int n2,
+                     float* scratch) {
+  const int N = n0 + n1 + n2;
+  if (N <= 0) return cudaSuccess;
+  dim3 grid(ceil_div(N, 256), CS_SPLIT);
+  ALEXCAP_NOTE_LAUNCH(); col_sum_part_kernel<<<grid, 256, 0, st>>>(X, M, N, ld, scratch);
+  ALEXCAP_LAUNCH_CHECK();
+  ALEXCAP_NOTE_LAUNCH(); col_sum_final3_kernel<<<ceil_div(N, 256), 256, 0, st>>>(scratch, N, o0, n0, o1, n1, o2);
+  return cudaGetLastError();
+}
+
 // the same over bf16 (hi, lo) pair copies: thread = two adjacent columns (one 4-byte load per copy and row)
 __global__ void __launch_bounds__(256) col_sum_bf16_part_kernel(const uint16_t* __restrict__ hi, const uint16_t* __restrict__ lo,
                                                                 int M, int N, int64_t ld, float* __restrict__ part) {

@@ -1,3 +1,2 @@
 timeout 900 python -m pytest tests/test_gpu_train.py tests/test_gpu_kernels.py -m gpu -x -q 2>&1 < /dev/null | tail -3
-timeout 300 python scripts/err_report.py 2>&1 < /dev/null | tail -21 | head -9
-python bench.py --steps 30 --warmup 5 --no-cpu-baseline > gpurun_out/r3i_bench.json 2> gpurun_out/r3i_bench.err < /dev/null; tail -3 gpurun_out/r3i_bench.err; cut -c50-200 gpurun_out/r3i_bench.json
+python bench.py --steps 30 --warmup 5 --no-cpu-baseline > gpurun_out/r3j_bench.json 2> gpurun_out/r3j_bench.err < /dev/null; tail -3 gpurun_out/r3j_bench.err; cut -c50-200 gpurun_out/r3j_bench.json

@@ -246,7 +246,10 @@ def test_three_phase_step_equals_fused(graph, need_dfeat):
         b.run_resident(phase=4)
         g1 = b.grad_groups()[1].clone()
         assert rel_err(g1, want[e[0]:e[1]]) < 1e-5                  # lstm.* and embedding final after phase 4
-        assert float(b.grad_groups()[2].abs().max()) == 0.0          # ... and nothing of the last group written yet
+        early = {'attention.U.bias', 'f_beta.bias'}                  # column sums of [dgates|dq|dbpre]: one pass in phase 4
+        for k, v in b.grads_by_name().items():                       # ... and nothing else of the last group written yet
+            if b._group(list(b.grads_by_name()).index(k)) == 2 and k not in early:
+                assert float(v.abs().max()) == 0.0, k
         b.run_resident(phase=8)
         assert rel_err(b._loss, want_loss) < 1e-6
         assert rel_err(b._flat_grads, want) < 1e-5
