@@ -120,12 +120,16 @@ int attn_fwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
   API_CK(gemm_f32(st, false, true, S * B, 4 * H, E, 1.f, w.EmbIn, E, P->lstm_w_ih, E + D, w.DGQ, W5, P->lstm_b_ih,
                   P->lstm_b_hh, false, ACT_NONE));
   // concatenated weights: Wcat = [W_ih[:,E:] | W_hh] (4H x (D+H));  Wub = [W_U ; W_beta] ((H+D) x H)
-  API_CK(copy_2d(st, 4 * H, D, P->lstm_w_ih + E, E + D, w.Wcat, DH));
-  API_CK(copy_2d(st, 4 * H, H, P->lstm_w_hh, H, w.Wcat + D, DH));
-  API_CK(cudaMemcpyAsync(w.Wub, P->att_U_w, sizeof(float) * H * H, cudaMemcpyDeviceToDevice, st));
-  API_CK(cudaMemcpyAsync(w.Wub + (int64_t)H * H, P->f_beta_w, sizeof(float) * D * H, cudaMemcpyDeviceToDevice, st));
-  API_CK(cudaMemcpyAsync(w.bub, P->att_U_b, sizeof(float) * H, cudaMemcpyDeviceToDevice, st));
-  API_CK(cudaMemcpyAsync(w.bub + H, P->f_beta_b, sizeof(float) * D, cudaMemcpyDeviceToDevice, st));
+  {
+    CopySegments cs;
+    cs.add(P->lstm_w_ih + E, E + D, w.Wcat, DH, 4 * H, D);
+    cs.add(P->lstm_w_hh, H, w.Wcat + D, DH, 4 * H, H);
+    cs.add(P->att_U_w, H, w.Wub, H, H, H);
+    cs.add(P->f_beta_w, H, w.Wub + (int64_t)H * H, H, D, H);
+    cs.add(P->att_U_b, H, w.bub, H, 1, H);
+    cs.add(P->f_beta_b, D, w.bub + H, D, 1, D);
+    API_CK(copy_segments(st, cs));
+  }
 
   // the per-step split-K GEMMs accumulate with red.add: their outputs are zeroed here, once, instead of by a memset
   // node in front of every GEMM (which would also cut the programmatic-dependent-launch chain of the time loop)
@@ -162,9 +166,13 @@ int attn_bwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
   const int SB = S * B;
   if (part & 1) {
   // Wback = [W_hh ; W_U ; W_beta]  ((4H + H + D) x H): dh_{t-1} = [dgates | dq | dbpre] Wback in one GEMM
-  API_CK(cudaMemcpyAsync(w.Wback, P->lstm_w_hh, sizeof(float) * 4 * H * H, cudaMemcpyDeviceToDevice, st));
-  API_CK(cudaMemcpyAsync(w.Wback + (int64_t)4 * H * H, P->att_U_w, sizeof(float) * H * H, cudaMemcpyDeviceToDevice, st));
-  API_CK(cudaMemcpyAsync(w.Wback + (int64_t)5 * H * H, P->f_beta_w, sizeof(float) * D * H, cudaMemcpyDeviceToDevice, st));
+  {
+    CopySegments cs;
+    cs.add(P->lstm_w_hh, H, w.Wback, H, 4 * H, H);
+    cs.add(P->att_U_w, H, w.Wback + (int64_t)4 * H * H, H, H, H);
+    cs.add(P->f_beta_w, H, w.Wback + (int64_t)5 * H * H, H, D, H);
+    API_CK(copy_segments(st, cs));
+  }
   API_CK(fill_f32(st, w.dc, (int64_t)B * H, 0.f));
   API_CK(fill_f32(st, w.dwv_part, (int64_t)B * H, 0.f));
   if (need_dfeat) API_CK(fill_f32(st, dfeat, (int64_t)B * L * D, 0.f));

@@ -124,6 +124,15 @@ cudaError_t tanh_bwd(cudaStream_t st, int rows, int cols, const float* dy, int64
                      float* out, int64_t out_ld);
 cudaError_t relu_bwd(cudaStream_t st, int64_t n, const float* dy, const float* pre, float* out);
 // dst[r, :cols] = src[r, :cols] with strides
+struct CopySegments {
+  static constexpr int MAX = 8;
+  const float* src[MAX]; float* dst[MAX]; int64_t src_ld[MAX], dst_ld[MAX]; int rows[MAX], cols[MAX]; int n = 0;
+  void add(const float* s, int64_t sld, float* d, int64_t dld, int r, int c) {
+    src[n] = s; dst[n] = d; src_ld[n] = sld; dst_ld[n] = dld; rows[n] = r; cols[n] = c; ++n;
+  }
+};
+// all segments in one launch; columns, pitches multiples of 4 floats, 16-byte aligned bases
+cudaError_t copy_segments(cudaStream_t st, const CopySegments& t);
 cudaError_t copy_2d(cudaStream_t st, int rows, int cols, const float* src, int64_t src_ld, float* dst, int64_t dst_ld);
 cudaError_t fill_f32(cudaStream_t st, float* p, int64_t n, float v);
 // dfeat[b,l,:] += dm[b,:] * scale

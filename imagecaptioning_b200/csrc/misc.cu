@@ -230,6 +230,35 @@ cudaError_t copy_2d(cudaStream_t st, int rows, int cols, const float* src, int64
   return cudaGetLastError();
 }
 
+// several strided 2-D copies in ONE launch (the per-step weight concatenations: 7 memcpy / copy nodes -> 1)
+__global__ void __launch_bounds__(256) copy_segments_kernel(const CopySegments t) {
+  const int sgm = blockIdx.y;
+  const float* __restrict__ src = t.src[sgm];
+  float* __restrict__ dst = t.dst[sgm];
+  const int64_t sld = t.src_ld[sgm], dld = t.dst_ld[sgm];
+  const int cols4 = t.cols[sgm] >> 2;
+  const int64_t n = (int64_t)t.rows[sgm] * cols4;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int r = (int)(i / cols4), c = (int)(i % cols4) * 4;
+    *reinterpret_cast<float4*>(dst + (int64_t)r * dld + c) = __ldg(reinterpret_cast<const float4*>(src + (int64_t)r * sld + c));
+  }
+}
+cudaError_t copy_segments(cudaStream_t st, const CopySegments& t) {
+  if (t.n <= 0) return cudaSuccess;
+  if (t.n > CopySegments::MAX) return cudaErrorInvalidValue;
+  int64_t most = 0;
+  for (int i = 0; i < t.n; ++i) {
+    if ((t.cols[i] & 3) || (t.src_ld[i] & 3) || (t.dst_ld[i] & 3) || !aligned16(t.src[i]) || !aligned16(t.dst[i])) return cudaErrorInvalidValue;
+    const int64_t n = (int64_t)t.rows[i] * (t.cols[i] >> 2);
+    if (n > most) most = n;
+  }
+  int bx = (int)((most + 255) / 256);
+  if (bx > 592) bx = 592;
+  if (bx < 1) bx = 1;
+  ALEXCAP_NOTE_LAUNCH(); copy_segments_kernel<<<dim3(bx, t.n), 256, 0, st>>>(t);
+  return cudaGetLastError();
+}
+
 __global__ void __launch_bounds__(256) fill_kernel(float* __restrict__ p, int64_t n, float v) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = v;
 }
