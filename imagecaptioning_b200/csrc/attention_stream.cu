@@ -683,13 +683,15 @@ __global__ void __launch_bounds__(SA_THREADS, 1) attn_bwd_stream_kernel(const SA
         const int i0 = r0 + rr, i1 = r0 + rr2;
         const float al0 = al_s[i0], al1 = has2 ? al_s[i1] : 0.f;
         float d0 = 0.f, d1 = 0.f;
+        pipe::f32x2 p0 = 0ull, p1 = 0ull;            // packed partial dot products (FFMA2)
 #pragma unroll 4
         for (int c = lane; c < D4; c += 32) {
           const float4 dc = reinterpret_cast<const float4*>(dctx_s)[c];
           const float4 x0 = st[rr * D4 + c];
           const float4 x1 = has2 ? st[rr2 * D4 + c] : x0;
-          d0 = fmaf(x0.x, dc.x, d0); d0 = fmaf(x0.y, dc.y, d0); d0 = fmaf(x0.z, dc.z, d0); d0 = fmaf(x0.w, dc.w, d0);
-          d1 = fmaf(x1.x, dc.x, d1); d1 = fmaf(x1.y, dc.y, d1); d1 = fmaf(x1.z, dc.z, d1); d1 = fmaf(x1.w, dc.w, d1);
+          const pipe::f32x2 dca = pipe::pk2(dc.x, dc.y), dcb = pipe::pk2(dc.z, dc.w);
+          p0 = pipe::fma2(pipe::pk2(x0.x, x0.y), dca, p0); p0 = pipe::fma2(pipe::pk2(x0.z, x0.w), dcb, p0);
+          p1 = pipe::fma2(pipe::pk2(x1.x, x1.y), dca, p1); p1 = pipe::fma2(pipe::pk2(x1.z, x1.w), dcb, p1);
           if (dfb) {
             float4 o = dfb[(int64_t)i0 * D4 + c];
             f4_fma(o, al0, dc);
@@ -701,6 +703,7 @@ __global__ void __launch_bounds__(SA_THREADS, 1) attn_bwd_stream_kernel(const SA
             }
           }
         }
+        { float u0, u1; pipe::upk2(p0, u0, u1); d0 = u0 + u1; pipe::upk2(p1, u0, u1); d1 = u0 + u1; }
         d0 = warp_sum(d0); d1 = warp_sum(d1);
         if (lane == 0) {
           if (a.ext) { d0 += __ldg(a.ext + (int64_t)b * a.ext_ld + l0 + i0); if (has2) d1 += __ldg(a.ext + (int64_t)b * a.ext_ld + l0 + i1); }
@@ -742,6 +745,12 @@ __global__ void __launch_bounds__(SA_THREADS, 1) attn_bwd_stream_kernel(const SA
       rc.z = tanh_r(fmaf(w0.z, TANH_C, qq.z)); rc.w = tanh_r(fmaf(w0.w, TANH_C, qq.w));
       tc = make_float4(fmaf(-2.f, rc.x, 1.f), fmaf(-2.f, rc.y, 1.f), fmaf(-2.f, rc.z, 1.f), fmaf(-2.f, rc.w, 1.f));
     }
+    // Packed fp32x2 arithmetic (FFMA2 / FADD2 / FMUL2): per element pair 6 packed instructions + 4 MUFU.  Accumulated per
+    // column: Y = sum ad*dr and Z = sum ad*dr^2 (and the alpha-weighted pair for split images); X = tc*Y - Z afterwards.
+    using pipe::f32x2; using pipe::pk2; using pipe::upk2; using pipe::fma2; using pipe::add2; using pipe::mul2;
+    const f32x2 c2 = pk2(TANH_C, TANH_C), one2 = pk2(1.f, 1.f);
+    const f32x2 qa = pk2(qq.x, qq.y), qb = pk2(qq.z, qq.w), nra = pk2(-rc.x, -rc.y), nrb = pk2(-rc.z, -rc.w);
+    f32x2 ya = 0ull, yb = 0ull, za = 0ull, zb = 0ull, y2a = 0ull, y2b = 0ull, z2a = 0ull, z2b = 0ull;   // +0.f pairs
     for (int r0 = 0; r0 < nl; r0 += R, k.next(ring.NST), kg = (kg + 1 == SA_NG) ? 0 : kg + 1) {
       if (kg != grp) continue;
       ring.wait_full(k);
@@ -751,22 +760,37 @@ __global__ void __launch_bounds__(SA_THREADS, 1) attn_bwd_stream_kernel(const SA
 #pragma unroll 2
         for (int rr = g; rr < rows; rr += G) {
           const float al = al_s[r0 + rr], ad = al * (da_s[r0 + rr] - ref);
+          const f32x2 ad2 = pk2(ad, ad);
           const float4 w = st[rr * H4 + f];
-          float dr, pu;
-#define SA_BWD_ELEM(X)                                                                          \
-  dr = tanh_r(fmaf(w.X, TANH_C, qq.X)) - rc.X; pu = dr * (tc.X - dr);                             \
-  x1.X = fmaf(ad, pu, x1.X); y1.X = fmaf(ad, dr, y1.X);                                           \
-  if (!ALLWHOLE) { x2.X = fmaf(al, pu, x2.X); y2.X = fmaf(al, dr, y2.X); }
-          SA_BWD_ELEM(x) SA_BWD_ELEM(y) SA_BWD_ELEM(z) SA_BWD_ELEM(w)
-#undef SA_BWD_ELEM
+          float e0, e1, e2, e3;
+          upk2(fma2(pk2(w.x, w.y), c2, qa), e0, e1);
+          upk2(fma2(pk2(w.z, w.w), c2, qb), e2, e3);
+          float d0, d1, d2, d3;
+          upk2(add2(pk2(ex2_ftz(e0), ex2_ftz(e1)), one2), d0, d1);
+          upk2(add2(pk2(ex2_ftz(e2), ex2_ftz(e3)), one2), d2, d3);
+          const f32x2 dra = add2(pk2(rcp_ftz(d0), rcp_ftz(d1)), nra), drb = add2(pk2(rcp_ftz(d2), rcp_ftz(d3)), nrb);
+          ya = fma2(ad2, dra, ya); yb = fma2(ad2, drb, yb);
+          za = fma2(mul2(ad2, dra), dra, za); zb = fma2(mul2(ad2, drb), drb, zb);
+          if (!ALLWHOLE) {
+            const f32x2 al2 = pk2(al, al);
+            y2a = fma2(al2, dra, y2a); y2b = fma2(al2, drb, y2b);
+            z2a = fma2(mul2(al2, dra), dra, z2a); z2b = fma2(mul2(al2, drb), drb, z2b);
+          }
         }
       }
       __syncwarp();
       if (lane == 0) ring.release(k);
     }
-    x1 = make_float4(4.f * x1.x, 4.f * x1.y, 4.f * x1.z, 4.f * x1.w); y1 = make_float4(-2.f * y1.x, -2.f * y1.y, -2.f * y1.z, -2.f * y1.w);
-    if (!ALLWHOLE) {
-      x2 = make_float4(4.f * x2.x, 4.f * x2.y, 4.f * x2.z, 4.f * x2.w); y2 = make_float4(-2.f * y2.x, -2.f * y2.y, -2.f * y2.z, -2.f * y2.w);
+    {
+      float4 Y, Z;
+      upk2(ya, Y.x, Y.y); upk2(yb, Y.z, Y.w); upk2(za, Z.x, Z.y); upk2(zb, Z.z, Z.w);
+      x1 = make_float4(4.f * fmaf(tc.x, Y.x, -Z.x), 4.f * fmaf(tc.y, Y.y, -Z.y), 4.f * fmaf(tc.z, Y.z, -Z.z), 4.f * fmaf(tc.w, Y.w, -Z.w));
+      y1 = make_float4(-2.f * Y.x, -2.f * Y.y, -2.f * Y.z, -2.f * Y.w);
+      if (!ALLWHOLE) {
+        upk2(y2a, Y.x, Y.y); upk2(y2b, Y.z, Y.w); upk2(z2a, Z.x, Z.y); upk2(z2b, Z.z, Z.w);
+        x2 = make_float4(4.f * fmaf(tc.x, Y.x, -Z.x), 4.f * fmaf(tc.y, Y.y, -Z.y), 4.f * fmaf(tc.z, Y.z, -Z.z), 4.f * fmaf(tc.w, Y.w, -Z.w));
+        y2 = make_float4(-2.f * Y.x, -2.f * Y.y, -2.f * Y.z, -2.f * Y.w);
+      }
     }
     // reduce over the consumer groups and the row sub-groups inside each
     red[tid] = x1; red[SA_CTHREADS + tid] = x2; red[2 * SA_CTHREADS + tid] = y1; red[3 * SA_CTHREADS + tid] = y2;
