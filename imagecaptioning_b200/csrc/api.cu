@@ -153,6 +153,28 @@ int attn_fwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
   return 0;
 }
 
+// A second stream + fork / join events per (thread, device) for the one place where two independent kernels of different
+// pipes are worth running side by side; inside a stream capture the event pair becomes a fork / join of the graph.
+struct SideStream { cudaStream_t s = nullptr; cudaEvent_t fork = nullptr, join = nullptr; int dev = -1; bool ok = false; };
+SideStream& side_stream() {
+  static thread_local SideStream ss;
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess) { ss.ok = false; return ss; }
+  if (ss.dev != dev) {
+    ss.ok = cudaStreamCreateWithFlags(&ss.s, cudaStreamNonBlocking) == cudaSuccess &&
+            cudaEventCreateWithFlags(&ss.fork, cudaEventDisableTiming) == cudaSuccess &&
+            cudaEventCreateWithFlags(&ss.join, cudaEventDisableTiming) == cudaSuccess;
+    ss.dev = dev;
+  }
+  return ss;
+}
+bool dws_overlap_enabled() {
+  // measured at cfg2: 2.08-2.17 ms/step with the fork (any CTA cap) vs 2.06 without -- the MUFU kernel slows the co-resident
+  // persistent GEMM CTAs more than it hides -- so the fork is OFF unless ALEXCAP_DWS_OVERLAP=1
+  static const bool on = [] { const char* v = getenv("ALEXCAP_DWS_OVERLAP"); return v && v[0] == '1'; }();
+  return on;
+}
+
 // ------------------------------------------------------------------------------------------ attention backward core
 // dHout [S*B,H] (time-major) = d loss / d (h_t before dropout is applied => masked inside if dropout is on).
 // part bit 1: the reverse-time chain, then lstm.* and embedding gradients (the largest tensors after deep_output);
@@ -199,6 +221,29 @@ int attn_bwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
     { WeightBScope wb; API_CK(gemm_f32(st, false, false, B, H, (int)W5, 1.f, g, W5, w.Wback, H, dhn, H, nullptr, nullptr, true, ACT_NONE)); }
   }
 
+  // dWs in one pass over Ws (MUFU-bound, 85 us at cfg2), FORKED onto a side stream: it only needs de / q, which are final
+  // here, and its only readers are the dW_W / dfeat GEMMs of part 2 -- so it runs concurrently with the tensor-pipe-bound
+  // lstm / embedding GEMMs below (different pipes, its CTAs need no shared memory and co-reside with the GEMM CTAs).
+  SideStream& side = side_stream();
+  const bool overlap = side.ok && dws_overlap_enabled();
+  cudaStream_t st_dws = overlap ? side.s : st;
+  if (overlap) {
+    API_CK(cudaEventRecord(side.fork, st));
+    API_CK(cudaStreamWaitEvent(side.s, side.fork, 0));
+  }
+  {
+    // when dW_W (and dfeat) run on the pre-split path the kernel writes the bf16 copies itself and the fp32 matrix is
+    // never materialised
+    uint16_t *d_hi = nullptr, *d_lo = nullptr;
+    int64_t d_ld = 0;
+    SplitArena* arena = split_arena();
+    const bool direct = arena && gemm_engine() >= 2 && gemm_ps_wanted(H, D, B * L) && (!need_dfeat || gemm_ps_wanted(B * L, D, H)) &&
+                        split_arena_reserve(arena, w.dWs, B * L, H, H, gemm_engine() == 3, &d_hi, &d_lo, &d_ld);
+    static const int per_sm = [] { const char* v = getenv("ALEXCAP_DWS_CTAS_PER_SM"); return v ? atoi(v) : 4; }();
+    API_CK(attn_dws(st_dws, B, L, H, S, w.Ws, w.QB, HD, P->att_v_w, w.DE, direct ? nullptr : w.dWs, d_hi, d_lo, d_ld,
+                    overlap ? 148 * per_sm : 0));
+  }
+  if (overlap) API_CK(cudaEventRecord(side.join, side.s));
   // lstm weights: dW = dgates_all^T [EmbIn | gctx | h_prev], K = S*B
   API_CK(gemm_f32(st, true, false, 4 * H, E, SB, 1.f, w.DGQ, W5, w.EmbIn, E, G->lstm_w_ih, E + D, nullptr, nullptr, false, ACT_NONE));
   API_CK(gemm_f32(st, true, false, 4 * H, D, SB, 1.f, w.DGQ, W5, w.XH, DH, G->lstm_w_ih + E, E + D, nullptr, nullptr, false, ACT_NONE));
@@ -211,20 +256,11 @@ int attn_bwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
   API_CK(gemm_f32(st, false, false, SB, E, 4 * H, 1.f, w.DGQ, W5, P->lstm_w_ih, E + D, w.dEmbIn, E, nullptr, nullptr, false, ACT_NONE));
   API_CK(fill_f32(st, G->emb_w, (int64_t)d->Vp * E, 0.f));
   API_CK(scatter_add_rows(st, w.dEmbIn, E, w.in_tm, SB, E, G->emb_w));
+  if (overlap) API_CK(cudaStreamWaitEvent(st, side.join, 0));     // join: dWs is complete for whatever follows on `st`
   }   // part & 1
   if (!(part & 2)) return 0;
 
-  // attention.W : dWs in one pass, then one K = B*L GEMM
-  {
-    // the only readers of dWs are the dW_W (and dfeat) GEMMs: when they run on the pre-split path the kernel writes the
-    // bf16 copies itself and the fp32 matrix is never materialised
-    uint16_t *d_hi = nullptr, *d_lo = nullptr;
-    int64_t d_ld = 0;
-    SplitArena* arena = split_arena();
-    const bool direct = arena && gemm_engine() >= 2 && gemm_ps_wanted(H, D, B * L) && (!need_dfeat || gemm_ps_wanted(B * L, D, H)) &&
-                        split_arena_reserve(arena, w.dWs, B * L, H, H, gemm_engine() == 3, &d_hi, &d_lo, &d_ld);
-    API_CK(attn_dws(st, B, L, H, S, w.Ws, w.QB, HD, P->att_v_w, w.DE, direct ? nullptr : w.dWs, d_hi, d_lo, d_ld));
-  }
+  // attention.W : dWs (made in part 1, concurrently with the lstm / embedding GEMMs), then one K = B*L GEMM
   API_CK(gemm_f32(st, true, false, H, D, B * L, 1.f, w.dWs, H, feat, D, G->att_W_w, D, nullptr, nullptr, false, ACT_NONE));
   if (need_dfeat)
     API_CK(gemm_f32(st, false, false, B * L, D, H, 1.f, w.dWs, H, P->att_W_w, D, dfeat, D, nullptr, nullptr, true, ACT_NONE));

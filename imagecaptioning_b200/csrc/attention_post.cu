@@ -26,7 +26,11 @@ __global__ void __launch_bounds__(256) attn_dws_kernel(int L, int H, int S, int 
                                                        const float* __restrict__ wv, const float* __restrict__ de,
                                                        float* __restrict__ dWs, uint16_t* __restrict__ d_hi,
                                                        uint16_t* __restrict__ d_lo, int64_t d_ld) {
-  const int b = blockIdx.y, l0 = blockIdx.x * DWS_ROWS, H4 = H >> 2;
+  const int H4 = H >> 2, gx = (L + DWS_ROWS - 1) / DWS_ROWS, ntiles = gx * B;
+  // grid-stride over (image, row group) tiles: the launcher may cap the grid so that the kernel leaves room on every SM for
+  // a concurrently running GEMM (see api.cu: dWs is forked next to the lstm dW GEMMs)
+  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+  const int b = tile / gx, l0 = (tile % gx) * DWS_ROWS;
   const float* deb = de + (int64_t)b * S * L;
   for (int c = threadIdx.x; c < H4; c += blockDim.x) {
     float4 ew[DWS_ROWS], acc[DWS_ROWS];
@@ -72,12 +76,14 @@ __global__ void __launch_bounds__(256) attn_dws_kernel(int L, int H, int S, int 
       }
     }
   }
+  }
 }
 
 cudaError_t attn_dws(cudaStream_t st, int B, int L, int H, int S, const float* Ws, const float* q, int64_t q_ld,
-                     const float* wv, const float* de, float* dWs, uint16_t* d_hi, uint16_t* d_lo, int64_t d_ld) {
+                     const float* wv, const float* de, float* dWs, uint16_t* d_hi, uint16_t* d_lo, int64_t d_ld, int max_ctas) {
   if ((H & 3) || (q_ld & 3) || (d_hi && (d_ld & 3))) return cudaErrorInvalidValue;
-  dim3 grid(ceil_div(L, DWS_ROWS), B);
+  int grid = ceil_div(L, DWS_ROWS) * B;
+  if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
   const int threads = (H / 4 >= 256) ? 256 : ((H / 4 + 31) / 32) * 32;
   ALEXCAP_NOTE_LAUNCH(); attn_dws_kernel<<<grid, threads, 0, st>>>(L, H, S, B, Ws, q, q_ld, wv, de, dWs, d_hi, d_lo, d_ld);
   return cudaGetLastError();

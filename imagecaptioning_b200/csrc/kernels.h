@@ -74,7 +74,8 @@ cudaError_t attn_step_bwd_stream(cudaStream_t st, int B, int L, int D, int H, co
 // de: [B][S][L].
 cudaError_t attn_dws(cudaStream_t st, int B, int L, int H, int S, const float* Ws, const float* q, int64_t q_ld,
                      const float* wv, const float* de, float* dWs, uint16_t* d_hi = nullptr, uint16_t* d_lo = nullptr,
-                     int64_t d_ld = 0);    // d_hi / d_lo: bf16 copies [B*L, d_ld] written as well as / instead of dWs (may be NULL)
+                     int64_t d_ld = 0, int max_ctas = 0);
+// d_hi / d_lo: bf16 copies [B*L, d_ld] written as well as / instead of dWs (may be NULL); max_ctas > 0 caps the grid
 // resid = 1 - sum_t alpha[b,t,l]; r[b,l] = -2*w*resid/(B*L); loss_reg = w*mean(resid^2) -> *loss_reg
 cudaError_t attn_regulariser(cudaStream_t st, int B, int S, int L, float weight, const float* alphas, float* r,
                              float* loss_reg, float* scratch);
