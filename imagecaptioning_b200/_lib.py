@@ -73,6 +73,8 @@ PROTOTYPES = {
     'alexcap_attn_decode_beam': (C.c_int, [_DP, _AP, _P, _I32, _P, _P, _P, _P, _P, _SZ, _P]),
     'alexcap_lstm_decode_workspace_bytes': (_SZ, [_DP]),
     'alexcap_lstm_decode_greedy': (C.c_int, [_DP, _LP, _P, _P, _P, _SZ, _P]),
+    'alexcap_lstm_decode_beam_workspace_bytes': (_SZ, [_DP, _I32]),
+    'alexcap_lstm_decode_beam': (C.c_int, [_DP, _LP, _P, _I32, _P, _P, _P, _P, _SZ, _P]),
     'alexcap_gemm_f32': (C.c_int, [_I32, _I32, _I32, _I32, _I32, _F, _P, _I64, _P, _I64, _P, _I64, _P, _P, _I32, _I32,
                                    _I32, _P]),
     'alexcap_attn_step_fwd': (C.c_int, [_I32, _I32, _I32, _I32, _P, _P, _P, _I64, _P, _I64, _P, _P, _I64, _P, _P, _P,

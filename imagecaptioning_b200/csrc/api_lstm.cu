@@ -7,6 +7,19 @@
 // recurrent step is one [B,H]x[H,4H] GEMM + one pointwise kernel.
 #include "api_util.h"
 
+namespace alexcap {
+// beam.cu
+cudaError_t beam_select(cudaStream_t st, int B, int K, int Vp, int S, int step, int end_tok, const float* logits, int64_t ldl,
+                        float* top, int32_t* kact, int32_t* words, int32_t* back, int32_t* rowrank, int32_t* src_row,
+                        int32_t* prev_word, int32_t* ncomp, float* comp_score, int32_t* comp_step, int32_t* comp_rank);
+cudaError_t beam_gather_state(cudaStream_t st, int B, int K, int H, const int32_t* src_row, const float* h_in, int64_t h_in_ld,
+                              const float* c_in, float* h_out, int64_t h_out_ld, float* c_out);
+cudaError_t beam_finalize(cudaStream_t st, int B, int K, int S, int L, const int32_t* words, const int32_t* back,
+                          const int32_t* rowrank, const int32_t* ncomp, const float* comp_score, const int32_t* comp_step,
+                          const int32_t* comp_rank, const float* alpha_steps, int64_t* ids, int32_t* lens, float* scores,
+                          float* alphas);
+}  // namespace alexcap
+
 using namespace alexcap;
 
 namespace {
@@ -322,6 +335,109 @@ int alexcap_lstm_decode_greedy(const alexcap_dims* d, const alexcap_lstm_params*
     API_CK(argmax_rows(st, logits, B, Vp, ldV, tok));
     API_CK(greedy_commit(st, B, S, 0, t, V + 2, tok, nullptr, ids, nullptr, done));
   }
+  return 0;
+}
+
+// ---- beam search for the plain LSTM: LanguageModel.caption (AlexCap/LanguageModule.py:152-198), batched over images ----
+struct LstmBeamWs {
+  float *seqA, *seqB, *Gimg, *Himg, *Cimg, *hst, *cst, *x, *g, *logits, *top, *comp_score;
+  int32_t *tok, *kact, *words, *back, *rowrank, *src_row, *ncomp, *comp_step, *comp_rank;
+  size_t bytes;
+};
+static LstmBeamWs lstm_beam_layout(const alexcap_dims* d, int K, void* base) {
+  LstmBeamWs w;
+  Bump a(base);
+  const int64_t B = d->B, L = d->L, D = d->D, H = d->H, E = d->E, nl = d->num_layers, R = B * K, S1 = d->S + 1;
+  const int64_t ldV = (d->Vp + 3) & ~int64_t(3);
+  w.seqA = a.take<float>(L * B * D);                 // raw features, time-major (the image pass runs on B rows)
+  w.seqB = a.take<float>(L * B * H);
+  w.Gimg = a.take<float>(L * B * 4 * H);
+  w.Himg = a.take<float>((L + 1) * B * H);
+  w.Cimg = a.take<float>((L + 1) * B * H);
+  w.hst = a.take<float>(nl * 2 * R * H);             // [layer][0 = current, 1 = after the step][R,H]
+  w.cst = a.take<float>(nl * 2 * R * H);
+  w.x = a.take<float>(R * E);
+  w.g = a.take<float>(R * 4 * H);
+  w.logits = a.take<float>(R * ldV);
+  w.top = a.take<float>(R);
+  w.comp_score = a.take<float>(R);
+  w.tok = a.take<int32_t>(R);
+  w.kact = a.take<int32_t>(B);
+  w.words = a.take<int32_t>(S1 * R);
+  w.back = a.take<int32_t>(S1 * R);
+  w.rowrank = a.take<int32_t>((S1 + 1) * R);
+  w.src_row = a.take<int32_t>(R);
+  w.ncomp = a.take<int32_t>(B);
+  w.comp_step = a.take<int32_t>(R);
+  w.comp_rank = a.take<int32_t>(R);
+  w.bytes = a.off + 256;
+  return w;
+}
+
+size_t alexcap_lstm_decode_beam_workspace_bytes(const alexcap_dims* d, int32_t beam) {
+  if (!d || d->num_layers < 1 || d->num_layers > ALEXCAP_MAX_LAYERS || beam < 1 || beam > 32) return 0;
+  return lstm_beam_layout(d, beam, nullptr).bytes;
+}
+
+int alexcap_lstm_decode_beam(const alexcap_dims* d, const alexcap_lstm_params* P, const float* feat, int32_t beam,
+                             int64_t* ids, int32_t* lens, float* scores, void* workspace, size_t workspace_bytes,
+                             void* stream) {
+  if (int rc = check_lstm_dims(d)) return rc;
+  if (beam < 1 || beam > 32) return fail(ALEXCAP_E_BADARG, "beam size must be in [1,32]");
+  if (d->D != d->E)   // :160 feeds img_features straight into nn.LSTM(input_size = embedding size)
+    return fail(ALEXCAP_E_BADARG, "LanguageModel.caption feeds the raw features to the LSTM: D must equal E");
+  ExactScope exact_scope;
+  if (int rc = check_lstm_args(d, P, feat, workspace, workspace_bytes, lstm_beam_layout(d, beam, nullptr).bytes)) return rc;
+  if (!ids || !lens || !scores) return fail(ALEXCAP_E_BADARG, "NULL ids / lens / scores");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int K = beam;
+  const int B = d->B, L = d->L, D = d->D, H = d->H, E = d->E, Vp = d->Vp, S1 = d->S + 1, nl = d->num_layers, V = Vp - 3;
+  const int R = B * K;
+  const int64_t ldV = (Vp + 3) & ~int64_t(3);
+  LstmBeamWs w = lstm_beam_layout(d, K, workspace);
+  // image pass (:160): all K rows of an image are identical -> run it on B rows, then replicate the final states
+  API_CK(permute_01(st, B, L, D, feat, w.seqA));
+  for (int l = 0; l < nl; ++l) {
+    const float* in = (l == 0) ? w.seqA : w.seqB;
+    if (int rc = run_layer_fwd(d, in, l == 0 ? D : H, P->w_ih[l], P->w_hh[l], P->b_ih[l], P->b_hh[l], w.Gimg, w.Himg, w.Cimg, L, st))
+      return rc;
+    float* h0 = w.hst + (int64_t)(l * 2) * R * H;
+    float* c0 = w.cst + (int64_t)(l * 2) * R * H;
+    for (int j = 0; j < K; ++j) {
+      API_CK(copy_2d(st, B, H, w.Himg + (int64_t)L * B * H, H, h0 + (int64_t)j * H, (int64_t)K * H));
+      API_CK(copy_2d(st, B, H, w.Cimg + (int64_t)L * B * H, H, c0 + (int64_t)j * H, (int64_t)K * H));
+    }
+    if (l + 1 < nl)
+      API_CK(cudaMemcpyAsync(w.seqB, w.Himg + (int64_t)B * H, sizeof(float) * L * B * H, cudaMemcpyDeviceToDevice, st));
+  }
+  API_CK(fill_i32(st, w.tok, R, V + 1));
+  API_CK(fill_i32(st, w.kact, B, K));
+  API_CK(fill_i32(st, w.ncomp, B, 0));
+  API_CK(fill_i32(st, w.rowrank, (int64_t)(S1 + 1) * R, 0));
+  API_CK(fill_f32(st, w.top, R, 0.f));
+  for (int s = 0; s < S1; ++s) {   // the reference's `step` is s+1; it stops after step seq_length+2 = S+1 (:190-192)
+    API_CK(gather_rows(st, P->emb_w, w.tok, R, E, w.x, E));
+    const float* in = w.x; int I = E;
+    for (int l = 0; l < nl; ++l) {
+      float* hc = w.hst + (int64_t)(l * 2) * R * H; float* hn = hc + (int64_t)R * H;
+      float* cc = w.cst + (int64_t)(l * 2) * R * H; float* cn = cc + (int64_t)R * H;
+      API_CK(gemm_f32(st, false, true, R, 4 * H, I, 1.f, in, I, P->w_ih[l], I, w.g, 4 * H, P->b_ih[l], P->b_hh[l], false, ACT_NONE));
+      API_CK(gemm_f32(st, false, true, R, 4 * H, H, 1.f, hc, H, P->w_hh[l], H, w.g, 4 * H, nullptr, nullptr, true, ACT_NONE));
+      API_CK(lstm_pointwise_fwd(st, R, H, w.g, 4 * H, cc, cn, hn, H, nullptr, 0));
+      in = hn; I = H;
+    }
+    // eval mode: rnn.drop is the identity
+    API_CK(gemm_f32(st, false, true, R, Vp, H, 1.f, in, H, P->out_w, H, w.logits, ldV, P->out_b, nullptr, false, ACT_NONE));
+    API_CK(beam_select(st, B, K, Vp, S1, s, V + 2, w.logits, ldV, w.top, w.kact, w.words + (int64_t)s * R,
+                       w.back + (int64_t)s * R, w.rowrank + (int64_t)(s + 1) * R, w.src_row, w.tok, w.ncomp, w.comp_score,
+                       w.comp_step, w.comp_rank));
+    for (int l = 0; l < nl; ++l) {   // surviving beams continue from their parent's state of every layer (:186)
+      float* hc = w.hst + (int64_t)(l * 2) * R * H; float* cc = w.cst + (int64_t)(l * 2) * R * H;
+      API_CK(beam_gather_state(st, B, K, H, w.src_row, hc + (int64_t)R * H, H, cc + (int64_t)R * H, hc, H, cc));
+    }
+  }
+  API_CK(beam_finalize(st, B, K, S1, 0, w.words, w.back, w.rowrank, w.ncomp, w.comp_score, w.comp_step, w.comp_rank, nullptr,
+                       ids, lens, scores, nullptr));
   return 0;
 }
 

@@ -294,6 +294,20 @@ def lstm_decode_greedy(dims, P: LstmParams, feat):
     return ids
 
 
+def lstm_decode_beam(dims, P: LstmParams, feat, beam):
+    """ids [B, S+1] (no leading START, END included, 0 after), lens [B] (0 = no beam completed), scores [B]."""
+    lib = ensure_device(feat.device)
+    _req(feat)
+    dev = feat.device
+    ids = torch.zeros(dims.B, dims.S + 1, dtype=torch.int64, device=dev)
+    lens = torch.zeros(dims.B, dtype=torch.int32, device=dev)
+    scores = torch.zeros(dims.B, dtype=torch.float32, device=dev)
+    ws = workspace(lib.alexcap_lstm_decode_beam_workspace_bytes(C.byref(dims), beam), dev)
+    check(lib.alexcap_lstm_decode_beam(C.byref(dims), C.byref(P), _ptr(feat), beam, _ptr(ids), _ptr(lens), _ptr(scores),
+                                       _ptr(ws), ws.numel(), _stream()), 'alexcap_lstm_decode_beam')
+    return ids, lens, scores
+
+
 # ------------------------------------------------------------------------------------------------ engine selection
 def set_gemm_engine(engine: int):
     """0 = fp32 CUDA-core tiles, 1 = tcgen05/TMEM/TMA 3xTF32 tiles (process-wide)."""

@@ -242,6 +242,21 @@ class DecoderTrainStep:
         preds = self.llm.forward(feat, gt_labels)
         return CustomCrossEntropyLoss()(preds, self.llm.get_target(gt_labels, make_target=True))
 
+    @torch.no_grad()
+    def forward_test(self, features):
+        """Decoder half of AlexCapModel.forward_test (LSTMwAttentionModel.py:76-87 -> (captions, alphas);
+        LSTMModel.py:76-86 -> captions): eval mode, decode branch of `llm.forward`, ids -> strings."""
+        self.llm.eval()
+        feat = _f32c(features)
+        dev = next(self.llm.parameters()).device
+        if feat.device != dev:
+            feat = feat.to(dev)
+        out = self.llm.forward(feat, feat.new())
+        if self.is_attn:
+            preds, alphas = out
+            return self.llm.decode_sequence(preds), alphas
+        return self.llm.decode_sequence(out)
+
     def _is_vocab(self, i):
         names = F_._lib.ATTN_STATE_NAMES if self.is_attn else self.llm.param_names()
         return names[i].startswith('deep_output.') or names[i].startswith('rnn.linear.')

@@ -343,11 +343,24 @@ class LanguageModel(nn.Module, _DecodeMixin):
         dims = self._dims(feat, train_dropout=False)
         return F_.lstm_decode_greedy(dims, self._struct([_f32c(t) for t in self.param_list()]), feat)
 
+    @torch.no_grad()
     def caption(self, img_features, beam_size):
-        """:152-198 -- beam search for the plain LSTM (feeds raw features to the LSTM, only valid when D == W).
-        Not on BASELINE.json's hot path and not yet built natively: fail loudly rather than fall back to torch."""
-        raise AlexcapError('LanguageModel.caption (beam search for the plain LSTM) is not implemented natively; '
-                           'use predict_caption (use_beam=False, the reference default)')
+        """:152-198 -- beam search for the plain LSTM.  The raw features go through the LSTM (no image_encoder, :160), so
+        image_vector_dim must equal embedding_size.  B=1: returns the sentence as a Python list of ids INCLUDING the
+        leading START, and raises ValueError when no beam completed, exactly like the reference.  B>1 (extension): returns
+        ids[B, S+1] in predict_caption's form (no START, 0 after END; rows whose beams never completed are all 0), which
+        is what decode_sequence takes for a 2-D tensor."""
+        feat = _f32c(img_features)
+        dims = self._dims(feat, train_dropout=False)
+        ids, lens, scores = F_.lstm_decode_beam(dims, self._struct([_f32c(t) for t in self.param_list()]), feat,
+                                                int(beam_size))
+        if feat.shape[0] == 1:
+            n = int(lens[0].item())
+            if n == 0:
+                raise ValueError('max() arg is an empty sequence')   # what the reference's max([]) raises (:194)
+            return [self.START_TOKEN] + ids[0, :n].tolist()
+        self.last_beam_lens, self.last_beam_scores = lens, scores
+        return ids
 
     def decode_sequence(self, seq):
         return self._decode_words(seq, start_as_sos=False)            # :52-97

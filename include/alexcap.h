@@ -199,6 +199,16 @@ ALEXCAP_API int alexcap_attn_decode_beam(const alexcap_dims* dims, const alexcap
 ALEXCAP_API size_t alexcap_lstm_decode_workspace_bytes(const alexcap_dims* dims);
 ALEXCAP_API int alexcap_lstm_decode_greedy(const alexcap_dims* dims, const alexcap_lstm_params* params, const float* feat,
                                int64_t* ids, void* workspace, size_t workspace_bytes, void* stream);
+/* LanguageModel.caption (LanguageModule.py:152-198) for B images at once, beam `beam` per image.  The RAW features are
+ * run through the LSTM (no image_encoder, :160): dims->D must equal dims->E (else ALEXCAP_E_BADARG).  Cumulative
+ * RAW-logit scores, step-1 top-k from beam row 0, finished beams shrink k, at most seq_length+2 = S+1 steps (:190-192),
+ * result = completed beam with the highest score.  ids [B,S+1] int64 (without the leading START the reference keeps,
+ * END included, 0 after), lens [B] int32 (0 = no beam completed: the reference's max([]) raises ValueError at :194),
+ * scores [B]. */
+ALEXCAP_API size_t alexcap_lstm_decode_beam_workspace_bytes(const alexcap_dims* dims, int32_t beam);
+ALEXCAP_API int alexcap_lstm_decode_beam(const alexcap_dims* dims, const alexcap_lstm_params* params, const float* feat,
+                             int32_t beam, int64_t* ids, int32_t* lens, float* scores, void* workspace,
+                             size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------ optimizer step ----------
  * Global-norm gradient clipping + Adam over ALL parameter tensors in three launches.  Replaces, with identical arithmetic,

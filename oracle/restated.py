@@ -474,3 +474,61 @@ def lstm_greedy(p: dict, feat: torch.Tensor, vocab_size: int, seq_length: int, n
             break
         ids[:, i] = tok
     return ids
+
+
+def lstm_beam(p: dict, feat1: torch.Tensor, vocab_size: int, seq_length: int, beam_size: int, num_layers: int = 1):
+    """LanguageModel.caption (LanguageModule.py:152-198) for ONE image feat1[1,L,D].
+    The RAW features go through the LSTM (no image_encoder, :160), so D must equal the embedding size; scores are
+    cumulative raw logits; step 1 takes top-k from row 0 (:167-168); finished beams shrink k; the loop runs while
+    `step <= seq_length+1` is true at the check AFTER a step, i.e. up to seq_length+2 steps (:190-192); result =
+    completed beam with the max score, first on ties (:194).  Raises ValueError when nothing completed.
+    Returns (ids list INCLUDING the leading START, as the reference does, score)."""
+    k = beam_size
+    Vp = vocab_size + 3
+    start, end = vocab_size + 1, vocab_size + 2
+    H = p['lstm.weight_hh_l0'].shape[1]
+    W = [[p[f'lstm.weight_ih_l{l}'], p[f'lstm.weight_hh_l{l}'], p[f'lstm.bias_ih_l{l}'], p[f'lstm.bias_hh_l{l}']]
+         for l in range(num_layers)]
+    x = feat1.expand(k, -1, -1)
+    z = torch.zeros(k, H, dtype=feat1.dtype)
+    states = []
+    for l in range(num_layers):                                                # :160
+        x, h, c, _ = _lstm_layer_fwd(x, z, z, *W[l])
+        states.append((h, c))
+    prev = torch.full((k,), start, dtype=torch.long)
+    sentences = prev.view(k, 1)
+    top = torch.zeros(k, 1, dtype=feat1.dtype)
+    done, done_scores = [], []
+    step = 1
+    while True:
+        x = p['lookup_table.weight'][prev].unsqueeze(1)                        # :163
+        for l in range(num_layers):
+            x, h, c, _ = _lstm_layer_fwd(x, states[l][0], states[l][1], *W[l])
+            states[l] = (h, c)
+        out = x[:, 0] @ p['rnn.linear.weight'].T + p['rnn.linear.bias']        # :165 (eval: dropout is the identity)
+        out = top.expand_as(out) + out                                         # :166
+        if step == 1:
+            top_s, top_w = out[0].topk(k, 0)                                   # :168-169
+        else:
+            top_s, top_w = out.reshape(-1).topk(k, 0)                          # :171
+        prev_idx = top_w // Vp
+        next_w = top_w % Vp
+        sentences = torch.cat([sentences[prev_idx], next_w.view(-1, 1)], dim=1)
+        inc = [i for i, w in enumerate(next_w.tolist()) if w != end]
+        comp = [i for i, w in enumerate(next_w.tolist()) if w == end]
+        for i in comp:
+            done.append(sentences[i].tolist()); done_scores.append(float(top_s[i]))
+        k -= len(comp)
+        if k == 0:
+            break
+        sentences = sentences[inc]
+        states = [(h[prev_idx[inc]], c[prev_idx[inc]]) for h, c in states]     # :186
+        top = top_s[inc].view(-1, 1)
+        prev = next_w[inc]
+        if step > seq_length + 1:                                              # :190-191
+            break
+        step += 1
+    if not done:
+        raise ValueError('no completed beam')
+    best = done_scores.index(max(done_scores))
+    return done[best], done_scores[best]

@@ -31,6 +31,9 @@ CASES = {
 }
 
 
+from tests.golden_consts import LSTM_BEAM_END_BIAS        # noqa: E402
+
+
 def dump(name, **arrs):
     np.savez_compressed(os.path.join(HERE, name + '.npz'), **{k: np.asarray(v) for k, v in arrs.items()})
 
@@ -100,11 +103,28 @@ def run_lstm(name, B, L, D, H, E, V, T, full, dtype):
         out['g:' + k] = v.grad.numpy()
     lm.eval()
     out['greedy_ids'] = lm.predict_caption(feat.detach()).numpy()
+    # beam decode (LanguageModule.py:152-198; END biased upward so beams complete; sentences keep their leading START)
+    lmb = LanguageModel(V, E, D, H, T, 1, {}, 0.0, 'cpu').eval()     # a copy: the arrays in `out` alias lm's parameters
+    lmb.load_state_dict(lm.state_dict())
+    with torch.no_grad():
+        lmb.rnn.linear.bias[V + 2] += LSTM_BEAM_END_BIAS
+        beams, flags = [], []
+        for b in range(B):
+            try:
+                row = [int(x) for x in lmb.caption(feat[b:b + 1].detach(), 3)]
+                flags.append(1)
+            except ValueError:
+                row = []; flags.append(0)
+            beams.append(row + [-1] * (T + 4 - len(row)))
+    out['beam3_ids'] = np.array(beams); out['beam3_ok'] = np.array(flags)
     dump(name, **out)
     print(name, 'loss', loss.item())
 
 
 if __name__ == '__main__':
+    only = sys.argv[1] if len(sys.argv) > 1 else ''          # e.g. `make_golden.py lstm` regenerates the lstm_* files only
     for name, cfg in CASES.items():
+        if not name.startswith(only):
+            continue
         (run_attn if name.startswith('attn') else run_lstm)(name + '_f64', *cfg, torch.float64)
     torch.set_default_dtype(torch.float32)

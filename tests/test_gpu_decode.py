@@ -77,6 +77,77 @@ def test_lstm_greedy_ids_exact_vs_golden(name):
     assert torch.equal(ids.cpu(), g['greedy_ids'].long())
 
 
+@pytest.mark.parametrize('name', golden_names('lstm_'))
+def test_lstm_beam_ids_exact_vs_golden(name):
+    """LanguageModel.caption (LanguageModule.py:152-198) against the fixtures recorded from the reference: one image per
+    call returns the reference's list (leading START kept) or raises its ValueError; the batched call agrees."""
+    from tests.golden_consts import LSTM_BEAM_END_BIAS
+    g = load_golden(name)
+    c = g['cfg']
+    p = {k: v.clone() for k, v in g['params'].items()}
+    p['rnn.linear.bias'][c['V'] + 2] += LSTM_BEAM_END_BIAS
+    lm = build_lstm(c, p).eval()
+    lm.idx_to_token = {str(i): f'w{i}' for i in range(1, c['V'] + 1)}
+    for b in range(c['B']):
+        f1 = g['feat'][b:b + 1].float().to(DEV)
+        ref = [x for x in g['beam3_ids'][b].tolist() if x >= 0]
+        if int(g['beam3_ok'][b]):
+            sent = lm.caption(f1, 3)
+            assert isinstance(sent, list) and sent == ref
+            lm.use_beam, lm.beam_size = True, 3                      # the forward() dispatch (LanguageModule.py:108-110)
+            assert lm(f1, torch.empty(0, device=DEV)) == ref
+            assert lm.decode_sequence(sent) == [' '.join(f'w{i}' for i in ref[1:-1])]
+        else:
+            with pytest.raises(ValueError):
+                lm.caption(f1, 3)
+    ids = lm.caption(g['feat'].float().to(DEV), 3)
+    assert ids.shape == (c['B'], c['T'] + 2)
+    for b in range(c['B']):
+        ref = [x for x in g['beam3_ids'][b].tolist() if x >= 0][1:]
+        n = int(lm.last_beam_lens[b])
+        assert ids.cpu()[b, :n].tolist() == (ref if int(g['beam3_ok'][b]) else []) and int(ids[b, n:].abs().sum()) == 0
+
+
+@pytest.mark.parametrize('num_layers', [1, 2])
+def test_lstm_beam_batched_vs_oracle(num_layers):
+    cfg = dict(B=10, L=3, D=24, H=40, E=24, V=80, T=10)
+    torch.manual_seed(17)
+    ref_lm = torch.nn.LSTM(cfg['E'], cfg['H'], num_layers)
+    p = {'lstm.' + k: v.detach().double() * 2.0 for k, v in ref_lm.state_dict().items()}
+    gen = torch.Generator().manual_seed(3)
+    p['image_encoder.encode.weight'] = torch.randn(cfg['E'], cfg['D'], generator=gen, dtype=torch.float64) * 0.2
+    p['image_encoder.encode.bias'] = torch.zeros(cfg['E'], dtype=torch.float64)
+    p['lookup_table.weight'] = torch.randn(cfg['V'] + 3, cfg['E'], generator=gen, dtype=torch.float64)
+    p['rnn.linear.weight'] = torch.randn(cfg['V'] + 3, cfg['H'], generator=gen, dtype=torch.float64) * 0.5
+    p['rnn.linear.bias'] = torch.zeros(cfg['V'] + 3, dtype=torch.float64)
+    p['rnn.linear.bias'][cfg['V'] + 2] += 1.0
+    feat, _ = synth_inputs(cfg['B'], cfg['L'], cfg['D'], cfg['V'], cfg['T'], seed=9, dtype=torch.float64)
+    lm = build_lstm(cfg, p, num_layers=num_layers).eval()
+    done = 0
+    for k in (1, 2, 3, 5):
+        ids = lm.caption(feat.float().to(DEV), k).cpu()
+        lens, scores = lm.last_beam_lens.cpu(), lm.last_beam_scores.cpu()
+        for b in range(cfg['B']):
+            try:
+                ref, score = R.lstm_beam(p, feat[b:b + 1], cfg['V'], cfg['T'], k, num_layers)
+            except ValueError:
+                ref, score = [cfg['V'] + 1], 0.0
+            assert ids[b, :int(lens[b])].tolist() == ref[1:], (k, b)
+            assert abs(float(scores[b]) - score) < 1e-3 * max(1.0, abs(score))
+            done += len(ref) > 1
+    assert done > 0
+
+
+def test_lstm_beam_needs_matching_dims():
+    """:160 feeds the raw features to nn.LSTM(input_size = embedding size): D != E cannot work and says so."""
+    from imagecaptioning_b200._lib import AlexcapError
+    from imagecaptioning_b200.modules import LanguageModel
+    torch.manual_seed(0)
+    lm = LanguageModel(20, 8, 16, 8, 4, 1, {}, 0.0, DEV).to(DEV).eval()
+    with pytest.raises(AlexcapError, match='D must equal E'):
+        lm.caption(torch.randn(2, 1, 16, device=DEV), 3)
+
+
 def test_decode_sequence_strings():
     cfg = dict(B=1, L=2, D=8, H=8, E=8, V=5, T=4)
     dec = build_decoder(cfg, random_attn_params(cfg))

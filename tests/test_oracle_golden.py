@@ -71,6 +71,24 @@ def test_lstm_greedy_matches_reference_golden(name):
     assert torch.equal(ids, g['greedy_ids'].long())
 
 
+@pytest.mark.parametrize('name', golden_names('lstm_'))
+def test_lstm_beam_matches_reference_golden(name):
+    """LanguageModel.caption (LanguageModule.py:152-198), beam 3, END biased as in tests/golden/make_golden.py."""
+    from tests.golden_consts import LSTM_BEAM_END_BIAS
+    g = load_golden(name)
+    c = g['cfg']
+    p = {k: v.clone() for k, v in g['params'].items()}
+    p['rnn.linear.bias'][c['V'] + 2] += LSTM_BEAM_END_BIAS
+    for b in range(c['B']):
+        if int(g['beam3_ok'][b]):
+            ids, _ = R.lstm_beam(p, g['feat'][b:b + 1], c['V'], c['T'], 3)
+            assert ids == [x for x in g['beam3_ids'][b].tolist() if x >= 0]
+            assert ids[0] == c['V'] + 1 and ids[-1] == c['V'] + 2
+        else:
+            with pytest.raises(ValueError):
+                R.lstm_beam(p, g['feat'][b:b + 1], c['V'], c['T'], 3)
+
+
 def test_ce_matches_torch_functional():
     torch.manual_seed(0)
     x = torch.randn(37, 53, dtype=torch.float64)

@@ -61,3 +61,34 @@ def test_ports_are_bit_identical_to_reference(reference_modules):
     pg = dict(lport.named_parameters())
     for k, a in lm.named_parameters():
         assert torch.equal(a.grad, pg[k].grad), k
+
+
+@pytest.mark.parametrize('num_layers', [1, 2])
+def test_lstm_beam_restated_vs_live_reference(reference_modules, num_layers):
+    """oracle lstm_beam == LanguageModel.caption run live (LanguageModule.py:152-198): sentence lists (START included)
+    and the ValueError when no beam completes, beam sizes 1..5, one and two LSTM layers."""
+    torch.set_default_dtype(torch.float64)
+    try:
+        seen = {True: 0, False: 0}
+        for (V, E, D, H, T, L), bias in (((50, 32, 32, 24, 5, 1), 0.35), ((37, 20, 20, 12, 6, 5), 0.55)):
+            torch.manual_seed(123)
+            lm = reference_modules['LanguageModel'](V, E, D, H, T, num_layers, {}, 0.0, 'cpu').eval()
+            with torch.no_grad():
+                lm.rnn.linear.bias[V + 2] += bias
+            p = {k: v.detach().clone() for k, v in lm.state_dict().items()}
+            feat, _ = synth_inputs(5, L, D, V, T, seed=5, dtype=torch.float64)
+            for b in range(5):
+                for k in (1, 2, 3, 5):
+                    try:
+                        ref = lm.caption(feat[b:b + 1], k)
+                    except ValueError:
+                        ref = None
+                    try:
+                        mine, _ = R.lstm_beam(p, feat[b:b + 1], V, T, k, num_layers)
+                    except ValueError:
+                        mine = None
+                    assert ref == mine, (V, b, k)
+                    seen[ref is not None] += 1
+        assert seen[True] > 0
+    finally:
+        torch.set_default_dtype(torch.float32)
