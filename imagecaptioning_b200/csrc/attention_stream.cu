@@ -68,10 +68,11 @@ int env_int(const char* name, int dflt) {
   const char* v = getenv(name);
   return (v && *v) ? atoi(v) : dflt;
 }
-struct Tune { int cps, rows, nst; };
+struct Tune { int cps, rows, nst, piece_kb; };
 // Debug/tuning knobs (read once): CTAs per SM, rows per piece, ring depth.
 const Tune& tune_override() {
-  static Tune t = {env_int("ALEXCAP_ATT_CPS", 0), env_int("ALEXCAP_ATT_ROWS", 0), env_int("ALEXCAP_ATT_NST", 0)};
+  static Tune t = {env_int("ALEXCAP_ATT_CPS", 0), env_int("ALEXCAP_ATT_ROWS", 0), env_int("ALEXCAP_ATT_NST", 0),
+                   env_int("ALEXCAP_ATT_PIECE_KB", 0)};
   return t;
 }
 
@@ -107,7 +108,8 @@ Geometry pick_geometry(int B, int L, int D, int H, size_t fixed_smem_bytes, int 
   g.maxseg = (g.rp + L - 1) / L + 1;
   const int row = (H > D ? H : D);
   int R = tune_override().rows > 0 ? tune_override().rows : 2 * SA_GWARPS;
-  while (R > 1 && (size_t)R * row * 4 > 32 * 1024) --R;            // pieces of at most 32 KB
+  const size_t piece_cap = (size_t)(tune_override().piece_kb > 0 ? tune_override().piece_kb : 32) * 1024;
+  while (R > 1 && (size_t)R * row * 4 > piece_cap) --R;            // pieces of at most 32 KB
   if (R > g.seg_rows) R = g.seg_rows;
   g.R = R;
   g.stage_floats = R * row;

@@ -117,28 +117,19 @@ __device__ __forceinline__ void store_chunk(const uint32_t* v, float* tile, cons
       if (p.bias) bsum += __ldg(p.bias + n);
       if (p.bias2) bsum += __ldg(p.bias2 + n);
     }
-    if (atomic) {
 #pragma unroll 4
-      for (int r = 0; r < 32; ++r) {
-        const int m = mrow0 + r;
-        if (m >= p.M) break;
-        atomicAdd(p.C + (int64_t)m * p.ldc + n, fmaf(p.alpha, tile[r * 33 + lane], bsum));   // C zeroed / accumulated onto
-      }
-    } else {
-      float old[32];
-      if (p.accumulate) {            // all loads first: a load placed after a store to C could not be hoisted above it
-#pragma unroll
-        for (int r = 0; r < 32; ++r) old[r] = (mrow0 + r < p.M) ? p.C[(int64_t)(mrow0 + r) * p.ldc + n] : 0.f;
-      }
-#pragma unroll
-      for (int r = 0; r < 32; ++r) {
-        const int m = mrow0 + r;
-        if (m >= p.M) break;
-        float x = fmaf(p.alpha, tile[r * 33 + lane], bsum);
-        if (p.accumulate) x += old[r];
+    for (int r = 0; r < 32; ++r) {
+      const int m = mrow0 + r;
+      if (m >= p.M) break;
+      float x = fmaf(p.alpha, tile[r * 33 + lane], bsum);
+      float* cp = p.C + (int64_t)m * p.ldc + n;
+      if (atomic) {
+        atomicAdd(cp, x);            // C was zeroed (or holds the value to accumulate onto) by the launcher
+      } else {
+        if (p.accumulate) x += *cp;
         if (p.act == ACT_TANH) x = tanhf(x);
         else if (p.act == ACT_RELU) x = fmaxf(x, 0.f);
-        p.C[(int64_t)m * p.ldc + n] = x;
+        *cp = x;
       }
     }
   }
@@ -273,10 +264,11 @@ gemm_ps_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
     const int half = ew >> 2;                     // which half of the tile's columns
     constexpr int CPW = BN / 64;                  // 32-column chunks per warp
     float* tile = epi + ew * (32 * 33);
-    // accumulate without an activation also goes through red.add (fire-and-forget, one writer per element: the same
-    // single fp32 add as `x += *cp`): the load->add->store form serialises 64 dependent global loads per warp, which
-    // cost ~40 us per launch on the M = 512 per-step GEMMs of cfg3 (profiles/r1k_gemm_step.txt)
-    const bool atomic = p.splits > 1 || (p.accumulate && p.act == ACT_NONE);
+    // accumulate without an activation onto a SMALL output (the per-step GEMMs: one wave of CTAs) also goes through
+    // red.add (fire-and-forget, one writer per element: the same single fp32 add as `x += *cp`): the load->add->store
+    // form serialises 64 dependent global loads per warp, ~40 us per launch on the M = 512 per-step GEMMs of cfg3
+    // (profiles/r1k_gemm_step.txt).  Large outputs keep load->add->store: many tiles per CTA hide that latency.
+    const bool atomic = p.splits > 1 || (p.accumulate && p.act == ACT_NONE && (int64_t)p.M * p.N <= (int64_t)(4 << 20));
     int li = 0;
     for (int w = blockIdx.x; w < p.n_items; w += gridDim.x, ++li) {
       const Item it = decode_item<BN>(p, w);

@@ -273,7 +273,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     float* tile = reinterpret_cast<float*>(smem) + warp * (32 * 33);   // stage memory is idle now (all MMAs retired)
     const bool first_split = (blockIdx.z == 0);
     // accumulate without an activation: red.add instead of load->add->store (see gemm_ps.cu: serialised dependent loads)
-    const bool atomic = gridDim.z > 1 || (p.accumulate && p.act == ACT_NONE);
+    const bool atomic = gridDim.z > 1 || (p.accumulate && p.act == ACT_NONE && (int64_t)p.M * p.N <= (int64_t)(4 << 20));
 #pragma unroll 1
     const int q4 = warp & 3;                       // TMEM lane quarter this warp may read (warp id mod 4)
     for (int cc = (warp >> 2); cc < BN / 32; cc += CONV_WARPS / 4) {
@@ -299,27 +299,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (p.bias2) bsum += __ldg(p.bias2 + n);
       }
       if (n < p.N) {
-        const int mr0 = m0 + q4 * 32;
-        if (atomic) {
 #pragma unroll 4
-          for (int r = 0; r < 32; ++r) {
-            if (mr0 + r >= p.M) break;
-            atomicAdd(p.C + (int64_t)(mr0 + r) * p.ldc + n, fmaf(p.alpha, tile[r * 33 + lane], bsum));   // C zeroed / accumulated onto
-          }
-        } else {
-          float old[32];
-          if (p.accumulate) {      // all loads first: a load placed after a store to C could not be hoisted above it
-#pragma unroll
-            for (int r = 0; r < 32; ++r) old[r] = (mr0 + r < p.M) ? p.C[(int64_t)(mr0 + r) * p.ldc + n] : 0.f;
-          }
-#pragma unroll
-          for (int r = 0; r < 32; ++r) {
-            if (mr0 + r >= p.M) break;
-            float x = fmaf(p.alpha, tile[r * 33 + lane], bsum);
-            if (p.accumulate) x += old[r];
+        for (int r = 0; r < 32; ++r) {
+          const int m = m0 + q4 * 32 + r;
+          if (m >= p.M) break;
+          float x = fmaf(p.alpha, tile[r * 33 + lane], bsum);
+          float* cp = p.C + (int64_t)m * p.ldc + n;
+          if (atomic) {
+            atomicAdd(cp, x);      // C was zeroed (or holds the value to accumulate onto) by the launcher
+          } else {
+            if (p.accumulate) x += *cp;
             if (p.act == ACT_TANH) x = tanhf(x);
             else if (p.act == ACT_RELU) x = fmaxf(x, 0.f);
-            p.C[(int64_t)(mr0 + r) * p.ldc + n] = x;
+            *cp = x;
           }
         }
       }
