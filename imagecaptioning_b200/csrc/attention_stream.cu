@@ -88,7 +88,7 @@ int sm_count() {
 }
 
 struct Geometry {
-  int nCTA, rp, R, NST, stage_floats, maxseg, seg_rows;   // rp: rows per CTA; seg_rows: longest segment
+  int nCTA, rp, RH, RD, NST, stage_floats, maxseg, seg_rows;   // rp: rows per CTA; RH / RD: rows per piece of Ws / feat rows
 };
 
 Geometry pick_geometry(int B, int L, int D, int H, size_t fixed_smem_bytes, int header_floats) {
@@ -106,13 +106,16 @@ Geometry pick_geometry(int B, int L, int D, int H, size_t fixed_smem_bytes, int 
   g.nCTA = (int)((total + g.rp - 1) / g.rp);
   g.seg_rows = g.rp < L ? g.rp : L;
   g.maxseg = (g.rp + L - 1) / L + 1;
-  const int row = (H > D ? H : D);
-  int R = tune_override().rows > 0 ? tune_override().rows : 2 * SA_GWARPS;
-  const size_t piece_cap = (size_t)(tune_override().piece_kb > 0 ? tune_override().piece_kb : 32) * 1024;
-  while (R > 1 && (size_t)R * row * 4 > piece_cap) --R;            // pieces of at most 32 KB
-  if (R > g.seg_rows) R = g.seg_rows;
-  g.R = R;
-  g.stage_floats = R * row;
+  // Rows per piece, chosen per row width so that BOTH passes fill a stage: with H != D (cfg3: H = 1024, D = 2048) one
+  // common row count left the narrow pass with half-empty stages and half of its warp-per-row consumers idle.
+  const size_t piece_cap = (size_t)(tune_override().piece_kb > 0 ? tune_override().piece_kb : 40) * 1024;
+  auto rows_for = [&](int n) {
+    int r = tune_override().rows > 0 ? tune_override().rows : 2 * SA_GWARPS;
+    while (r > 1 && (size_t)r * n * 4 > piece_cap) --r;            // pieces of at most 40 KB (16 rows of <= 2.5 KB: 32 KB at cfg2)
+    return r > g.seg_rows ? g.seg_rows : r;
+  };
+  g.RH = rows_for(H); g.RD = rows_for(D);
+  g.stage_floats = g.RH * H > g.RD * D ? g.RH * H : g.RD * D;
   if (g.stage_floats < header_floats) g.stage_floats = header_floats;
   const size_t budget = (cps == 1 ? 216 : 100) * 1024;
   int nst = tune_override().nst > 0 ? tune_override().nst
@@ -195,8 +198,8 @@ struct Ring {
 // Small per-image vectors that open every segment (the "header piece"): up to 4 rows copied back to back.
 struct Header { const float* p[5]; int64_t ld[5]; int n[5]; int count; };
 
-// Producer: for every image segment of this CTA's row range stream [header] [X0 rows] [X1 rows] (R-row pieces).
-__device__ __forceinline__ void produce(const Ring& ring, int64_t row0, int64_t row1, int L, int R, int rpi,
+// Producer: for every image segment of this CTA's row range stream [header] [X0 rows] [X1 rows] (R0- / R1-row pieces).
+__device__ __forceinline__ void produce(const Ring& ring, int64_t row0, int64_t row1, int L, int R0, int R1, int rpi,
                                         const Header& hd, const float* X0, int n0, const float* X1, int n1) {
   Cursor k{0, 0u};
   for (int64_t lo = row0; lo < row1;) {
@@ -219,6 +222,7 @@ __device__ __forceinline__ void produce(const Ring& ring, int64_t row0, int64_t 
     for (int pass = 0; pass < 2; ++pass) {
       const float* X = pass ? X1 : X0;
       const int n = pass ? n1 : n0;
+      const int R = pass ? R1 : R0;
       for (int r0 = 0; r0 < nl; r0 += R, k.next(ring.NST)) {
         const int rows = min(R, nl - r0);
         const uint32_t bytes = (uint32_t)rows * (uint32_t)n * 4u;
@@ -241,7 +245,7 @@ struct SAttnFwdP {
   const float* Ws; const float* feat; const float* q; int64_t q_ld; const float* bpre; int64_t bpre_ld;
   const float* wv; float* alpha; int64_t alpha_ld; float* ctx; float* beta; float* gctx; int64_t gctx_ld;
   float* scratch; unsigned* counters;
-  int B, L, D, H, rpi, rp, R, NST, stage_floats, maxseg, seg_pad, slot_floats, dry;
+  int B, L, D, H, rpi, rp, RH, RD, NST, stage_floats, maxseg, seg_pad, slot_floats, dry;
   float l2_frac;
 };
 
@@ -250,7 +254,7 @@ struct SAttnFwdP {
 template <int NJ, bool FULL>
 __global__ void __launch_bounds__(SA_THREADS, 1) attn_fwd_stream_kernel(const SAttnFwdP a) {
   extern __shared__ __align__(128) float sm[];
-  const int L = a.L, D = a.D, H4 = a.H >> 2, D4 = D >> 2, R = a.R;
+  const int L = a.L, D = a.D, H4 = a.H >> 2, D4 = D >> 2, RH = a.RH, RD = a.RD;
   Ring ring;
   ring.base = sm; ring.NST = a.NST; ring.stage_floats = a.stage_floats;
   ring.full = reinterpret_cast<uint64_t*>(sm + (int64_t)a.NST * a.stage_floats);
@@ -282,7 +286,7 @@ __global__ void __launch_bounds__(SA_THREADS, 1) attn_fwd_stream_kernel(const SA
       hd.p[1] = a.bpre; hd.ld[1] = a.bpre_ld; hd.n[1] = D;
       hd.count = 2;
       if (a.l2_frac > 0.f) { ring.policy = pipe::l2_policy_evict_last(a.l2_frac); ring.hinted = true; }
-      produce(ring, row0, row1, L, R, a.rpi, hd, a.Ws, a.H, a.feat, D);
+      produce(ring, row0, row1, L, RH, RD, a.rpi, hd, a.Ws, a.H, a.feat, D);
     }
     return;
   }
@@ -333,12 +337,12 @@ __global__ void __launch_bounds__(SA_THREADS, 1) attn_fwd_stream_kernel(const SA
     k.next(ring.NST); kg = (kg + 1 == SA_NG) ? 0 : kg + 1;
 
     // ---- pass 1: e[l] = w_v . tanh(Ws[b,l,:] + q[b,:])     two rows per warp in flight   (AttentionLanguageModule.py:18-19)
-    for (int r0 = 0; r0 < nl; r0 += R, k.next(ring.NST), kg = (kg + 1 == SA_NG) ? 0 : kg + 1) {
+    for (int r0 = 0; r0 < nl; r0 += RH, k.next(ring.NST), kg = (kg + 1 == SA_NG) ? 0 : kg + 1) {
       if (kg != grp) continue;
       ring.wait_full(k);
       if (a.dry) { __syncwarp(); if (lane == 0) ring.release(k); continue; }   // debug: pure streaming rate
       const float4* st = reinterpret_cast<const float4*>(ring.stage(k));
-      const int rows = min(R, nl - r0);
+      const int rows = min(RH, nl - r0);
       for (int rr = gw; rr < rows; rr += 2 * SA_GWARPS) {
         const int rr2 = rr + SA_GWARPS;
         const bool has2 = rr2 < rows;
@@ -388,12 +392,12 @@ __global__ void __launch_bounds__(SA_THREADS, 1) attn_fwd_stream_kernel(const SA
     float4 acc[SA_NC];
 #pragma unroll
     for (int ci = 0; ci < SA_NC; ++ci) acc[ci] = f4_zero();
-    for (int r0 = 0; r0 < nl; r0 += R, k.next(ring.NST), kg = (kg + 1 == SA_NG) ? 0 : kg + 1) {
+    for (int r0 = 0; r0 < nl; r0 += RD, k.next(ring.NST), kg = (kg + 1 == SA_NG) ? 0 : kg + 1) {
       if (kg != grp) continue;
       ring.wait_full(k);
       if (a.dry) { __syncwarp(); if (lane == 0) ring.release(k); continue; }   // debug: pure streaming rate
       const float4* st = reinterpret_cast<const float4*>(ring.stage(k));
-      const int rows = min(R, nl - r0);
+      const int rows = min(RD, nl - r0);
       if (g < G) {
 #pragma unroll 4
         for (int rr = g; rr < rows; rr += G) {
@@ -527,7 +531,7 @@ cudaError_t attn_step_fwd_stream(cudaStream_t st, int B, int L, int D, int H, co
   unsigned* counters = nullptr;
   ACK(get_scratch((size_t)g.nCTA * g.maxseg * slot_floats, (size_t)B, &scratch, &counters));
   SAttnFwdP a{Ws, feat, q, q_ld, bpre, bpre_ld, wv, alpha, alpha_ld, ctx, beta, gctx, gctx_ld, scratch, counters,
-              B, L, D, H, rows_per_image < 1 ? 1 : rows_per_image, g.rp, g.R, g.NST, g.stage_floats, g.maxseg, seg_pad,
+              B, L, D, H, rows_per_image < 1 ? 1 : rows_per_image, g.rp, g.RH, g.RD, g.NST, g.stage_floats, g.maxseg, seg_pad,
               slot_floats, env_int("ALEXCAP_ATT_DRY", 0), l2_fraction()};
   const size_t smem = (size_t)g.NST * g.stage_floats * 4 + fwd_fixed_smem(D, seg_pad, g.maxseg);
   const int nj = ceil_div(H, 128);
@@ -567,7 +571,7 @@ struct SAttnBwdP {
   const float* ext; int64_t ext_ld; const float* reg_r;
   float* dq; int64_t dq_ld; float* dbpre; int64_t dbpre_ld; float* de; int64_t de_ld; float* dwv_part; float* dfeat;
   float* scratch; unsigned* counters;
-  int B, L, D, H, rp, R, NST, stage_floats, maxseg, seg_pad, rp_pad, slot_floats;
+  int B, L, D, H, rp, RH, RD, NST, stage_floats, maxseg, seg_pad, rp_pad, slot_floats;
   float l2_frac;
 };
 
@@ -576,7 +580,7 @@ struct SAttnBwdP {
 template <bool ALLWHOLE>
 __global__ void __launch_bounds__(SA_THREADS, 1) attn_bwd_stream_kernel(const SAttnBwdP a) {
   extern __shared__ __align__(128) float sm[];
-  const int L = a.L, D = a.D, H = a.H, H4 = H >> 2, D4 = D >> 2, R = a.R;
+  const int L = a.L, D = a.D, H = a.H, H4 = H >> 2, D4 = D >> 2, RH = a.RH, RD = a.RD;
   Ring ring;
   ring.base = sm; ring.NST = a.NST; ring.stage_floats = a.stage_floats;
   ring.full = reinterpret_cast<uint64_t*>(sm + (int64_t)a.NST * a.stage_floats);
@@ -615,7 +619,7 @@ __global__ void __launch_bounds__(SA_THREADS, 1) attn_bwd_stream_kernel(const SA
       hd.p[4] = a.Ws; hd.ld[4] = (int64_t)L * H; hd.n[4] = H;          // Ws[b,0,:]: the reference row of pass D
       hd.count = 5;
       if (a.l2_frac > 0.f) { ring.policy = pipe::l2_policy_evict_last(a.l2_frac); ring.hinted = true; }
-      produce(ring, row0, row1, L, R, 1, hd, a.feat, D, a.Ws, H);     // feat pieces, then Ws pieces
+      produce(ring, row0, row1, L, RD, RH, 1, hd, a.feat, D, a.Ws, H);     // feat pieces, then Ws pieces
     }
     return;
   }
@@ -674,11 +678,11 @@ __global__ void __launch_bounds__(SA_THREADS, 1) attn_bwd_stream_kernel(const SA
     // ---- B: d alpha[l] = dctx . feat[b,l,:] (+ upstream terms);  dfeat += alpha[l] * dctx        (:21)
     // (Centring the dot product -- dctx . (feat_l - ctx) -- was measured: no accuracy gain, 40 % more pass-B instructions.)
     float4* dfb = a.dfeat ? reinterpret_cast<float4*>(a.dfeat) + ((int64_t)b * L + l0) * D4 : nullptr;
-    for (int r0 = 0; r0 < nl; r0 += R, k.next(ring.NST), kg = (kg + 1 == SA_NG) ? 0 : kg + 1) {
+    for (int r0 = 0; r0 < nl; r0 += RD, k.next(ring.NST), kg = (kg + 1 == SA_NG) ? 0 : kg + 1) {
       if (kg != grp) continue;
       ring.wait_full(k);
       const float4* st = reinterpret_cast<const float4*>(ring.stage(k));
-      const int rows = min(R, nl - r0);
+      const int rows = min(RD, nl - r0);
       for (int rr = gw; rr < rows; rr += 2 * SA_GWARPS) {
         const int rr2 = rr + SA_GWARPS;
         const bool has2 = rr2 < rows;
@@ -753,11 +757,11 @@ __global__ void __launch_bounds__(SA_THREADS, 1) attn_bwd_stream_kernel(const SA
     const f32x2 c2 = pk2(TANH_C, TANH_C), one2 = pk2(1.f, 1.f);
     const f32x2 qa = pk2(qq.x, qq.y), qb = pk2(qq.z, qq.w), nra = pk2(-rc.x, -rc.y), nrb = pk2(-rc.z, -rc.w);
     f32x2 ya = 0ull, yb = 0ull, za = 0ull, zb = 0ull, y2a = 0ull, y2b = 0ull, z2a = 0ull, z2b = 0ull;   // +0.f pairs
-    for (int r0 = 0; r0 < nl; r0 += R, k.next(ring.NST), kg = (kg + 1 == SA_NG) ? 0 : kg + 1) {
+    for (int r0 = 0; r0 < nl; r0 += RH, k.next(ring.NST), kg = (kg + 1 == SA_NG) ? 0 : kg + 1) {
       if (kg != grp) continue;
       ring.wait_full(k);
       const float4* st = reinterpret_cast<const float4*>(ring.stage(k));
-      const int rows = min(R, nl - r0);
+      const int rows = min(RH, nl - r0);
       if (g < G && f < H4) {
 #pragma unroll 2
         for (int rr = g; rr < rows; rr += G) {
@@ -900,7 +904,7 @@ cudaError_t attn_step_bwd_stream(cudaStream_t st, int B, int L, int D, int H, co
   ACK(get_scratch((size_t)g.nCTA * g.maxseg * slot_floats, (size_t)B, &scratch, &counters));
   SAttnBwdP a{Ws, feat, q, q_ld, wv, alpha, alpha_ld, ctx, beta, dgctx, dgctx_ld, dalpha_ext, ext_ld, reg_r,
               dq, dq_ld, dbpre, dbpre_ld, de, de_ld, dwv_part, dfeat, scratch, counters,
-              B, L, D, H, g.rp, g.R, g.NST, g.stage_floats, g.maxseg, seg_pad, rp_pad, slot_floats, l2_fraction()};
+              B, L, D, H, g.rp, g.RH, g.RD, g.NST, g.stage_floats, g.maxseg, seg_pad, rp_pad, slot_floats, l2_fraction()};
   const size_t smem = (size_t)g.NST * g.stage_floats * 4 + bwd_fixed_smem(D, H, seg_pad, rp_pad, g.maxseg);
   if (g.rp % L == 0) {
     ACK(set_smem(attn_bwd_stream_kernel<true>, smem));
