@@ -335,7 +335,13 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device('cuda', local)
     dist = None
+    saved_stdout = None
     if world > 1:
+        # NCCL writes a "NCCL version ..." banner to stdout (fd 1) when the communicator is created: route fd 1 to stderr
+        # until the result is ready, so that stdout carries exactly the one JSON line
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
         import torch.distributed as dist
         dist.init_process_group('nccl', device_id=dev)
     from imagecaptioning_b200 import _lib
@@ -430,6 +436,9 @@ def main():
         if world == 1 and not args.no_cpu_baseline:
             cb, _, _ = time_cpu_port(c, steps=3, warmup=1, budget_s=25.0)
             line['cpu_baseline'] = cb
+        if saved_stdout is not None:
+            sys.stdout.flush()
+            os.dup2(saved_stdout, 1)
         print(json.dumps(line), flush=True)
     if dist:
         # the whole-step CUDA graphs hold captured NCCL kernels: drop them before the communicator, and do not let the
