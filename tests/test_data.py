@@ -161,3 +161,30 @@ def test_write_dataset_and_reference_checkpoint(tmp_path, reference_modules):
     for k, v in ref.state_dict().items():
         assert torch.equal(ours.state_dict()[k], v), k
     assert load_reference_checkpoint(Decoder(50, 16, 32, 24, 5, {}, 0.0, 'cpu'), ref.state_dict()) == []
+
+
+def test_h5lite_round_trip_property(tmp_path):
+    """Random shapes / dtypes / byte orders / chunkings: write() -> File() returns the same arrays (hypothesis)."""
+    from hypothesis import given, settings, strategies as st
+    from hypothesis.extra import numpy as hnp
+
+    dtypes = st.sampled_from(['<i1', '<u1', '<i2', '>i2', '<u2', '<i4', '>i4', '<u4', '<i8', '>u8', '<f4', '>f4', '<f8'])
+    arrays = dtypes.flatmap(lambda dt: hnp.arrays(dt, hnp.array_shapes(min_dims=1, max_dims=4, min_side=0, max_side=6),
+                                                  elements=None if 'f' not in dt else st.floats(-1e6, 1e6, width=32)))
+    counter = [0]
+
+    @settings(max_examples=40, deadline=None)
+    @given(st.lists(arrays, min_size=0, max_size=9), st.sampled_from([0, 512]), st.booleans(), st.booleans())
+    def run(arrs, userblock, deflate, shuffle):
+        counter[0] += 1
+        ds = {f'd{i}_{"x" * (i % 4)}': a for i, a in enumerate(arrs)}
+        chunks = {k: tuple(max(1, s // 2 + 1) for s in a.shape) for k, a in ds.items() if a.size and a.ndim <= 3}
+        p = str(tmp_path / f'p{counter[0]}.h5')
+        h5lite.write(p, ds, userblock=userblock, chunks=chunks, deflate=deflate, shuffle=shuffle)
+        with h5lite.File(p) as f:
+            assert f.keys() == sorted(ds)
+            for k, v in ds.items():
+                a = f[k][:]
+                assert a.shape == v.shape and a.dtype == v.dtype and np.array_equal(a, v), k
+
+    run()
