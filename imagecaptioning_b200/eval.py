@@ -20,6 +20,7 @@ def eval_split(kwargs, scorer=None, verbose=False):
     split = getopt(kwargs, 'split', 'val')
     max_images = getopt(kwargs, 'max_images', -1)
     batch_size = getopt(kwargs, 'val_batch_size', 1)
+    skip_incomplete = bool(kwargs.get('skip_incomplete', False))    # extension: record '' instead of aborting
     assert split == 'val' or split == 'test', 'split must be "val" or "test"'
     split = {'val': 1, 'test': 2}[split]
     model.llm.eval()
@@ -36,7 +37,7 @@ def eval_split(kwargs, scorer=None, verbose=False):
             captions = model.forward_test(features)
             captions = captions[0] if isinstance(captions, tuple) else captions
         except ValueError:                     # the reference's caption() when no beam completed (B = 1 only): it aborts
-            if getopt(kwargs, 'skip_incomplete', False) is False:
+            if not skip_incomplete:
                 raise
             captions, no_beam = [''] * features.shape[0], no_beam + 1
         gt_captions = model.llm.decode_sequence(gt_labels)
