@@ -35,6 +35,8 @@ CONFIGS = {
     # BASELINE.json configs[2] / configs[4]: bf16 tensor-core GEMMs with fp32 master weights / accumulation (E = 1024 assumed)
     'cfg3': dict(ref='BASELINE.json configs[2]', model='LSTMwAttentionModel', B=512, L=49, D=2048, H=1024, E=1024, V=10000, T=16, dtype='bf16'),
     'cfg5': dict(ref='BASELINE.json configs[4]', model='LSTMwAttentionModel', B=256, L=49, D=2048, H=1024, E=1024, V=32000, T=32, dtype='bf16'),
+    # BASELINE.json configs[3]: decode (greedy / beam-5), exact token ids in fp32 -- `--config cfg4` runs the decode arm
+    'cfg4': dict(ref='BASELINE.json configs[3]', model='LSTMwAttentionModel', B=1024, L=196, D=512, H=512, E=512, V=10000, T=20, dtype='f32', decode=True),
 }
 METRIC = 'captions/sec (attn-LSTM fwd+bwd, T=16)'
 
@@ -145,44 +147,60 @@ def time_graph_events(fn, launches_per_graph, reps, warm=2):
 
 
 def dominant_kernel_roofline(c, dev, pk):
-    """The fused attention-step kernels (forward and backward: 34 launches per training step, each streaming Ws and
-    feat once) timed alone at the bench shape.  S distinct q/bpre slices per pass over the same Ws/feat, exactly as
-    inside a training step; launches replayed from a CUDA graph, CUDA events on the launching stream."""
+    """The fused attention-step kernels (34 launches per training step, each streaming Ws and feat once) timed alone at the
+    bench shape, launches replayed from a CUDA graph, CUDA events on the launching stream.  The dominant kernel BY STEP SHARE
+    is the backward one (profiles/r2*_step_breakdown.txt), so it is the headline; the forward kernel is nested.
+    Two figures each: `achieved` is COLD -- consecutive launches alternate between two distinct Ws/feat sets (2 x 103 MB at
+    cfg2 > the 126 MB L2), so every byte comes from HBM, which is what `peak` measures; `l2_warm` replays over ONE set (as
+    round 1 did), where part of the 103 MB hits L2: algorithmic bytes over time, NOT HBM bandwidth.  Inside a training step
+    the truth lies between (the same set is re-read by the next launch, with the GEMMs' traffic in between)."""
     from imagecaptioning_b200 import functional as F_
     B, L, D, H, S = c['B'], c['L'], c['D'], c['H'], c['T'] + 1
     g = torch.Generator(device='cpu').manual_seed(1)
-    Ws = torch.randn(B, L, H, generator=g).to(dev)
-    feat = torch.randn(B, L, D, generator=g).relu().to(dev)
+    sets = []
+    nsets = 2 if B * L * (H + D) * 4 * 2 > 140e6 else max(2, int(160e6 // (B * L * (H + D) * 4)) + 1)
+    for _ in range(nsets):
+        sets.append((torch.randn(B, L, H, generator=g).to(dev), torch.randn(B, L, D, generator=g).relu().to(dev)))
     q = torch.randn(S, B, H, generator=g).to(dev)
     bp = torch.randn(S, B, D, generator=g).to(dev)
     dg = torch.randn(S, B, D, generator=g).to(dev)
     wv = (torch.randn(H, generator=g) / H ** 0.5).to(dev)
-    outs = [F_.attn_step_fwd(Ws, feat, q[t], bp[t], wv) for t in range(S)]
-    state = {'t': 0}
+    outs = [[F_.attn_step_fwd(Ws, feat, q[t], bp[t], wv) for t in range(S)] for Ws, feat in sets]
+    state = {'t': 0, 'n': 1}
 
     def fwd():
         t = state['t'] = (state['t'] + 1) % S
+        Ws, feat = sets[t % state['n']]
         F_.attn_step_fwd(Ws, feat, q[t], bp[t], wv)
 
     def bwd():
         t = state['t'] = (state['t'] + 1) % S
-        a, cx, be, _ = outs[t]
+        Ws, feat = sets[t % state['n']]
+        a, cx, be, _ = outs[t % state['n']][t]
         F_.attn_step_bwd(Ws, feat, q[t], wv, a, cx, be, dg[t])
 
-    ms_f = time_graph_events(fwd, S, 12)
-    ms_b = time_graph_events(bwd, S, 12)
+    res = {}
+    for name, fn in (('fwd', fwd), ('bwd', bwd)):
+        state['n'] = 1
+        warm = time_graph_events(fn, 2 * S, 8)
+        state['n'] = nsets
+        cold = time_graph_events(fn, 2 * S, 8)
+        res[name] = (cold, warm)
     w = algorithmic_work(c)
-    ach = w['attn_fwd_bytes_per_launch'] / (ms_f * 1e-3) / 1e9
-    ach_b = w['attn_bwd_bytes_per_launch'] / (ms_b * 1e-3) / 1e9
-    return dict(kernel='attn_fwd_stream_kernel', bound='hbm', achieved=round(ach, 1), peak=pk['hbm'], unit='GB/s',
-                frac=round(ach / pk['hbm'], 4), traffic=NCU_TRAFFIC.get('attn_fwd') if c is CONFIGS['cfg2'] else None, ms_per_launch=round(ms_f, 5),
-                algorithmic_bytes_per_launch=w['attn_fwd_bytes_per_launch'], peak_source=pk['src'],
-                backward=dict(kernel='attn_bwd_stream_kernel', achieved=round(ach_b, 1), frac=round(ach_b / pk['hbm'], 4),
-                              ms_per_launch=round(ms_b, 5), algorithmic_bytes_per_launch=w['attn_bwd_bytes_per_launch'],
-                              traffic=NCU_TRAFFIC.get('attn_bwd') if c is CONFIGS['cfg2'] else None),
-                note='Ws+feat = %.0f MB per launch, re-read by each of the 2*S launches of a step; with a 126 MB L2 part '
-                     'of it can hit L2 between consecutive launches (ncu, cache flushed: dram__bytes_read = algorithmic '
-                     'bytes, see profiles/)' % (2 * B * L * max(H, D) * 4 / 1e6))
+    is2 = c is CONFIGS['cfg2']
+
+    def block(kernel, nbytes, cold, warm, traffic):
+        ach = nbytes / (cold * 1e-3) / 1e9
+        achw = nbytes / (warm * 1e-3) / 1e9
+        return dict(kernel=kernel, bound='hbm', achieved=round(ach, 1), peak=pk['hbm'], unit='GB/s', frac=round(ach / pk['hbm'], 4),
+                    traffic=traffic, ms_per_launch=round(cold, 5), algorithmic_bytes_per_launch=nbytes, peak_source=pk['src'],
+                    l2_warm=dict(achieved=round(achw, 1), frac=round(achw / pk['hbm'], 4), ms_per_launch=round(warm, 5)))
+    out = block('attn_bwd_stream_kernel', w['attn_bwd_bytes_per_launch'], *res['bwd'], NCU_TRAFFIC.get('attn_bwd') if is2 else None)
+    out['forward'] = block('attn_fwd_stream_kernel', w['attn_fwd_bytes_per_launch'], *res['fwd'], NCU_TRAFFIC.get('attn_fwd') if is2 else None)
+    out['share_of_step'] = 'backward 18.9 %, forward 15.2 % of the cfg2 step (profiles/r1i_step_breakdown.txt)'
+    out['note'] = ('achieved = cold (launches alternate over %d distinct Ws/feat sets, %.0f MB each: no L2 reuse); l2_warm = one set '
+                   're-read by every launch (part of it hits the 126 MB L2)' % (nsets, B * L * (H + D) * 4 / 1e6))
+    return out
 
 
 def optimizer_step_timing(model, step, dev, iters=20):
@@ -304,12 +322,194 @@ def run_reference(args, c, rank):
     print(json.dumps(line), flush=True)
 
 
-def workload_config(c, n):
+def workload_config(c, n, dropout_p=0.0):
     return dict(workload=f"{c['model']} decoder train step fwd+bwd ({c.get('ref', 'BASELINE.json configs[1]')}): B={c['B']}/GPU, "
                          f"L={c['L']}, D={c['D']}, H={c['H']}, E={c['E']}, V={c['V']}, T={c['T']}, {c['dtype']}, full-length captions, "
-                         f"dropout p=0",
+                         f"dropout p={dropout_p:g}",
                 global_batch=c['B'] * n, parallelism=f'dp{n}',
                 l2='no explicit flush: per-step working set (Ws+feat+logits+saved state ~ 400 MB) exceeds the 126 MB L2')
+
+
+class TrainRun:
+    """One model + DecoderTrainStep (+ GradAllReducer) on synthetic inputs of config `c`; times the resident step and the
+    end-to-end step (pinned host inputs -> H2D -> step (+ all-reduce) -> loss D2H)."""
+
+    def __init__(self, c, dev, rank, world, dist, graph=True, dropout_p=0.0):
+        from imagecaptioning_b200 import _lib
+        from imagecaptioning_b200.ddp import GradAllReducer
+        from imagecaptioning_b200.model import DecoderTrainStep
+        from oracle.synth import synth_inputs       # input generator shared with the oracle arm (not a compute path)
+        self.c, self.dev, self.dist, self.world, self.graph = c, dev, dist, world, graph
+        self.model = make_model(c, dev)
+        if dropout_p > 0:
+            self.model.dropout.p = dropout_p        # the reference's train() mode: nn.Dropout() p = 0.5 (AttentionLanguageModule.py:54)
+        self.model.train()
+        self.step = DecoderTrainStep(self.model, use_cuda_graph=graph)
+        feat, gt = synth_inputs(c['B'], c['L'], c['D'], c['V'], c['T'], seed=123 + rank, full_length=True)
+        self.feat_h, self.gt_h = feat.pin_memory(), gt.pin_memory()
+        self.step.stage(self.feat_h.to(dev), self.gt_h.to(dev))
+        self.reducer = GradAllReducer(self.step, world) if world > 1 else None
+        self.lib = _lib.load()
+
+    def one_step_resident(self):
+        if self.reducer:             # gradient groups all-reduced on a side stream under the running step
+            return self.reducer.step_overlapped()
+        return self.step.run_resident()
+
+    def barrier(self):
+        if self.dist:
+            self.dist.barrier()
+        torch.cuda.synchronize()
+
+    def launches_per_step(self):
+        st = self.step
+        st.use_cuda_graph = False
+        n0 = self.lib.alexcap_launch_count(); st.run_resident(); torch.cuda.synchronize()
+        n = int(self.lib.alexcap_launch_count() - n0)
+        st.use_cuda_graph = self.graph
+        return n
+
+    def time_resident(self, steps, warmup, local=None):
+        for _ in range(warmup):
+            self.one_step_resident()
+        self.barrier()
+        clk = ClockSampler(local) if local is not None else None
+        if clk:
+            clk.__enter__()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(steps):
+            loss4 = self.one_step_resident()
+        e.record()
+        self.barrier()
+        if clk:
+            clk.__exit__()
+        self.loss = float(loss4[0])
+        return s.elapsed_time(e) / steps, (clk.summary() if clk else None)
+
+    def time_e2e(self, steps):
+        """Every step's inputs start in PINNED HOST memory, are copied H2D inside the timed region (prefetch(): on a side
+        stream into the idle input set, overlapping the previous step's compute), the step runs (+ all-reduce), and the
+        loss is read back D2H (a host sync) every step."""
+        st = self.step
+        st.prefetch(self.feat_h, self.gt_h)
+
+        def one():
+            st.swap()                                   # compute stream waits for this step's H2D copy
+            st.prefetch(self.feat_h, self.gt_h)         # next step's inputs: H2D overlapped with this step
+            return float(self.one_step_resident()[0].item())
+        for _ in range(3):
+            one()
+        self.barrier()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(steps):
+            one()
+        e.record()
+        self.barrier()
+        return s.elapsed_time(e) / steps
+
+    def time_forward_train(self, steps):
+        """The call INTEGRATION.md documents -- DecoderTrainStep.forward_train(features, gt_labels) with HOST tensors, exactly
+        as the reference loop drives it (train_LSTMwAttention.py:78-96): zero_grad(set_to_none=True), forward_train, loss.item().
+        No prefetch: the H2D copy is in line.  Single GPU only (the data-parallel caller is GradAllReducer)."""
+        params = list(self.model.parameters())
+
+        def one():
+            for p in params:
+                p.grad = None
+            return float(self.step.forward_train(self.feat_h, self.gt_h).item())
+        for _ in range(3):
+            one()
+        torch.cuda.synchronize()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(steps):
+            one()
+        e.record()
+        torch.cuda.synchronize()
+        return s.elapsed_time(e) / steps
+
+    def close(self):
+        if self.reducer:
+            self.reducer.close()
+
+
+def max_over_ranks(vals, dev, dist):
+    t = torch.tensor(vals, device=dev, dtype=torch.float64)
+    if dist:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return [float(x) for x in t]
+
+
+def run_decode(args, c, dev, rank, world, local):
+    """BASELINE.json configs[3]: greedy and beam-5 caption decoding, batch 1024, T_max = 20 (fp32, exact token ids are a
+    parity test: tests/test_gpu_decode.py).  A 'step' is one decode of the whole batch; each token step streams Ws + feat once
+    (B*L*(H+D)*4 bytes) -> the HBM figure.  Replicas only at N > 1 (no exchange step): every rank decodes its own batch."""
+    from imagecaptioning_b200 import _lib
+    from oracle.synth import synth_inputs
+    model = make_model(c, dev)
+    model.eval()
+    with torch.no_grad():
+        model.deep_output.bias[c['V'] + 2] += 6.0          # END reachable with random weights (as in the decode fixtures)
+    feat, _ = synth_inputs(c['B'], c['L'], c['D'], c['V'], c['T'], seed=123 + rank, full_length=True)
+    feat_h = feat.pin_memory()
+    feat_d = feat_h.to(dev)
+    empty = torch.empty(0, device=dev)
+    lib = _lib.load()
+    out = {}
+    S = c['T'] + 1
+    for name, beam in (('greedy', 0), ('beam5', 5)):
+        model.use_beam = beam > 0
+        model.beam_size = beam
+
+        def one(f):
+            ids, _ = model(f, empty)
+            return ids
+        for _ in range(max(args.warmup, 3)):
+            ids = one(feat_d)
+        torch.cuda.synchronize()
+        n0 = lib.alexcap_launch_count()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(args.steps):
+            ids = one(feat_d)
+        e.record(); torch.cuda.synchronize()
+        ms = s.elapsed_time(e) / args.steps
+        launches = int(lib.alexcap_launch_count() - n0) // args.steps
+        # end to end: features from pinned host memory, ids back to the host
+        s2, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s2.record()
+        for _ in range(args.steps):
+            ids_h = one(feat_h.to(dev, non_blocking=True)).cpu()
+        e2.record(); torch.cuda.synchronize()
+        ms2 = s2.elapsed_time(e2) / args.steps
+        steps_run = int((ids != 0).any(dim=0).sum().item()) if beam == 0 else S
+        out[name] = dict(ms=ms, ms_e2e=ms2, launches=launches, token_steps=steps_run, d2h=int(ids_h.numel() * 8))
+    if rank != 0:
+        return
+    pk = peaks()
+    g, b5 = out['greedy'], out['beam5']
+    step_bytes = c['B'] * c['L'] * (c['H'] + c['D']) * 4
+    ach = step_bytes * g['token_steps'] / (g['ms'] * 1e-3) / 1e9
+    line = dict(metric='captions/sec (attn-LSTM greedy decode, T_max=20)', value=round(c['B'] * world / (g['ms'] * 1e-3), 1),
+                unit='captions/s', n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3), ms_per_step=round(g['ms'], 4),
+                higher_is_better=True, scaling='weak', vs_baseline=None, dtype='f32', data='synthetic',
+                config=dict(workload=f"LSTMwAttentionModel greedy / beam-5 decode (BASELINE.json configs[3]): B={c['B']}/GPU, L={c['L']}, "
+                                     f"D={c['D']}, H={c['H']}, E={c['E']}, V={c['V']}, T_max={c['T']}, f32 (3xTF32 tensor-core engine, exact ids)",
+                            global_batch=c['B'] * world, parallelism=f'replicas x{world}',
+                            l2='inputs (Ws+feat = %d MB per token step) exceed the 126 MB L2' % (step_bytes >> 20)),
+                e2e=dict(value=round(c['B'] * world / (g['ms_e2e'] * 1e-3), 1), unit='captions/s',
+                         h2d_bytes_per_step=int(feat_h.numel() * 4), d2h_bytes_per_step=g['d2h'], ms_per_step=round(g['ms_e2e'], 4)),
+                gpu_launches=g['launches'] * args.steps, gpu_launches_per_step=g['launches'],
+                beam5=dict(value=round(c['B'] * world / (b5['ms'] * 1e-3), 1), unit='captions/s', ms_per_step=round(b5['ms'], 4),
+                           e2e=round(c['B'] * world / (b5['ms_e2e'] * 1e-3), 1), gpu_launches_per_step=b5['launches']),
+                roofline=dict(kernel='attn_fwd_stream_kernel (decode: one launch per token step)', bound='hbm', achieved=round(ach, 1),
+                              peak=pk['hbm'], unit='GB/s', frac=round(ach / pk['hbm'], 4), traffic=None,
+                              algorithmic_bytes_per_launch=step_bytes, token_steps=g['token_steps'],
+                              note='whole greedy decode: token_steps x (Ws + feat) bytes over the decode time (GEMMs, argmax and '
+                                   'bookkeeping included in the time, not in the bytes)', peak_source=pk['src']))
+    print(json.dumps(line), flush=True)
 
 
 def main():
@@ -344,94 +544,84 @@ def main():
         os.dup2(2, 1)
         import torch.distributed as dist
         dist.init_process_group('nccl', device_id=dev)
-    from imagecaptioning_b200 import _lib
-    from imagecaptioning_b200.ddp import GradAllReducer
-    from imagecaptioning_b200.model import DecoderTrainStep
-    from oracle.synth import synth_inputs       # input generator shared with the oracle arm (not a compute path)
-
-    model = make_model(c, dev)
-    step = DecoderTrainStep(model, use_cuda_graph=not args.no_graph)
-    feat, gt = synth_inputs(c['B'], c['L'], c['D'], c['V'], c['T'], seed=123 + rank, full_length=True)
-    feat_h, gt_h = feat.pin_memory(), gt.pin_memory()
-    step.stage(feat_h.to(dev), gt_h.to(dev))
-    reducer = GradAllReducer(step, world) if world > 1 else None
-    lib = _lib.load()
-
-    def one_step_resident():
-        if reducer:                  # all-reduce of the vocab-projection bucket overlapped with the reverse chain
-            return reducer.step_overlapped()
-        return step.run_resident()
-
-    def barrier():
+    if c.get('decode'):
+        run_decode(args, c, dev, rank, world, local)
         if dist:
-            dist.barrier()
-        torch.cuda.synchronize()
+            dist.barrier(); sys.stdout.flush(); sys.stderr.flush(); os._exit(0)
+        return
 
-    # launches per step (counted on an un-graphed step)
-    step.use_cuda_graph = False
-    n0 = lib.alexcap_launch_count(); step.run_resident(); torch.cuda.synchronize()
-    launches_per_step = int(lib.alexcap_launch_count() - n0)
-    step.use_cuda_graph = not args.no_graph
+    run = TrainRun(c, dev, rank, world, dist, graph=not args.no_graph)
+    step, model = run.step, run.model
+    launches_per_step = run.launches_per_step()
+    ms, clocks = run.time_resident(args.steps, args.warmup, local)
+    loss_val = run.loss
+    ms_e2e = run.time_e2e(args.steps)
+    ms, ms_e2e = max_over_ranks([ms, ms_e2e], dev, dist)
+    total = c['B'] * world
+    extra = {}
+    is_attn = c['model'] == 'LSTMwAttentionModel'
 
-    for _ in range(args.warmup):
-        one_step_resident()
-    barrier()
-    with ClockSampler(local) as clk:
-        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        s.record()
-        for _ in range(args.steps):
-            loss4 = one_step_resident()
-        e.record()
-        barrier()
-    ms = s.elapsed_time(e) / args.steps
-    loss_val = float(loss4[0])
-
-    # end to end through the public API: every step's inputs start in PINNED HOST memory, are copied H2D inside the
-    # timed region (prefetch(): on a side stream into the idle input set, overlapping the previous step's compute),
-    # the step runs (+ all-reduce), and the loss is read back D2H (a host sync) every step.
-    step.prefetch(feat_h, gt_h)
-
-    def one_step_e2e():
-        step.swap()                          # compute stream waits for this step's H2D copy
-        step.prefetch(feat_h, gt_h)          # next step's inputs: H2D overlapped with this step
-        l4 = one_step_resident()
-        return float(l4[0].item())           # D2H read of the loss
-    for _ in range(3):
-        one_step_e2e()
-    barrier()
-    s2, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    s2.record()
-    for _ in range(args.steps):
-        one_step_e2e()
-    e2.record()
-    barrier()
-    ms_e2e = s2.elapsed_time(e2) / args.steps
-
-    t = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
-    if dist:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms, ms_e2e = float(t[0]), float(t[1])
+    if is_attn:
+        # the reference's REAL training mode: nn.Dropout() p = 0.5 in train() (AttentionLanguageModule.py:54,79), mask drawn on
+        # the device from a Philox counter that lives on the device -> same CUDA graph, fresh mask per replay
+        drun = TrainRun(c, dev, rank, world, dist, graph=not args.no_graph, dropout_p=0.5)
+        d_launch = drun.launches_per_step()
+        d_ms, _ = drun.time_resident(args.steps, args.warmup)
+        (d_ms,) = max_over_ranks([d_ms], dev, dist)
+        extra['dropout_p05'] = dict(value=round(total / (d_ms * 1e-3), 1), unit='captions/s', ms_per_step=round(d_ms, 4),
+                                    slowdown_vs_p0=round(d_ms / ms, 4), gpu_launches_per_step=d_launch, cuda_graph=not args.no_graph,
+                                    loss=round(drun.loss, 5))
+        drun.close(); del drun
+    if world == 1:
+        ft = run.time_forward_train(args.steps)
+        extra['e2e_forward_train'] = dict(
+            value=round(total / (ft * 1e-3), 1), unit='captions/s', ms_per_step=round(ft, 4),
+            what='DecoderTrainStep.forward_train(features_host_pinned, gt_host) + loss.item() per step, zero_grad(set_to_none) '
+                 'before each (the call INTEGRATION.md documents; in-line H2D copy, no prefetch)',
+            h2d_bytes_per_step=int(run.feat_h.numel() * 4 + run.gt_h.numel() * 4), d2h_bytes_per_step=4)
+    if world > 1 and is_attn:
+        # correctness of the overlapped exchange ON THIS HARDWARE: ragged captions, every rank's averaged gradients vs the
+        # single-process step on the concatenated batch; the all-reduced loss (tests/ddp_worker.py)
+        from tests.ddp_worker import ddp_check
+        cc = dict(c); cc['B'] = min(c['B'], 64)
+        worst, loss_rel, spread, nv_ddp, nv_one = ddp_check(dev, rank, world, cc, graph=not args.no_graph)
+        gl = run.reducer.global_loss()
+        extra['ddp_check'] = dict(grad_rel_vs_single_process=float('%.3e' % worst), loss_rel=float('%.3e' % loss_rel),
+                                  rank_spread=float('%.3e' % spread), n_valid_sum_over_ranks=nv_ddp, n_valid_single_process=nv_one,
+                                  shape='B=%d/rank ragged captions, rest as the workload' % cc['B'],
+                                  global_loss=round(float(gl[0]), 5))
+        if args.config == 'cfg2':
+            # the configuration BASELINE.json names for data parallelism (configs[2]): bf16 mode, B = 512 per GPU
+            c3 = CONFIGS['cfg3']
+            r3 = TrainRun(c3, dev, rank, world, dist, graph=not args.no_graph)
+            m3, _ = r3.time_resident(max(5, args.steps // 2), args.warmup)
+            m3e = r3.time_e2e(max(5, args.steps // 2))
+            m3, m3e = max_over_ranks([m3, m3e], dev, dist)
+            extra['cfg3'] = dict(value=round(c3['B'] * world / (m3 * 1e-3), 1), unit='captions/s', ms_per_step=round(m3, 4),
+                                 e2e=round(c3['B'] * world / (m3e * 1e-3), 1), dtype='bf16', config=workload_config(c3, world),
+                                 loss=round(r3.loss, 5))
+            r3.close(); del r3
 
     if rank == 0:
         pk = peaks()
-        total = c['B'] * world
         line = dict(metric=METRIC, value=round(total / (ms * 1e-3), 1), unit='captions/s', n_gpus=world, steps=args.steps,
                     warmup=args.warmup, ms_per_step=round(ms, 4), higher_is_better=True, scaling='weak', vs_baseline=None,
                     dtype=c['dtype'], data='synthetic', config=workload_config(c, world), loss=round(loss_val, 5),
                     cuda_graph=not args.no_graph,
                     e2e=dict(value=round(total / (ms_e2e * 1e-3), 1), unit='captions/s',
-                             h2d_bytes_per_step=int(feat_h.numel() * 4 + gt_h.numel() * 4), d2h_bytes_per_step=4,
+                             h2d_bytes_per_step=int(run.feat_h.numel() * 4 + run.gt_h.numel() * 4), d2h_bytes_per_step=4,
                              ms_per_step=round(ms_e2e, 4)),
                     gpu_launches=launches_per_step * args.steps, gpu_launches_per_step=launches_per_step,
-                    clocks=clk.summary())
+                    clocks=clocks)
+        line.update(extra)
         w = algorithmic_work(c)
         line['gemm_group'] = dict(algorithmic_gflop_per_step=round(w['gemm_flops_step'] / 1e9, 2),
                                   engine='tcgen05 bf16x3: hi/lo bf16 operand pairs, 3 MMAs per product, fp32 accumulate (fp32 in/out, 1e-4 parity)' if c['dtype'] == 'f32' else
                                   'tcgen05 bf16 operands, fp32 accumulate (2e-2 parity)')
-        if c['model'] == 'LSTMwAttentionModel':
+        if is_attn:
             line['roofline'] = dominant_kernel_roofline(c, dev, pk)
             line['roofline_gemm'] = gemm_roofline(c, dev, pk)
-        if world == 1 and c['model'] == 'LSTMwAttentionModel':
+        if world == 1 and is_attn:
             line['next_row_optimizer'] = optimizer_step_timing(model, step, dev)
         if world == 1 and not args.no_cpu_baseline:
             cb, _, _ = time_cpu_port(c, steps=3, warmup=1, budget_s=25.0)
@@ -440,6 +630,7 @@ def main():
             sys.stdout.flush()
             os.dup2(saved_stdout, 1)
         print(json.dumps(line), flush=True)
+    reducer = run.reducer
     if dist:
         # the whole-step CUDA graphs hold captured NCCL kernels: drop them before the communicator, and do not let the
         # communicator's teardown outlive the measurement (every rank has finished its timed region by the barrier)

@@ -17,7 +17,8 @@ class Dims(C.Structure):
     _fields_ = [('B', C.c_int32), ('L', C.c_int32), ('D', C.c_int32), ('H', C.c_int32), ('E', C.c_int32),
                 ('Vp', C.c_int32), ('S', C.c_int32), ('num_layers', C.c_int32), ('dtype', C.c_int32),
                 ('need_dfeat', C.c_int32), ('ignore_index', C.c_int32), ('label_smoothing', C.c_float),
-                ('reg_weight', C.c_float), ('dropout_p', C.c_float), ('seed', C.c_uint64), ('offset', C.c_uint64)]
+                ('reg_weight', C.c_float), ('dropout_p', C.c_float), ('seed', C.c_uint64), ('offset', C.c_uint64),
+                ('philox_state', C.c_void_p)]
 
 
 ATTN_FIELDS = ['init_h_w', 'init_h_b', 'init_c_w', 'init_c_b', 'f_beta_w', 'f_beta_b', 'deep_w', 'deep_b',
@@ -53,6 +54,9 @@ PROTOTYPES = {
     'alexcap_set_gemm_engine': (C.c_int, [C.c_int]),
     'alexcap_get_gemm_engine': (C.c_int, []),
     'alexcap_attn_workspace_bytes': (_SZ, [_DP]),
+    'alexcap_attn_workspace_region': (C.c_int, [_DP, C.c_char_p, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
+    'alexcap_mean_over_L': (C.c_int, [_P, _I32, _I32, _I32, _P, _P]),
+    'alexcap_count_valid_targets': (C.c_int, [_P, _I32, _I32, _P, _P]),
     'alexcap_attn_train_fused': (C.c_int, [_DP, _AP, _P, _P, _AP, _P, _P, _P, _P, _P, _P, _SZ, _P]),
     'alexcap_clip_adam_scratch_floats': (C.c_size_t, []),
     'alexcap_clip_adam_step': (C.c_int, [C.c_int32, _P, _P, _P, _P, _P, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float,
@@ -108,7 +112,7 @@ def load(build_if_missing: bool = True):
     for name, (res, args) in PROTOTYPES.items():
         fn = getattr(lib, name)      # AttributeError here == header/ABI mismatch: fail loudly
         fn.restype, fn.argtypes = res, args
-    if lib.alexcap_abi_version() != 1:
+    if lib.alexcap_abi_version() != 2:
         raise AlexcapError('libalexcap_b200.so ABI version mismatch')
     _lib = lib
     return lib

@@ -15,6 +15,9 @@
 //                    dWs in one pass, embedding scatter-add, init-state gradients.
 #include <stdlib.h>
 
+#include <mutex>
+#include <unordered_map>
+
 #include "api_util.h"
 
 using namespace alexcap;
@@ -38,7 +41,7 @@ namespace {
 
 // ------------------------------------------------------------------------------------------ attention workspace
 struct AttnWs {
-  int32_t *in_bm, *tgt_bm, *in_tm, *tgt_tm;
+  int32_t *in_bm, *tgt_bm, *in_tm, *tgt_tm, *bad_rows;
   float *m, *XH, *Call, *Ws, *EmbIn, *DGQ, *QB, *BETA, *CTX, *ALPHA, *DE;
   float *Wcat, *Wub, *bub, *Wback;
   float *MASK, *Hd;
@@ -57,6 +60,7 @@ AttnWs attn_layout(const alexcap_dims* d, void* base, bool with_logits) {
   w.ldV = (Vp + 3) & ~int64_t(3);
   w.in_bm = a.take<int32_t>(B * S); w.tgt_bm = a.take<int32_t>(B * S);
   w.in_tm = a.take<int32_t>(B * S); w.tgt_tm = a.take<int32_t>(B * S);
+  w.bad_rows = a.take<int32_t>(B);
   w.m = a.take<float>(B * D);
   w.XH = a.take<float>((S + 1) * B * (D + H));
   w.Call = a.take<float>((S + 1) * B * H);
@@ -109,7 +113,7 @@ int attn_fwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
   const int B = d->B, L = d->L, D = d->D, H = d->H, E = d->E, Vp = d->Vp, S = d->S;
   const int64_t DH = D + H, W5 = 5 * (int64_t)H + D, HD = H + D;
   const int V = Vp - 3;
-  API_CK(make_target(st, gt, B, S - 1, V + 1, V + 2, w.in_bm, w.tgt_bm, w.in_tm, w.tgt_tm));
+  API_CK(make_target(st, gt, B, S - 1, V + 1, V + 2, w.in_bm, w.tgt_bm, w.in_tm, w.tgt_tm, Vp, w.bad_rows));
   // initial state (AttentionLanguageModule.py:116-125)
   API_CK(mean_over_L(st, feat, B, L, D, w.m));
   API_CK(gemm_f32(st, false, true, B, H, D, 1.f, w.m, D, P->init_h_w, D, w.XH + D, DH, P->init_h_b, nullptr, false, ACT_TANH));
@@ -146,9 +150,13 @@ int attn_fwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
                               xh + (int64_t)B * DH + D, DH, nullptr, 0));
   }
   if (d->dropout_p > 0.f) {                                                 // :79 dropout(h)
-    if (drop_mask) API_CK(cudaMemcpyAsync(w.MASK, drop_mask, sizeof(float) * S * B * H, cudaMemcpyDeviceToDevice, st));
-    else API_CK(dropout_mask(st, w.MASK, (int64_t)S * B * H, d->dropout_p, d->seed, d->offset));
-    API_CK(mul_2d(st, S * B, H, w.XH + (int64_t)B * DH + D, DH, w.MASK, H, w.Hd, H));
+    if (drop_mask) {
+      API_CK(cudaMemcpyAsync(w.MASK, drop_mask, sizeof(float) * S * B * H, cudaMemcpyDeviceToDevice, st));
+      API_CK(mul_2d(st, S * B, H, w.XH + (int64_t)B * DH + D, DH, w.MASK, H, w.Hd, H));
+    } else {              // mask drawn and applied in one pass; counter on the device when the caller gave one (graph replays)
+      API_CK(dropout_mask(st, w.MASK, (int64_t)S * B * H, d->dropout_p, d->seed, d->offset, d->philox_state,
+                          w.XH + (int64_t)B * DH + D, DH, H, w.Hd));
+    }
   }
   return 0;
 }
@@ -288,6 +296,18 @@ int attn_bwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
   return 0;
 }
 
+// Host-side bookkeeping of the training step a workspace holds (which bf16 operand copies exist in its arena after which
+// phase).  Keyed by the workspace pointer; entries live for the process (a few hundred bytes + the entry table each).
+struct StepState { std::mutex mu; SplitArena arena; size_t mark_after_16 = 0, mark_after_1 = 0, mark_after_4 = 0; };
+StepState& step_state(void* workspace) {
+  static std::mutex mu;
+  static std::unordered_map<void*, StepState*> table;
+  std::lock_guard<std::mutex> lock(mu);
+  StepState*& e = table[workspace];
+  if (!e) e = new StepState();
+  return *e;
+}
+
 int check_attn_args(const alexcap_dims* d, const alexcap_attn_params* P, const void* feat, const void* ws, size_t ws_bytes,
                     size_t need) {
   int rc = check_dims_common(d);
@@ -310,6 +330,7 @@ unsigned long long alexcap_launch_count(void) { return launch_counter(); }
 
 int alexcap_set_gemm_engine(int engine) {
   if (engine < 0 || engine > 3) return fail(ALEXCAP_E_BADARG, "engine must be 0 (fp32 CUDA cores), 1 (tcgen05 3xTF32) or 2 (tcgen05 bf16)");
+  gemm_engine_set_default(engine);
   gemm_engine() = engine;
   return 0;
 }
@@ -342,16 +363,22 @@ static int attn_train_phases(const alexcap_dims* d, const alexcap_attn_params* P
   AttnWs w = attn_layout(d, nullptr, true);
   if (int rc = check_attn_args(d, P, feat, workspace, workspace_bytes, w.bytes)) return rc;
   if (!gt || !G || !loss_out) return fail(ALEXCAP_E_BADARG, "NULL gt / grads / loss_out");
-  if (phase != 1 && phase != 2 && phase != 3 && phase != 4 && phase != 8)
-    return fail(ALEXCAP_E_BADARG, "phase must be 1, 2, 3 (= 1|2), 4 or 8 (the halves of 2)");
+  if (phase != 1 && phase != 2 && phase != 3 && phase != 4 && phase != 8 && phase != 16 && phase != 32)
+    return fail(ALEXCAP_E_BADARG, "phase must be 1, 2, 3 (= 1|2), 4 or 8 (the halves of 2), 16 or 32 (the halves of 1)");
   w = attn_layout(d, workspace, true);
-  // phases 2 / 4 / 8 continue the step phase 1 started (same arguments and workspace): feat, W_W, dgates ... stay split
-  // -- but only what the EARLIER phases made: a repeated phase 4 (say) must not find the copies of its previous run.
-  static thread_local SplitArena step_arena;
-  static thread_local size_t mark_after_1 = 0, mark_after_4 = 0;
-  ArenaScope arena_scope(w.arena, w.arena_bytes, &step_arena, (phase & 1) != 0);
-  if (!(phase & 1) && step_arena.base) {
-    size_t mark = (phase == 8) ? mark_after_4 : mark_after_1;
+  // phases 2 / 4 / 8 / 32 continue the step an earlier phase started (same arguments and workspace): feat, W_W, dgates ... stay
+  // split -- but only what the EARLIER phases made: a repeated phase 4 (say) must not find the copies of its previous run.
+  // The bookkeeping belongs to the WORKSPACE (not to the thread): interleaved steps of two models, or a validation step
+  // between the phases of a training step, each keep their own.
+  StepState& ss = step_state(workspace);
+  std::lock_guard<std::mutex> step_lock(ss.mu);
+  SplitArena& step_arena = ss.arena;
+  const bool fresh = (phase & 1) || phase == 16;
+  if (!fresh && (step_arena.base != w.arena || step_arena.bytes != w.arena_bytes))
+    return fail(ALEXCAP_E_BADARG, "phase 2/4/8/32 on a workspace whose step was not started by phase 1/16 with the same dims");
+  ArenaScope arena_scope(w.arena, w.arena_bytes, &step_arena, fresh);
+  if (!fresh && step_arena.base) {
+    size_t mark = (phase == 8) ? ss.mark_after_4 : (phase == 32) ? ss.mark_after_16 : ss.mark_after_1;
     if (mark > step_arena.used) mark = step_arena.used;
     split_arena_release(&step_arena, mark);
   }
@@ -359,8 +386,11 @@ static int attn_train_phases(const alexcap_dims* d, const alexcap_attn_params* P
   const int B = d->B, D = d->D, H = d->H, Vp = d->Vp, S = d->S, L = d->L, SB = S * B;
   const int64_t DH = D + H;
   const bool reg = d->reg_weight != 0.f;
-  if (phase & 1) {
+  if ((phase & 1) || phase == 16) {
     if (int rc = attn_fwd_core(d, P, feat, gt, drop_mask, w, st)) return rc;
+    ss.mark_after_16 = ss.mark_after_1 = ss.mark_after_4 = step_arena.used;
+  }
+  if ((phase & 1) || phase == 32) {
     const float* hout = w.Hd ? w.Hd : w.XH + (int64_t)B * DH + D;
     const int64_t hld = w.Hd ? H : DH;
     // vocabulary projection (AttentionLanguageModule.py:79) + CustomCrossEntropyLoss + vocab backward, in L2-sized row chunks
@@ -370,15 +400,15 @@ static int attn_train_phases(const alexcap_dims* d, const alexcap_attn_params* P
                                   w.dHout, w.cs_scratch)) return rc;
     API_CK(reduce_sum(st, w.row_loss, SB, w.scal + 1));
     if (reg) API_CK(attn_regulariser(st, B, S, L, d->reg_weight, w.ALPHA, w.R, w.scal + 2, w.reg_scratch));
-    API_CK(finalize_loss(st, w.scal + 1, reg ? w.scal + 2 : nullptr, w.scal, loss_out));
+    API_CK(finalize_loss(st, w.scal + 1, reg ? w.scal + 2 : nullptr, w.scal, loss_out, w.bad_rows, B));
     if (alphas_out)
       API_CK(cudaMemcpyAsync(alphas_out, w.ALPHA, sizeof(float) * (size_t)B * S * L, cudaMemcpyDeviceToDevice, st));
-    mark_after_1 = mark_after_4 = step_arena.used;
+    ss.mark_after_1 = ss.mark_after_4 = step_arena.used;
   }
   int rc = 0;
   if (phase & 2) rc = attn_bwd_core(d, P, feat, nullptr, reg ? w.R : nullptr, G, dfeat, w, st, 3);
-  else if (phase & 12) rc = attn_bwd_core(d, P, feat, nullptr, reg ? w.R : nullptr, G, dfeat, w, st, phase == 4 ? 1 : 2);
-  if (phase == 4) mark_after_4 = step_arena.used;
+  else if (phase == 4 || phase == 8) rc = attn_bwd_core(d, P, feat, nullptr, reg ? w.R : nullptr, G, dfeat, w, st, phase == 4 ? 1 : 2);
+  if (phase == 4) ss.mark_after_4 = step_arena.used;
   return rc;
 }
 
@@ -455,6 +485,33 @@ int alexcap_make_target(const int32_t* gt, int32_t* in_tok, int32_t* tgt, int32_
                         int32_t end_token, void* stream) {
   if (!gt || B <= 0 || T <= 0) return fail(ALEXCAP_E_BADARG, "alexcap_make_target: bad arguments");
   API_CK(make_target(static_cast<cudaStream_t>(stream), gt, B, T, start_token, end_token, in_tok, tgt, nullptr, nullptr));
+  return 0;
+}
+
+int alexcap_count_valid_targets(const int32_t* gt, int32_t B, int32_t T, float* n_valid_out, void* stream) {
+  if (!gt || !n_valid_out || B <= 0 || T <= 0) return fail(ALEXCAP_E_BADARG, "alexcap_count_valid_targets: bad arguments");
+  API_CK(count_valid_targets(static_cast<cudaStream_t>(stream), gt, B, T, n_valid_out));
+  return 0;
+}
+
+int alexcap_mean_over_L(const float* feat, int32_t B, int32_t L, int32_t D, float* m, void* stream) {
+  if (!feat || !m || B <= 0 || L <= 0 || D <= 0 || (D & 3)) return fail(ALEXCAP_E_BADARG, "alexcap_mean_over_L: bad arguments (D % 4 == 0)");
+  API_CK(mean_over_L(static_cast<cudaStream_t>(stream), feat, B, L, D, m));
+  return 0;
+}
+
+int alexcap_attn_workspace_region(const alexcap_dims* d, const char* name, size_t* offset, size_t* bytes) {
+  if (int rc = check_dims_common(d)) return rc;
+  if (!name || !offset || !bytes) return fail(ALEXCAP_E_BADARG, "alexcap_attn_workspace_region: NULL argument");
+  char* base = reinterpret_cast<char*>(uintptr_t(1) << 20);       // a fake, aligned base: only differences are used
+  const AttnWs w = attn_layout(d, base, true);
+  const size_t B = d->B, L = d->L, D = d->D, H = d->H, S = d->S;
+  const void* p = nullptr; size_t n = 0;
+  if (!strcmp(name, "MASK")) { p = w.MASK; n = S * B * H * 4; }
+  else if (!strcmp(name, "ALPHA")) { p = w.ALPHA; n = B * S * L * 4; }
+  else if (!strcmp(name, "H")) { p = w.XH; n = (S + 1) * B * (D + H) * 4; }
+  if (!p) return fail(ALEXCAP_E_BADARG, "alexcap_attn_workspace_region: unknown region name, or a region these dims do not have");
+  *offset = (size_t)(static_cast<const char*>(p) - base); *bytes = n;
   return 0;
 }
 

@@ -25,7 +25,7 @@ using namespace alexcap;
 namespace {
 
 struct LstmWs {
-  int32_t *in_bm, *tgt_bm, *in_tm, *tgt_tm;
+  int32_t *in_bm, *tgt_bm, *in_tm, *tgt_tm, *bad_rows;
   float *enc_bm, *In0;
   float *G[ALEXCAP_MAX_LAYERS], *Hs[ALEXCAP_MAX_LAYERS], *Cs[ALEXCAP_MAX_LAYERS];
   float *MASK, *Hd, *logits, *row_loss, *scal, *dHout, *dA, *dB, *dh_next, *dc, *dpre_bm, *cs_scratch;
@@ -42,6 +42,7 @@ LstmWs lstm_layout(const alexcap_dims* d, void* base, bool with_logits) {
   w.ldV = (Vp + 3) & ~int64_t(3);
   w.in_bm = a.take<int32_t>(B * S); w.tgt_bm = a.take<int32_t>(B * S);
   w.in_tm = a.take<int32_t>(B * S); w.tgt_tm = a.take<int32_t>(B * S);
+  w.bad_rows = a.take<int32_t>(B);
   w.enc_bm = a.take<float>(B * L * E);
   w.In0 = a.take<float>(LT * B * E);
   for (int l = 0; l < nl; ++l) {
@@ -113,7 +114,7 @@ int run_layer_fwd(const alexcap_dims* d, const float* in, int I, const float* w_
 int lstm_fwd_core(const alexcap_dims* d, const alexcap_lstm_params* P, const float* feat, const int32_t* gt,
                   const float* drop_mask, LstmWs& w, cudaStream_t st) {
   const int B = d->B, L = d->L, D = d->D, H = d->H, E = d->E, S = d->S, LT = L + S, V = d->Vp - 3;
-  API_CK(make_target(st, gt, B, S - 1, V + 1, V + 2, w.in_bm, w.tgt_bm, w.in_tm, w.tgt_tm));
+  API_CK(make_target(st, gt, B, S - 1, V + 1, V + 2, w.in_bm, w.tgt_bm, w.in_tm, w.tgt_tm, d->Vp, w.bad_rows));
   // image_encoder: ReLU(Linear) on every region (LanguageModule.py:35-37,103), then to time-major
   API_CK(gemm_f32(st, false, true, B * L, E, D, 1.f, feat, D, P->enc_w, D, w.enc_bm, E, P->enc_b, nullptr, false, ACT_RELU));
   API_CK(permute_01(st, B, L, E, w.enc_bm, w.In0));
@@ -125,9 +126,13 @@ int lstm_fwd_core(const alexcap_dims* d, const alexcap_lstm_params* P, const flo
       return rc;
   }
   if (d->dropout_p > 0.f) {   // rnn.drop (:48,:106)
-    if (drop_mask) API_CK(cudaMemcpyAsync(w.MASK, drop_mask, sizeof(float) * S * B * H, cudaMemcpyDeviceToDevice, st));
-    else API_CK(dropout_mask(st, w.MASK, (int64_t)S * B * H, d->dropout_p, d->seed, d->offset));
-    API_CK(mul_2d(st, S * B, H, w.Hs[d->num_layers - 1] + (int64_t)(1 + L) * B * H, H, w.MASK, H, w.Hd, H));
+    const float* htop = w.Hs[d->num_layers - 1] + (int64_t)(1 + L) * B * H;
+    if (drop_mask) {
+      API_CK(cudaMemcpyAsync(w.MASK, drop_mask, sizeof(float) * S * B * H, cudaMemcpyDeviceToDevice, st));
+      API_CK(mul_2d(st, S * B, H, htop, H, w.MASK, H, w.Hd, H));
+    } else {
+      API_CK(dropout_mask(st, w.MASK, (int64_t)S * B * H, d->dropout_p, d->seed, d->offset, d->philox_state, htop, H, H, w.Hd));
+    }
   }
   return 0;
 }
@@ -214,7 +219,7 @@ int alexcap_lstm_train_fused(const alexcap_dims* d, const alexcap_lstm_params* P
                                 d->ignore_index, ce_denominator ? ce_denominator : w.scal, w.row_loss, G->out_w, G->out_b,
                                 w.dHout, w.cs_scratch)) return rc;
   API_CK(reduce_sum(st, w.row_loss, SB, w.scal + 1));
-  API_CK(finalize_loss(st, w.scal + 1, nullptr, w.scal, loss_out));
+  API_CK(finalize_loss(st, w.scal + 1, nullptr, w.scal, loss_out, w.bad_rows, B));
   return lstm_bwd_core(d, P, feat, G, dfeat, w, st);
 }
 

@@ -55,7 +55,8 @@ __global__ void __launch_bounds__(CE_THREADS) ce_rows_kernel(const float* __rest
   for (int c = threadIdx.x; c < C; c += CE_THREADS) se += expf(x[c] - mx);
   se = block_sum(se, scratch);
   const float lse = mx + logf(se);
-  const float inv_d = 1.f / fmaxf(denom[0], 1.f);
+  const float dn = denom[0];
+  const float inv_d = dn > 0.f ? 1.f / dn : 0.f;     // (a data-parallel divisor N_valid_global / world may be < 1)
   if (threadIdx.x == 0) {
     const float nll = lse - xy;
     const float smooth = lse - sx / (float)C;

@@ -6,6 +6,8 @@
 // Layout: BMxBN output tile per CTA, BK=16 k-slab double-buffered in shared memory (k-major, so the inner loop
 // reads float4 along m and n), 128-bit global loads when the operand's leading dimension allows it,
 // (4*RM)x(4*RN) accumulators per thread.
+#include <atomic>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -213,12 +215,23 @@ bool& gemm_b_is_weight() {
   static thread_local bool on = false;
   return on;
 }
+// 0 = fp32 CUDA-core tiles; 1 = tcgen05 3xTF32 (2^-21: decoding always uses it); 2 = tcgen05 bf16 (mixed precision);
+// 3 = tcgen05 bf16x3 (hi/lo bf16 pairs, 2^-17, 1.3x faster than 3xTF32: the training default).  Per-call fallback to
+// engine 0 when TMA cannot map the operands.  The process-wide default (alexcap_set_gemm_engine) is mirrored into a
+// thread-local value, which is what the scoped per-call overrides (DtypeScope, ExactScope) change: concurrent calls on
+// different host threads do not see each other's overrides.
+static std::atomic<int> g_engine_default{3};
+static std::atomic<unsigned> g_engine_gen{0};
 int& gemm_engine() {
-  // 0 = fp32 CUDA-core tiles; 1 = tcgen05 3xTF32 (2^-21: decoding always uses it); 2 = tcgen05 bf16 (mixed precision);
-  // 3 = tcgen05 bf16x3 (hi/lo bf16 pairs, 2^-17, 1.3x faster than 3xTF32: the training default).  Per-call fallback to
-  // engine 0 when TMA cannot map the operands.
-  static int engine = 3;
-  return engine;
+  static thread_local int eng = 3;
+  static thread_local unsigned gen = ~0u;
+  const unsigned g = g_engine_gen.load(std::memory_order_acquire);
+  if (gen != g) { eng = g_engine_default.load(std::memory_order_relaxed); gen = g; }
+  return eng;
+}
+void gemm_engine_set_default(int engine) {
+  g_engine_default.store(engine, std::memory_order_relaxed);
+  g_engine_gen.fetch_add(1, std::memory_order_release);
 }
 
 // Engine dispatch used by every GEMM on the hot path.

@@ -40,7 +40,8 @@ cudaError_t gemm_ps_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, 
                         const float* bias, const float* bias2, bool accumulate, int act, int force_splits, int nprod,
                         SplitArena* arena);
 bool gemm_tc_supported(int M, int N, int K, const float* A, int64_t lda, const float* B, int64_t ldb, const float* C);
-int& gemm_engine();
+int& gemm_engine();                      // this thread's engine (scoped overrides write it)
+void gemm_engine_set_default(int engine); // process-wide default, picked up by every thread
 // Hint for the calls made while it is true: the B operand holds weights that were final before the PREVIOUS kernel of the
 // stream started, so the kernel may fetch B tiles ahead of its programmatic-dependent-launch wait (api.cu: WeightBScope).
 bool& gemm_b_is_weight();
@@ -108,8 +109,12 @@ cudaError_t ce_rows(cudaStream_t st, const float* logits, const int32_t* tgt, in
 cudaError_t reduce_sum(cudaStream_t st, const float* x, int n, float* out, float* scratch = nullptr);
 
 // ---- misc (misc.cu)
+// n_classes > 0: tokens outside [0, n_classes) are replaced by 0 and the row is flagged in bad_rows[B] (may be NULL)
 cudaError_t make_target(cudaStream_t st, const int32_t* gt, int B, int T, int start_tok, int end_tok,
-                        int32_t* in_bm, int32_t* tgt_bm, int32_t* in_tm, int32_t* tgt_tm);
+                        int32_t* in_bm, int32_t* tgt_bm, int32_t* in_tm, int32_t* tgt_tm, int n_classes = 0,
+                        int32_t* bad_rows = nullptr);
+// out[0] = nnz(gt) + B = number of non-ignored targets of get_target(gt, make_target=True)
+cudaError_t count_valid_targets(cudaStream_t st, const int32_t* gt, int B, int T, float* out);
 cudaError_t mean_over_L(cudaStream_t st, const float* feat, int B, int L, int D, float* m);
 // out[r,:] = table[idx[r],:]   (rows of `width` floats; out row stride out_ld)
 cudaError_t gather_rows(cudaStream_t st, const float* table, const int32_t* idx, int rows, int width, float* out,
@@ -141,10 +146,14 @@ cudaError_t add_broadcast_L(cudaStream_t st, int B, int L, int D, const float* d
 // out[i] = a[i] * b[i]
 cudaError_t mul_2d(cudaStream_t st, int rows, int cols, const float* a, int64_t a_ld, const float* b, int64_t b_ld,
                    float* out, int64_t out_ld);
-// mask[i] = (philox(seed, offset+i) >= p) ? 1/(1-p) : 0
-cudaError_t dropout_mask(cudaStream_t st, float* mask, int64_t n, float p, uint64_t seed, uint64_t offset);
-// loss_out = {a+b, a, b, n_valid}
-cudaError_t finalize_loss(cudaStream_t st, const float* ce_sum, const float* reg, const float* n_valid, float* loss_out);
+// mask[i] = (philox(seed, offset+i) >= p) ? 1/(1-p) : 0.  state (device {seed, offset}) overrides seed / offset and is
+// advanced on the device afterwards.  y != NULL: also y[i] = mask[i] * x[i / cols][i % cols] (x row stride x_ld).
+cudaError_t dropout_mask(cudaStream_t st, float* mask, int64_t n, float p, uint64_t seed, uint64_t offset,
+                         uint64_t* state = nullptr, const float* x = nullptr, int64_t x_ld = 0, int cols = 1,
+                         float* y = nullptr);
+// loss_out = {a+b, a, b, n_valid}; a = NaN when n_valid == 0 or any bad_rows[i] != 0
+cudaError_t finalize_loss(cudaStream_t st, const float* ce_sum, const float* reg, const float* n_valid, float* loss_out,
+                          const int32_t* bad_rows = nullptr, int n_bad = 0);
 
 // ---- decode (decode.cu)
 // per row argmax over logits[B,C] (row stride ld); first max wins (torch.argmax semantics)

@@ -8,26 +8,49 @@ namespace alexcap {
 // get_target (AlexCap/AttentionLanguageModule.py:197-212, AlexCap/LanguageModule.py:113-128): both variants, written
 // batch-major [B,S] (the reference layout) and time-major [S,B] (what the per-step kernels index).
 // The reference runs a Python double loop with one device sync per element; this is one thread per caption.
-__global__ void make_target_kernel(const int32_t* __restrict__ gt, int B, int T, int start_tok, int end_tok,
-                                   int32_t* in_bm, int32_t* tgt_bm, int32_t* in_tm, int32_t* tgt_tm) {
+__global__ void make_target_kernel(const int32_t* __restrict__ gt, int B, int T, int start_tok, int end_tok, int n_classes,
+                                   int32_t* in_bm, int32_t* tgt_bm, int32_t* in_tm, int32_t* tgt_tm, int32_t* bad_rows) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= B) return;
   const int S = T + 1;
   bool placed = false;
+  int bad = 0;
   for (int t = 0; t < S; ++t) {
-    const int in_v = (t == 0) ? start_tok : gt[(int64_t)b * T + t - 1];
+    int in_v = (t == 0) ? start_tok : gt[(int64_t)b * T + t - 1];
     int tg = (t < T) ? gt[(int64_t)b * T + t] : 0;
+    // A token outside [0, n_classes) would index the embedding / logits out of bounds (torch raises a device-side assert):
+    // it is replaced by 0 here so that no kernel reads or writes out of range, and the row is reported in bad_rows, which
+    // makes finalize_loss return NaN.
+    if (n_classes > 0) {
+      if ((unsigned)in_v >= (unsigned)n_classes) { in_v = 0; bad = 1; }
+      if ((unsigned)tg >= (unsigned)n_classes) { tg = 0; bad = 1; }
+    }
     if (t >= 1 && !placed && tg == 0) { tg = end_tok; placed = true; }   // first 0 at index >= 1 becomes END
     if (in_bm) in_bm[(int64_t)b * S + t] = in_v;
     if (tgt_bm) tgt_bm[(int64_t)b * S + t] = tg;
     if (in_tm) in_tm[(int64_t)t * B + b] = in_v;
     if (tgt_tm) tgt_tm[(int64_t)t * B + b] = tg;
   }
+  if (bad_rows) bad_rows[b] = bad;
 }
 cudaError_t make_target(cudaStream_t st, const int32_t* gt, int B, int T, int start_tok, int end_tok,
-                        int32_t* in_bm, int32_t* tgt_bm, int32_t* in_tm, int32_t* tgt_tm) {
+                        int32_t* in_bm, int32_t* tgt_bm, int32_t* in_tm, int32_t* tgt_tm, int n_classes, int32_t* bad_rows) {
   if (B <= 0) return cudaSuccess;
-  ALEXCAP_NOTE_LAUNCH(); make_target_kernel<<<ceil_div(B, 128), 128, 0, st>>>(gt, B, T, start_tok, end_tok, in_bm, tgt_bm, in_tm, tgt_tm);
+  ALEXCAP_NOTE_LAUNCH(); make_target_kernel<<<ceil_div(B, 128), 128, 0, st>>>(gt, B, T, start_tok, end_tok, n_classes, in_bm, tgt_bm, in_tm, tgt_tm, bad_rows);
+  return cudaGetLastError();
+}
+
+// N_valid of get_target(gt, make_target=True) straight from the captions: every row keeps its non-zero tokens and gets
+// exactly one END (the first 0 at index >= 1 of [gt..., 0]), so N_valid = nnz(gt) + B.
+__global__ void __launch_bounds__(256) count_valid_targets_kernel(const int32_t* __restrict__ gt, int B, int T, float* __restrict__ out) {
+  __shared__ float scratch[40];
+  float c = 0.f;
+  for (int64_t i = threadIdx.x; i < (int64_t)B * T; i += blockDim.x) c += (gt[i] != 0) ? 1.f : 0.f;
+  c = block_sum(c, scratch);
+  if (threadIdx.x == 0) out[0] = c + (float)B;
+}
+cudaError_t count_valid_targets(cudaStream_t st, const int32_t* gt, int B, int T, float* out) {
+  ALEXCAP_NOTE_LAUNCH(); count_valid_targets_kernel<<<1, 256, 0, st>>>(gt, B, T, out);
   return cudaGetLastError();
 }
 
@@ -317,8 +340,12 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
   }
   return ctr;
 }
+// state != NULL: {seed, offset} are read from the device (graph replays draw fresh masks; philox_advance bumps offset)
 __global__ void __launch_bounds__(256) dropout_mask_kernel(float* __restrict__ mask, int64_t n, float p, float scale,
-                                                           uint64_t seed, uint64_t offset) {
+                                                           uint64_t seed, uint64_t offset, const uint64_t* __restrict__ state,
+                                                           const float* __restrict__ x, int64_t x_ld, int cols,
+                                                           float* __restrict__ y) {
+  if (state) { seed = state[0]; offset = state[1]; }
   const int64_t n4 = (n + 3) / 4;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
     const uint64_t c = offset + (uint64_t)i;
@@ -330,25 +357,42 @@ __global__ void __launch_bounds__(256) dropout_mask_kernel(float* __restrict__ m
       const int64_t e = i * 4 + j;
       if (e < n) {
         const float u = (float)(rr[j] >> 8) * (1.0f / 16777216.0f);   // [0,1)
-        mask[e] = (u >= p) ? scale : 0.f;
+        const float mk = (u >= p) ? scale : 0.f;
+        mask[e] = mk;
+        if (y) y[e] = mk * x[(e / cols) * x_ld + (e % cols)];           // fused dropout(h): y = mask * x
       }
     }
   }
 }
-cudaError_t dropout_mask(cudaStream_t st, float* mask, int64_t n, float p, uint64_t seed, uint64_t offset) {
+__global__ void philox_advance_kernel(uint64_t* state, uint64_t by) { state[1] += by; }
+cudaError_t dropout_mask(cudaStream_t st, float* mask, int64_t n, float p, uint64_t seed, uint64_t offset, uint64_t* state,
+                         const float* x, int64_t x_ld, int cols, float* y) {
   if (n <= 0) return cudaSuccess;
   const int64_t n4 = (n + 3) / 4;
   const int blocks = (int)(((n4 + 255) / 256 < 8192) ? (n4 + 255) / 256 : 8192);
-  ALEXCAP_NOTE_LAUNCH(); dropout_mask_kernel<<<blocks, 256, 0, st>>>(mask, n, p, 1.f / (1.f - p), seed, offset);
+  ALEXCAP_NOTE_LAUNCH(); dropout_mask_kernel<<<blocks, 256, 0, st>>>(mask, n, p, 1.f / (1.f - p), seed, offset, state, x, x_ld, cols, y);
+  ACK(cudaGetLastError());
+  if (state) {            // same stream: ordered after every reader of the old counter
+    ALEXCAP_NOTE_LAUNCH(); philox_advance_kernel<<<1, 1, 0, st>>>(state, (uint64_t)1 << 32);
+  }
   return cudaGetLastError();
 }
 
-__global__ void finalize_loss_kernel(const float* ce_sum, const float* reg, const float* n_valid, float* out) {
-  const float a = ce_sum ? ce_sum[0] : 0.f, b = reg ? reg[0] : 0.f;
-  out[0] = a + b; out[1] = a; out[2] = b; out[3] = n_valid ? n_valid[0] : 0.f;
+// loss_out = {ce + reg, ce, reg, n_valid}.  ce is NaN when no target is valid (the reference's mean over zero rows,
+// CustomLoss.py:7) or when make_target flagged an out-of-range token (bad_rows[0..n_bad)).
+__global__ void finalize_loss_kernel(const float* ce_sum, const float* reg, const float* n_valid, float* out,
+                                     const int32_t* bad_rows, int n_bad) {
+  float a = ce_sum ? ce_sum[0] : 0.f;
+  const float b = reg ? reg[0] : 0.f;
+  const float nv = n_valid ? n_valid[0] : 0.f;
+  bool bad = n_valid && nv == 0.f;
+  for (int i = 0; bad_rows && i < n_bad; ++i) bad |= bad_rows[i] != 0;
+  if (bad) a = __int_as_float(0x7fc00000);
+  out[0] = a + b; out[1] = a; out[2] = b; out[3] = nv;
 }
-cudaError_t finalize_loss(cudaStream_t st, const float* ce_sum, const float* reg, const float* n_valid, float* loss_out) {
-  ALEXCAP_NOTE_LAUNCH(); finalize_loss_kernel<<<1, 1, 0, st>>>(ce_sum, reg, n_valid, loss_out);
+cudaError_t finalize_loss(cudaStream_t st, const float* ce_sum, const float* reg, const float* n_valid, float* loss_out,
+                          const int32_t* bad_rows, int n_bad) {
+  ALEXCAP_NOTE_LAUNCH(); finalize_loss_kernel<<<1, 1, 0, st>>>(ce_sum, reg, n_valid, loss_out, bad_rows, n_bad);
   return cudaGetLastError();
 }
 

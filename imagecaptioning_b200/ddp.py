@@ -8,6 +8,12 @@ buffer laid out in gradient-finalisation order, so buckets are contiguous slices
     group 1  lstm.*, embedding           final right after the chain (phase 4)
     group 2  everything else             final at the end (phase 8)
 `allreduce()` averages the whole buffer; `step_overlapped()` all-reduces group g on a side stream while phase g+1 runs.
+
+Ragged captions: CustomLoss.py:7 is a mean over the NON-IGNORED targets, so a rank's CE divisor must be the global
+N_valid / world for the AVERAGED gradient to equal the single-process gradient on the concatenated batch.
+`step_overlapped()` therefore counts the local N_valid from the staged captions (alexcap_count_valid_targets), averages that
+one float over the ranks on the side stream while the forward recurrence (phase 16) runs, and hands it to phase 32
+(vocabulary projection + loss) as `ce_denominator` -- all inside the captured whole-step graph.
 """
 from __future__ import annotations
 
@@ -53,15 +59,24 @@ class GradAllReducer:
         chain runs, group 1 (lstm.*, embedding) WHILE the remaining gradients are computed; only the small last group
         is exposed.  Returns the loss tensor."""
         step = self.step
-        if self.world <= 1 or not step.is_attn:
+        if self.world <= 1:
+            return step.run_resident()
+        if not step.is_attn:                                 # plain LSTM: one phase; the divisor exchange is exposed (1 float)
+            from . import functional as F_
+            F_.count_valid_targets(step._gt, out=step._slot.n_valid)
+            self._reduce(step._slot.n_valid)
+            step.ce_denominator = step._slot.n_valid
             loss = step.run_resident()
             self.allreduce()
             return loss
-        if self._graph_ok and step.use_cuda_graph and step._dims.dropout_p == 0:
-            # the whole step -- three phase launches, the side-stream fork / join and the NCCL all-reduces -- as ONE graph
-            key = step._cur
-            if key in self._graphs:
-                self._graphs[key].replay()
+        step.ce_denominator = step._slot.n_valid            # (part of the graph key: set before any launch of this step)
+        if self._graph_ok and step.use_cuda_graph:
+            # the whole step -- the phase launches, the side-stream forks / joins and the NCCL all-reduces -- as ONE graph
+            step._sync_dims()
+            key = step._graph_key('ddp')
+            graphs = self._graphs.setdefault(id(step._slot), {})
+            if key in graphs:
+                graphs[key].replay()
                 return step._loss
             loss = self._run_phases(step, graphs=False)      # this call's step, eagerly (also warms up NCCL and the kernels)
             try:
@@ -69,7 +84,7 @@ class GradAllReducer:
                 g = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(g):
                     self._run_phases(step, graphs=False)
-                self._graphs[key] = g
+                graphs[key] = g
             except Exception as e:                            # capture of the collectives not supported here: phase graphs
                 self._graph_ok = False
                 print(f'[imagecaptioning_b200.ddp] whole-step graph capture failed ({type(e).__name__}: {e}); '
@@ -78,10 +93,18 @@ class GradAllReducer:
         return self._run_phases(step, graphs=True)
 
     def _run_phases(self, step, graphs):
+        from . import functional as F_
         main = torch.cuda.current_stream()
         groups = step.grad_groups()
         run = step.run_resident if graphs else (lambda phase: step._launch(phase))
-        for gi, (phase, g) in enumerate(((1, groups[0]), (4, groups[1]))):
+        # N_valid_global / world -> phase 32's CE divisor; exchanged under the forward recurrence
+        self.side.wait_stream(main)
+        with torch.cuda.stream(self.side):
+            F_.count_valid_targets(step._gt, out=step._slot.n_valid)
+            self._reduce(step._slot.n_valid)
+        run(phase=16)
+        main.wait_stream(self.side)
+        for gi, (phase, g) in enumerate(((32, groups[0]), (4, groups[1]))):
             run(phase=phase)
             self.side.wait_stream(main)
             with torch.cuda.stream(self.side):
@@ -92,6 +115,14 @@ class GradAllReducer:
             self._reduce(groups[2], 2)
         main.wait_stream(self.side)
         return step._loss
+
+    def global_loss(self):
+        """The data-parallel loss of the last step: CE terms sum to the global mean (each rank's CE is already divided by
+        N_valid_global / world), the regulariser is a per-rank mean over equal B*L.  Returns a new 4-vector (AVG over ranks)."""
+        t = self.step._loss.clone()
+        if self.world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.AVG, group=self.group)
+        return t
 
     def global_ce_denominator(self, n_valid_local: torch.Tensor) -> torch.Tensor:
         """N_valid_global / world: with it as the CE divisor on every rank, the AVERAGED gradient equals the

@@ -46,9 +46,13 @@ def ensure_device(device):
 
 
 def make_dims(B, L, D, H, E, Vp, S, num_layers=1, dtype=_lib.F32, need_dfeat=False, label_smoothing=0.1,
-              ignore_index=0, reg_weight=1.0, dropout_p=0.0, seed=0, offset=0) -> Dims:
+              ignore_index=0, reg_weight=1.0, dropout_p=0.0, seed=0, offset=0, philox_state=None) -> Dims:
+    """philox_state: int64 CUDA tensor {seed, offset} -- the dropout counter lives on the device and is advanced there, so a
+    captured CUDA graph draws a fresh mask at every replay (the caller keeps the tensor alive)."""
+    if philox_state is not None and (not philox_state.is_cuda or philox_state.dtype != torch.int64 or philox_state.numel() < 2):
+        raise _lib.AlexcapError('philox_state must be a CUDA int64 tensor with 2 elements {seed, offset}')
     return Dims(B, L, D, H, E, Vp, S, num_layers, dtype, int(bool(need_dfeat)), ignore_index, label_smoothing,
-                reg_weight, dropout_p, seed, offset)
+                reg_weight, dropout_p, seed, offset, None if philox_state is None else philox_state.data_ptr())
 
 
 def attn_param_struct(tensors) -> AttnParams:
@@ -172,6 +176,37 @@ def make_target(gt, vocab_size):
     check(lib.alexcap_make_target(_ptr(gt), _ptr(in_tok), _ptr(tgt), B, T, vocab_size + 1, vocab_size + 2, _stream()),
           'alexcap_make_target')
     return in_tok, tgt
+
+
+def count_valid_targets(gt, out=None):
+    """Number of non-ignored targets get_target(gt, make_target=True) yields (nnz(gt) + B) as a 1-element device float."""
+    lib = ensure_device(gt.device)
+    if gt.dtype != torch.int32:
+        raise _lib.AlexcapError('count_valid_targets takes int32 captions')
+    _req(gt, out)
+    B, T = gt.shape
+    if out is None:
+        out = torch.empty(1, dtype=torch.float32, device=gt.device)
+    check(lib.alexcap_count_valid_targets(_ptr(gt), B, T, _ptr(out), _stream()), 'alexcap_count_valid_targets')
+    return out
+
+
+def mean_over_L(feat):
+    """[B, L, D] -> [B, D] mean over regions (Decoder.get_init_lstm_state, AttentionLanguageModule.py:117)."""
+    lib = ensure_device(feat.device)
+    _req(feat)
+    B, L, D = feat.shape
+    m = torch.empty(B, D, dtype=torch.float32, device=feat.device)
+    check(lib.alexcap_mean_over_L(_ptr(feat), B, L, D, _ptr(m), _stream()), 'alexcap_mean_over_L')
+    return m
+
+
+def attn_workspace_region(dims: Dims, ws: torch.Tensor, name: str, shape) -> torch.Tensor:
+    """fp32 view of a named region of an attention training workspace (test / introspection hook)."""
+    off, n = C.c_size_t(0), C.c_size_t(0)
+    check(_lib.load().alexcap_attn_workspace_region(C.byref(dims), name.encode(), C.byref(off), C.byref(n)),
+          'alexcap_attn_workspace_region')
+    return ws[off.value:off.value + n.value].view(torch.float32).view(*shape)
 
 
 def cross_entropy(logits2d, tgt, label_smoothing=0.1, ignore_index=0, want_grad=True):

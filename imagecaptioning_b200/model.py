@@ -17,7 +17,14 @@ from . import functional as F_
 from .modules import Decoder, LanguageModel, _f32c
 
 
+class _Slot:
+    """Everything that depends on the batch SHAPE: dims, workspace, loss cell, the two static input sets, captured graphs."""
+    __slots__ = ('dims', 'ws', 'loss', 'feats', 'gts', 'dfeat', 'graphs', 'cur', 'copied', 'consumed', 'n_valid', 'ce_den')
+
+
 class DecoderTrainStep:
+    MAX_SLOTS = 4                            # batch shapes kept alive (a loader's partial last batch gets its own slot)
+
     def __init__(self, llm, use_cuda_graph: bool = False, need_dfeat: bool = False):
         if not isinstance(llm, (Decoder, LanguageModel)):
             raise TypeError('llm must be an imagecaptioning_b200 Decoder or LanguageModel')
@@ -28,13 +35,12 @@ class DecoderTrainStep:
         self.eval_mode = False
         self.ce_denominator = None          # device float tensor: global N_valid / world (data parallel), or None
         self._key = None
-        self._graphs = {}                   # (input set, phase) -> captured CUDA graph
-        self._cur = 0
+        self._slots = {}                    # shape key -> _Slot (insertion order = age)
+        self._slot = None
+        self._param_dev = None
         self._copy_stream = None
-        self._copied = [None, None]         # event: H2D into buffer i finished (copy stream)
-        self._consumed = [None, None]       # event: last step reading buffer i finished (compute stream)
+        self._philox = None                 # int64 {seed, offset} on the device: the dropout counter (advanced by the library)
         self.last_alphas = None
-        self.dfeat = None
 
     # -- reference API ---------------------------------------------------------------------------------
     def set_eval(self, value: bool):
@@ -45,13 +51,14 @@ class DecoderTrainStep:
         torch.nn.utils.clip_grad_norm_(self.llm.parameters(), max_norm=norm)
 
     # -- internals --------------------------------------------------------------------------------------
-    def _prepare(self, feat, gt, dev=None):
-        dev = dev if dev is not None else feat.device
-        key = (tuple(feat.shape), tuple(gt.shape), dev, self.llm.training, self.need_dfeat)
-        if key == self._key:
+    def _drop_p(self):
+        return float(self.llm._train_dropout_p()) if self.llm.training else 0.0
+
+    def _prepare_params(self, dev):
+        if self._param_dev == dev:
             return
-        self._key, self._graphs, self._cur = key, {}, 0
-        self._copied, self._consumed = [None, None], [None, None]
+        self._param_dev = dev
+        self._slots, self._slot, self._key = {}, None, None
         F_.ensure_device(dev)
         self._params = self.llm.param_list()
         for p in self._params:
@@ -73,47 +80,111 @@ class DecoderTrainStep:
                 self._vocab_elems = off
             for gi in range(self._group(i), 3):
                 self._group_end[gi] = off
-        self._dims = self.llm._dims(feat, gt, need_dfeat=self.need_dfeat)
-        nbytes = F_.attn_workspace_bytes(self._dims) if self.is_attn else F_.lstm_workspace_bytes(self._dims)
-        self._ws = F_.workspace(nbytes, dev)
-        self._loss = torch.zeros(4, dtype=torch.float32, device=dev)
-        # two static input buffer sets: the step reads set `_cur` while prefetch() fills the other one
-        self._feats = [torch.empty(feat.shape, dtype=torch.float32, device=dev) for _ in range(2)]
-        self._gts = [torch.empty(gt.shape, dtype=torch.int32, device=dev) for _ in range(2)]
-        self.dfeat = torch.empty_like(self._feat) if self.need_dfeat else None
-        self._alphas = None
+        # dropout counter on the device: seeded from torch's generator (torch.manual_seed reproducibility), offset 0
+        self._philox = torch.tensor([int(torch.randint(0, 2 ** 62, (1,)).item()), 0], dtype=torch.int64, device=dev)
+
+    def _prepare(self, feat, gt, dev=None):
+        dev = dev if dev is not None else feat.device
+        self._prepare_params(dev)
+        # everything a workspace LAYOUT depends on; what only changes the captured work (compute dtype, ce_denominator,
+        # an injected mask) is part of the graph key instead (see _graph_key)
+        key = (tuple(feat.shape), tuple(gt.shape), self.need_dfeat, self._drop_p() > 0)
+        if key == self._key:
+            return
+        self._key = key
+        slot = self._slots.pop(key, None)
+        if slot is None:
+            while len(self._slots) >= self.MAX_SLOTS:           # drop the oldest shape (its graphs and buffers with it)
+                self._slots.pop(next(iter(self._slots)))
+            slot = _Slot()
+            slot.dims = self.llm._dims(feat, gt, need_dfeat=self.need_dfeat)
+            nbytes = F_.attn_workspace_bytes(slot.dims) if self.is_attn else F_.lstm_workspace_bytes(slot.dims)
+            slot.ws = F_.workspace(nbytes, dev)
+            slot.loss = torch.zeros(4, dtype=torch.float32, device=dev)
+            # two static input buffer sets: the step reads set `cur` while prefetch() fills the other one
+            slot.feats = [torch.empty(feat.shape, dtype=torch.float32, device=dev) for _ in range(2)]
+            slot.gts = [torch.empty(gt.shape, dtype=torch.int32, device=dev) for _ in range(2)]
+            slot.dfeat = torch.empty(feat.shape, dtype=torch.float32, device=dev) if self.need_dfeat else None
+            slot.graphs, slot.cur = {}, 0
+            slot.copied, slot.consumed = [None, None], [None, None]
+            slot.n_valid = torch.zeros(1, dtype=torch.float32, device=dev)    # data parallel: local, then global / world
+        self._slots[key] = slot                                  # (re)insert as the youngest
+        self._slot = slot
+
+    # the current slot's members under their historical names
+    _dims = property(lambda self: self._slot.dims)
+    _ws = property(lambda self: self._slot.ws)
+    _loss = property(lambda self: self._slot.loss)
+    _feats = property(lambda self: self._slot.feats)
+    _gts = property(lambda self: self._slot.gts)
+    _graphs = property(lambda self: self._slot.graphs)
+    _copied = property(lambda self: self._slot.copied)
+    _consumed = property(lambda self: self._slot.consumed)
+    dfeat = property(lambda self: self._slot.dfeat if self._slot is not None else None)
+    _alphas = None
+
+    @property
+    def _cur(self):
+        return self._slot.cur
+
+    @_cur.setter
+    def _cur(self, v):
+        self._slot.cur = v
 
     @property
     def _feat(self):
-        return self._feats[self._cur]
+        return self._slot.feats[self._slot.cur]
 
     @property
     def _gt(self):
-        return self._gts[self._cur]
+        return self._slot.gts[self._slot.cur]
+
+    def _sync_dims(self):
+        """Settings that may change between steps without changing the workspace layout are written into dims at every
+        launch (and are part of the graph key): compute dtype, dropout p, the dropout counter."""
+        d = self._slot.dims
+        d.dtype = F_._lib.BF16 if getattr(self.llm, 'compute_dtype', 'f32') == 'bf16' else F_._lib.F32
+        p = self._drop_p()
+        if (p > 0) != (d.dropout_p > 0):
+            raise F_._lib.AlexcapError('dropout was switched on/off without re-staging the batch (the workspace layout differs)')
+        d.dropout_p = p
+        d.philox_state = self._philox.data_ptr() if (p > 0 and self.llm._drop_mask_override is None) else None
+        return d
+
+    def _graph_key(self, phase):
+        d = self._slot.dims
+        mask = self.llm._drop_mask_override
+        den = self.ce_denominator
+        return (self._slot.cur, phase, int(d.dtype), float(d.dropout_p), None if mask is None else mask.data_ptr(),
+                None if den is None else den.data_ptr())
 
     def _launch(self, phase=3):
-        d = self._dims
-        if d.dropout_p > 0 and phase in (1, 3):   # fresh mask every step (Philox counter advances)
-            d.offset += 1 << 32
+        d = self._sync_dims()
         mask = self.llm._drop_mask_override
         if self.is_attn:
             F_.attn_train_fused(d, self._params, self._feat, self._gt, self._grads, self._ws, dfeat=self.dfeat,
                                 loss_out=self._loss, alphas_out=self._alphas, drop_mask=mask,
                                 ce_denominator=self.ce_denominator, phase=phase)
-        elif phase in (2, 4, 8):
-            return                               # plain LSTM: one call does the whole step (phase 1)
+        elif phase in (2, 4, 8, 32):
+            return                               # plain LSTM: one call does the whole step (phase 1 / 16)
         else:
             P = self.llm._struct(self._params)
             G = self.llm._struct(self._grads)
             F_.lstm_train_fused(d, P, self._feat, self._gt, G, self._ws, dfeat=self.dfeat, loss_out=self._loss,
                                 drop_mask=mask, ce_denominator=self.ce_denominator)
 
+    # phases whose saved state a warm-up run of `phase` consumes (gates -> dgates in place, accumulations): re-run after it
+    _PREREQ = {2: (1,), 4: (1,), 8: (1, 4), 32: (16,)}
+
     def run_resident(self, phase=3):
         """One step on the inputs already staged in the static device buffers (bench: inputs resident in HBM).
-        phase=1 then phase=2 -- or 1, 4, 8 (the two halves of 2) -- run the same step in several launches (see
-        GradAllReducer.step_overlapped)."""
-        if self.use_cuda_graph and self._dims.dropout_p == 0:
-            key = (self._cur, phase)
+        phase=1 then phase=2 -- or 16, 32, 4, 8 (the halves of 1 and of 2) -- run the same step in several launches (see
+        GradAllReducer.step_overlapped).  With use_cuda_graph every (input set, phase, compute dtype, dropout p, injected
+        mask, ce_denominator) combination is captured once and replayed; dropout p > 0 is captured too (the Philox counter
+        lives on the device and advances at every replay)."""
+        if self.use_cuda_graph:
+            self._sync_dims()
+            key = self._graph_key(phase)
             if key not in self._graphs:
                 s = torch.cuda.Stream()
                 s.wait_stream(torch.cuda.current_stream())
@@ -124,8 +195,7 @@ class DecoderTrainStep:
                 with torch.cuda.graph(g):
                     self._launch(phase)
                 self._graphs[key] = g
-                # the warm-up consumed the saved state of the earlier phases (gates -> dgates in place, accumulations)
-                for prev in {2: (1,), 4: (1,), 8: (1, 4)}.get(phase, ()):
+                for prev in self._PREREQ.get(phase, ()):
                     self._launch(prev)
             self._graphs[key].replay()
         else:
@@ -167,14 +237,32 @@ class DecoderTrainStep:
         """forward_train on the backbone's NCHW output.  With need_dfeat=True, `dfeat_nchw()` afterwards returns the
         gradient w.r.t. `cnn_out` in its own layout (the fine-tune phase, train_LSTMwAttention.py:51-55)."""
         self.stage_nchw(cnn_out, gt_labels)
+        self._unalias_grads()
         loss4 = self.run_resident()
-        for p, g in zip(self._params, self._grads):
-            if p.requires_grad:
-                if p.grad is None:
-                    p.grad = g.clone()
-                else:
-                    p.grad.add_(g)
+        self._publish_grads()
         return loss4[0]
+
+    def _unalias_grads(self):
+        """A .grad that still IS a slice of the flat gradient buffer (the caller did not zero_grad(set_to_none=True) since the
+        previous step) is about to be overwritten: give it its own storage so that accumulation semantics hold."""
+        for p, g in zip(self._params, self._grads):
+            if p.grad is not None and p.grad.data_ptr() == g.data_ptr():
+                p.grad = p.grad.clone()
+
+    def _publish_grads(self):
+        """loss.backward() semantics on .grad (LSTMwAttentionModel.py:72) without a copy in the common case: after
+        optim.zero_grad(set_to_none=True) (train_LSTMwAttention.py:80) every .grad is None and simply BECOMES the slice of
+        the flat gradient buffer the step wrote (valid until the next forward_train); otherwise one multi-tensor add."""
+        acc_dst, acc_src = [], []
+        for p, g in zip(self._params, self._grads):
+            if not p.requires_grad:
+                continue
+            if p.grad is None:
+                p.grad = g
+            else:
+                acc_dst.append(p.grad); acc_src.append(g)
+        if acc_dst:
+            torch._foreach_add_(acc_dst, acc_src)
 
     def dfeat_nchw(self, out=None, accumulate=False):
         if self.dfeat is None:
@@ -185,8 +273,8 @@ class DecoderTrainStep:
         """Start the H2D copy of the NEXT batch (pinned host tensors) into the idle input buffer set on a side stream,
         so that it overlaps the step running on the current set.  Pair with swap()+run_resident()."""
         dev = next(self.llm.parameters()).device
-        if self._key is None:
-            self.stage(features, gt_labels)     # first call sizes the buffers
+        if self._slot is None or tuple(features.shape) != tuple(self._feat.shape) or tuple(gt_labels.shape) != tuple(self._gt.shape):
+            self.stage(features, gt_labels)     # first call of a shape sizes (or re-selects) the buffers
         if features.dtype != torch.float32 or gt_labels.dtype != torch.int32:
             raise F_._lib.AlexcapError('prefetch() takes float32 features and int32 captions')
         if self._copy_stream is None:
@@ -220,13 +308,9 @@ class DecoderTrainStep:
         if self.eval_mode:
             return self.forward_eval(features, gt_labels)
         self.stage(features, gt_labels)
+        self._unalias_grads()
         loss4 = self.run_resident()
-        for p, g in zip(self._params, self._grads):
-            if p.requires_grad:
-                if p.grad is None:
-                    p.grad = g.clone()
-                else:
-                    p.grad.add_(g)
+        self._publish_grads()
         return loss4[0]
 
     @torch.no_grad()

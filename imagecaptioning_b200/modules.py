@@ -183,6 +183,9 @@ class Decoder(nn.Module, _DecodeMixin):
         sd = dict(self.named_parameters())
         return [sd[n] for n in ATTN_STATE_NAMES]
 
+    def _train_dropout_p(self):
+        return self.dropout.p
+
     def _dims(self, feat, gt=None, need_dfeat=False, train_dropout=True):
         B, L, D = feat.shape
         if D != self.image_vector_dim:
@@ -211,7 +214,7 @@ class Decoder(nn.Module, _DecodeMixin):
     def get_init_lstm_state(self, img_features):
         """:116-125 (inference helper): h0, c0."""
         with torch.no_grad():
-            m = _f32c(img_features).mean(dim=1).contiguous()   # tiny; the train path uses the mean_over_L kernel
+            m = F_.mean_over_L(_f32c(img_features))             # mean_L_kernel, the kernel the train path uses
             h = F_.gemm(m, _f32c(self.init_h.weight), bias=_f32c(self.init_h.bias), act=1)
             c = F_.gemm(m, _f32c(self.init_c.weight), bias=_f32c(self.init_c.bias), act=1)
         return h, c
@@ -312,6 +315,9 @@ class LanguageModel(nn.Module, _DecodeMixin):
         return F_.lstm_param_struct(tensors[0], tensors[1], tensors[2], tensors[3], tensors[4],
                                     [rest[4 * l] for l in range(nl)], [rest[4 * l + 1] for l in range(nl)],
                                     [rest[4 * l + 2] for l in range(nl)], [rest[4 * l + 3] for l in range(nl)])
+
+    def _train_dropout_p(self):
+        return self.rnn.drop.p
 
     def _dims(self, feat, gt=None, need_dfeat=False, train_dropout=True):
         B, L, D = feat.shape

@@ -8,8 +8,13 @@
  * binds this header with ctypes (imagecaptioning_b200/_lib.py); INTEGRATION.md shows the stub.
  *
  * Conventions
- *   - plain pointers + sizes only; every buffer is a DEVICE buffer owned by the caller (torch);
- *     the library never allocates or frees device memory and keeps no pointer after return.
+ *   - plain pointers + sizes only; every buffer a call reads or writes is a DEVICE buffer owned by the caller (torch),
+ *     and the library keeps no caller pointer after return.  The training / decode entry points never allocate or free
+ *     device memory per call; the only device memory the library owns is one process-lifetime scratch per GPU for the
+ *     attention kernels' cross-CTA combine (grown on the first call that needs more, never freed or moved, so captured
+ *     graphs stay valid -- do the first call of a shape outside stream capture), and the operand-copy arena of the
+ *     test / micro-benchmark hook alexcap_gemm_f32 with engine >= 300 (that hook may synchronise the device when it
+ *     grows and is not capturable then).
  *   - all work is enqueued on `stream` (a cudaStream_t passed as void*), asynchronously, with no
  *     device-wide synchronisation: a call is capturable into a CUDA graph.
  *   - return 0 on success; <0 on failure (ALEXCAP_E_*), message via alexcap_last_error().
@@ -30,7 +35,7 @@
 extern "C" {
 #endif
 
-#define ALEXCAP_ABI_VERSION 1
+#define ALEXCAP_ABI_VERSION 2
 
 #if defined(__GNUC__)
 #define ALEXCAP_API __attribute__((visibility("default")))
@@ -55,7 +60,11 @@ typedef struct alexcap_dims {
   float   label_smoothing;         /* CustomLoss.py:7 -> 0.1 */
   float   reg_weight;              /* LSTMwAttentionModel.py:70-71 -> 1.0 (0 disables the regulariser) */
   float   dropout_p;               /* AttentionLanguageModule.py:54 -> 0.5 in train(), 0 in eval() */
-  uint64_t seed, offset;           /* Philox counter for the dropout mask when drop_mask == NULL */
+  uint64_t seed, offset;           /* Philox counter for the dropout mask when drop_mask == NULL and philox_state == NULL */
+  uint64_t* philox_state;          /* DEVICE {seed, offset} or NULL.  When set (and drop_mask == NULL) the mask kernel reads
+                                      the counter from the device and the call advances `offset` ON the device afterwards, so
+                                      a captured CUDA graph draws a fresh mask at every replay (the reference's train() mode:
+                                      nn.Dropout() p = 0.5, AttentionLanguageModule.py:54,79). */
 } alexcap_dims;
 
 /* Parameters of AlexCap.AttentionLanguageModule.Decoder (AttentionLanguageModule.py:46-58), state_dict order.
@@ -127,7 +136,10 @@ ALEXCAP_API int alexcap_attn_train_fused(const alexcap_dims* dims, const alexcap
  * single-GPU and has no counterpart).  phase 1: forward + loss + vocab backward; phase 2: reverse-time chain and all
  * other weight gradients (same arguments and workspace as phase 1); phase 3: both (== alexcap_attn_train_fused).
  * Phase 2 may itself be run as phase 4 (reverse-time chain, then the lstm.* and embedding gradients) followed by phase 8
- * (all remaining gradients), so that the second-largest gradient group can be exchanged while phase 8 runs. */
+ * (all remaining gradients), so that the second-largest gradient group can be exchanged while phase 8 runs.
+ * Phase 1 may itself be run as phase 16 (targets + the teacher-forced forward recurrence) followed by phase 32 (vocabulary
+ * projection, loss, vocabulary backward, regulariser): `ce_denominator` is only read by phase 32, so a data-parallel caller
+ * can all-reduce N_valid (alexcap_count_valid_targets) on a side stream while phase 16 runs. */
 ALEXCAP_API int alexcap_attn_train_phase(const alexcap_dims* dims, const alexcap_attn_params* params,
                              const float* feat, const int32_t* gt,
                              const alexcap_attn_params* grads, float* dfeat,
@@ -147,6 +159,14 @@ ALEXCAP_API int alexcap_attn_backward(const alexcap_dims* dims, const alexcap_at
                           const float* feat, const float* dpreds, const float* dalphas,
                           const alexcap_attn_params* grads, float* dfeat,
                           void* workspace, size_t workspace_bytes, void* stream);
+
+/* Test / introspection hook: byte offset and size of a named region of the attention training workspace for `dims`
+ * ("MASK": the [S,B,H] dropout mask the last step drew; "ALPHA": [B,S,L]; "H": [S+1,B,D+H] slots [gctx_t | h_{t-1}]).
+ * Returns 0, or ALEXCAP_E_BADARG for an unknown name / a region this `dims` does not have. */
+ALEXCAP_API int alexcap_attn_workspace_region(const alexcap_dims* dims, const char* name, size_t* offset, size_t* bytes);
+
+/* m[b,:] = mean_l feat[b,l,:]  (Decoder.get_init_lstm_state, AttentionLanguageModule.py:117).  feat [B,L,D], m [B,D]. */
+ALEXCAP_API int alexcap_mean_over_L(const float* feat, int32_t B, int32_t L, int32_t D, float* m, void* stream);
 
 /* ------------------------------------------------------------------ plain LSTM decoder (train) ---------- */
 ALEXCAP_API size_t alexcap_lstm_workspace_bytes(const alexcap_dims* dims);
@@ -172,6 +192,11 @@ ALEXCAP_API int alexcap_lstm_backward(const alexcap_dims* dims, const alexcap_ls
  * Either output may be NULL. */
 ALEXCAP_API int alexcap_make_target(const int32_t* gt, int32_t* in_tok, int32_t* tgt, int32_t B, int32_t T,
                         int32_t start_token, int32_t end_token, void* stream);
+
+/* Number of non-ignored targets get_target(gt, make_target=True) yields for gt [B,T] (ignore_index 0): nnz(gt) + B (every
+ * row gets exactly one END).  n_valid_out: 1 device float.  The divisor of CustomLoss.py:7's reduction='mean'; data-parallel
+ * callers all-reduce it and hand N_valid_global / world to the training entry points as `ce_denominator`. */
+ALEXCAP_API int alexcap_count_valid_targets(const int32_t* gt, int32_t B, int32_t T, float* n_valid_out, void* stream);
 
 /* CustomCrossEntropyLoss.forward (CustomLoss.py:9-15) on logits [N,C] (row stride ld), targets [N] int32.
  * loss_out[2] (device) = {mean loss over non-ignored rows, n_valid}; dlogits [N,C] (row stride ld) or NULL

@@ -26,13 +26,13 @@ def test_library_builds_and_exports_every_header_symbol():
     assert exported == set(names), (sorted(exported - set(names)), sorted(set(names) - exported))
     assert set(_lib.PROTOTYPES) == set(names)            # the ctypes binding covers the whole header
     lib = _lib.load()
-    assert lib.alexcap_abi_version() == 1
+    assert lib.alexcap_abi_version() == 2
 
 
 def test_struct_layout_matches_header():
     from imagecaptioning_b200 import _lib
     # 10 int32 + 3 float... : B,L,D,H,E,Vp,S,num_layers,dtype,need_dfeat,ignore_index (11 x 4) + 3 floats + pad + 2 x u64
-    assert C.sizeof(_lib.Dims) == 72
+    assert C.sizeof(_lib.Dims) == 80      # ABI 2: + uint64_t* philox_state
     assert C.sizeof(_lib.AttnParams) == 19 * 8
     assert C.sizeof(_lib.LstmParams) == (5 + 4 * 8) * 8
     d = _lib.Dims(2, 3, 4, 4, 4, 8, 3, 1, 0, 0, 0, 0.1, 1.0, 0.0, 0, 0)
