@@ -103,8 +103,8 @@ def algorithmic_work(c):
     f_fwd = (2 * B * L * D * H + 4 * B * D * H + 2 * B * S * E * 4 * H
              + S * (2 * B * H * H + 2 * B * H * D + 2 * B * D * 4 * H + 2 * B * H * 4 * H) + 2 * B * S * H * Vp)
     f_step = 3 * f_fwd - 2 * B * L * D * H - 2 * B * D * H
-    e = 4
-    attn_fwd_step = B * L * (H + D) * e + B * L * 4 + B * (H + D) * e
+    e = 2 if c['dtype'] == 'bf16' else 4     # bf16 configs stream Ws / feat as bf16 rows (e = 2)
+    attn_fwd_step = B * L * (H + D) * e + B * L * 4 + B * (H + D) * 4
     attn_bwd_step = B * L * (H + D) * e
     return dict(gemm_flops_step=f_step, attn_fwd_bytes_per_launch=attn_fwd_step, attn_bwd_bytes_per_launch=attn_bwd_step)
 
@@ -158,9 +158,13 @@ def dominant_kernel_roofline(c, dev, pk):
     B, L, D, H, S = c['B'], c['L'], c['D'], c['H'], c['T'] + 1
     g = torch.Generator(device='cpu').manual_seed(1)
     sets = []
-    nsets = 2 if B * L * (H + D) * 4 * 2 > 140e6 else max(2, int(160e6 // (B * L * (H + D) * 4)) + 1)
+    esz = 2 if c['dtype'] == 'bf16' else 4
+    nsets = 2 if B * L * (H + D) * esz * 2 > 140e6 else max(2, int(160e6 // (B * L * (H + D) * esz)) + 1)
     for _ in range(nsets):
-        sets.append((torch.randn(B, L, H, generator=g).to(dev), torch.randn(B, L, D, generator=g).relu().to(dev)))
+        Ws_, ft_ = torch.randn(B, L, H, generator=g).to(dev), torch.randn(B, L, D, generator=g).relu().to(dev)
+        if c['dtype'] == 'bf16':             # the storage type the training step streams in this mode
+            Ws_, ft_ = Ws_.bfloat16(), ft_.bfloat16()
+        sets.append((Ws_, ft_))
     q = torch.randn(S, B, H, generator=g).to(dev)
     bp = torch.randn(S, B, D, generator=g).to(dev)
     dg = torch.randn(S, B, D, generator=g).to(dev)
@@ -199,7 +203,7 @@ def dominant_kernel_roofline(c, dev, pk):
     out['forward'] = block('attn_fwd_stream_kernel', w['attn_fwd_bytes_per_launch'], *res['fwd'], NCU_TRAFFIC.get('attn_fwd') if is2 else None)
     out['share_of_step'] = 'backward 18.9 %, forward 15.2 % of the cfg2 step (profiles/r1i_step_breakdown.txt)'
     out['note'] = ('achieved = cold (launches alternate over %d distinct Ws/feat sets, %.0f MB each: no L2 reuse); l2_warm = one set '
-                   're-read by every launch (part of it hits the 126 MB L2)' % (nsets, B * L * (H + D) * 4 / 1e6))
+                   're-read by every launch (part of it hits the 126 MB L2)' % (nsets, B * L * (H + D) * esz / 1e6))
     return out
 
 
@@ -484,7 +488,7 @@ def run_decode(args, c, dev, rank, world, local):
             ids_h = one(feat_h.to(dev, non_blocking=True)).cpu()
         e2.record(); torch.cuda.synchronize()
         ms2 = s2.elapsed_time(e2) / args.steps
-        steps_run = int((ids != 0).any(dim=0).sum().item()) if beam == 0 else S
+        steps_run = S               # every token step's kernels run (the all-rows-emitted-END exit is evaluated on the device, no host sync)
         out[name] = dict(ms=ms, ms_e2e=ms2, launches=launches, token_steps=steps_run, d2h=int(ids_h.numel() * 8))
     if rank != 0:
         return
@@ -572,6 +576,23 @@ def main():
                                     slowdown_vs_p0=round(d_ms / ms, 4), gpu_launches_per_step=d_launch, cuda_graph=not args.no_graph,
                                     loss=round(drun.loss, 5))
         drun.close(); del drun
+    if world == 1 and is_attn:
+        # north_star (3): the forward recurrence as ONE persistent weight-stationary kernel (time_loop.cu: LSTM pointwise in the
+        # tcgen05 epilogue, next query GEMM behind a grid barrier).  Built, parity-tested, and measured here next to the default
+        # PDL-chained per-step launches, which are faster on this shape -- so it is opt-in.
+        from imagecaptioning_b200 import functional as F_
+        prev = F_.set_time_loop(True)
+        try:
+            lrun = TrainRun(c, dev, rank, world, dist, graph=not args.no_graph)
+            l_launch = lrun.launches_per_step()
+            l_ms, _ = lrun.time_resident(args.steps, args.warmup)
+            extra['time_loop_kernel'] = dict(ms_per_step=round(l_ms, 4), value=round(total / (l_ms * 1e-3), 1), unit='captions/s',
+                                             gpu_launches_per_step=l_launch, loss=round(lrun.loss, 5),
+                                             used=bool(l_launch < launches_per_step),
+                                             what='alexcap_set_time_loop(1): persistent forward-recurrence kernel instead of 4 launches per time step')
+            del lrun
+        finally:
+            F_.set_time_loop(prev)
     if world == 1:
         ft = run.time_forward_train(args.steps)
         extra['e2e_forward_train'] = dict(

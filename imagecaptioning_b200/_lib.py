@@ -55,6 +55,8 @@ PROTOTYPES = {
     'alexcap_get_gemm_engine': (C.c_int, []),
     'alexcap_attn_workspace_bytes': (_SZ, [_DP]),
     'alexcap_attn_workspace_region': (C.c_int, [_DP, C.c_char_p, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
+    'alexcap_set_time_loop': (C.c_int, [_I32]),
+    'alexcap_time_loop_profile': (C.c_int, [C.POINTER(C.c_ulonglong), _I32]),
     'alexcap_mean_over_L': (C.c_int, [_P, _I32, _I32, _I32, _P, _P]),
     'alexcap_count_valid_targets': (C.c_int, [_P, _I32, _I32, _P, _P]),
     'alexcap_attn_train_fused': (C.c_int, [_DP, _AP, _P, _P, _AP, _P, _P, _P, _P, _P, _P, _SZ, _P]),
@@ -82,9 +84,9 @@ PROTOTYPES = {
     'alexcap_gemm_f32': (C.c_int, [_I32, _I32, _I32, _I32, _I32, _F, _P, _I64, _P, _I64, _P, _I64, _P, _P, _I32, _I32,
                                    _I32, _P]),
     'alexcap_attn_step_fwd': (C.c_int, [_I32, _I32, _I32, _I32, _P, _P, _P, _I64, _P, _I64, _P, _P, _I64, _P, _P, _P,
-                                        _I64, _P]),
+                                        _I64, _I32, _P]),
     'alexcap_attn_step_bwd': (C.c_int, [_I32, _I32, _I32, _I32, _P, _P, _P, _I64, _P, _P, _I64, _P, _P, _P, _I64, _P,
-                                        _I64, _P, _P, _I64, _P, _I64, _P, _I64, _P, _P, _P]),
+                                        _I64, _P, _P, _I64, _P, _I64, _P, _I64, _P, _P, _I32, _P]),
 }
 
 _lib = None

@@ -49,6 +49,8 @@ struct AttnWs {
   float *dHout, *dh_next, *dc, *dgctx, *R, *dwv_part, *dWs, *dEmbIn, *dh0, *dc0, *dm;
   float *cs_scratch, *reg_scratch;
   uint8_t* arena; size_t arena_bytes;   // bf16 hi/lo operand copies of the big GEMMs (training layout only)
+  uint16_t* loop_bf16; unsigned* loop_bar;   // persistent time loop: bf16 operand copies of h / gctx / weight slices; grid barrier
+  float4* ce_stats; float* row_lse;          // fused vocabulary CE: per-row partial statistics, log-sum-exp
   int64_t ldV;
   size_t bytes;
 };
@@ -79,7 +81,10 @@ AttnWs attn_layout(const alexcap_dims* d, void* base, bool with_logits) {
   const bool drop = d->dropout_p > 0.f;
   w.MASK = drop ? a.take<float>(S * B * H) : nullptr;
   w.Hd = drop ? a.take<float>(S * B * H) : nullptr;
-  w.logits = with_logits ? a.take<float>((int64_t)vocab_chunk_rows((int)(S * B), w.ldV) * w.ldV) : nullptr;   // ONE chunk
+  const bool ce_fused = with_logits && vocab_ce_fused_ok((int)(S * B), (int)Vp, (int)H);
+  w.logits = (with_logits && !ce_fused) ? a.take<float>((int64_t)vocab_chunk_rows((int)(S * B), w.ldV) * w.ldV) : nullptr;   // ONE chunk
+  w.ce_stats = ce_fused ? a.take<float4>(S * B * gemm_ps_ce_partials((int)Vp)) : nullptr;   // fused CE: no logits anywhere
+  w.row_lse = ce_fused ? a.take<float>(S * B) : nullptr;
   w.row_loss = a.take<float>(S * B);
   w.scal = a.take<float>(64);
   w.dHout = a.take<float>(S * B * H);
@@ -97,6 +102,11 @@ AttnWs attn_layout(const alexcap_dims* d, void* base, bool with_logits) {
   if (W5 > maxn) maxn = W5;
   w.cs_scratch = a.take<float>(64 * maxn);
   w.reg_scratch = a.take<float>(256);
+  w.loop_bar = a.take<unsigned>(64);
+  {
+    const size_t n = attn_loop_workspace_elems_bf16((int)B, (int)S, (int)D, (int)H);
+    w.loop_bf16 = n ? a.take<uint16_t>(n) : nullptr;
+  }
   w.arena = nullptr; w.arena_bytes = 0;
   if (with_logits) {
     w.arena_bytes = split_arena_bytes(B, L, D, H, E, Vp, S, vocab_chunk_rows((int)(S * B), w.ldV));
@@ -105,6 +115,28 @@ AttnWs attn_layout(const alexcap_dims* d, void* base, bool with_logits) {
   }
   w.bytes = a.off + 256;
   return w;
+}
+
+// ALEXCAP_BF16 storage of the attention streams (BASELINE.json configs[2] / [4]): the per-step attention kernels read Ws and
+// feat 2 * S times per training step; in bf16 mode they read bf16 copies (half the bytes per launch).  feat's copy is the one
+// the hoisted Ws GEMM made of its A operand; Ws gets one split pass per training step.  NULL pointers = stream fp32.
+struct AttnRows { const float* Ws; const float* feat; bool bf16; };
+AttnRows attn_rows(const alexcap_dims* d, const float* feat, const AttnWs& w, cudaStream_t st) {
+  AttnRows r{w.Ws, feat, false};
+  static const bool off = [] { const char* v = getenv("ALEXCAP_ATT_BF16_ROWS"); return v && v[0] == '0'; }();
+  SplitArena* arena = split_arena();
+  if (off || d->dtype != ALEXCAP_BF16 || !arena || attn_engine() != 1 || !attn_stream_supported(d->D, d->H) || (d->D & 7) || (d->H & 7))
+    return r;
+  const uint16_t *fh = nullptr, *wh = nullptr;
+  int64_t fld = 0, wld = 0;
+  const size_t mark = arena->used;
+  if (split_arena_get_hi(st, arena, feat, d->B * d->L, d->D, d->D, &fh, &fld) != cudaSuccess ||
+      split_arena_get_hi(st, arena, w.Ws, d->B * d->L, d->H, d->H, &wh, &wld) != cudaSuccess || fld != d->D || wld != d->H) {
+    split_arena_release(arena, mark);
+    return r;
+  }
+  r.Ws = reinterpret_cast<const float*>(wh); r.feat = reinterpret_cast<const float*>(fh); r.bf16 = true;
+  return r;
 }
 
 // ------------------------------------------------------------------------------------------ attention forward core
@@ -123,8 +155,11 @@ int attn_fwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
   API_CK(gather_rows(st, P->emb_w, w.in_tm, S * B, E, w.EmbIn, E));
   API_CK(gemm_f32(st, false, true, S * B, 4 * H, E, 1.f, w.EmbIn, E, P->lstm_w_ih, E + D, w.DGQ, W5, P->lstm_b_ih,
                   P->lstm_b_hh, false, ACT_NONE));
+  // The recurrence.  Default (tcgen05 engines, shapes whose recurrent weights fit in shared memory): ONE persistent kernel
+  // for all S steps (time_loop.cu).  Otherwise the per-step chain below.
+  const bool loop_ok = w.loop_bf16 && gemm_engine() >= 2 && attn_engine() != 0 && attn_loop_supported(B, L, D, H);
   // concatenated weights: Wcat = [W_ih[:,E:] | W_hh] (4H x (D+H));  Wub = [W_U ; W_beta] ((H+D) x H)
-  {
+  if (!loop_ok) {
     CopySegments cs;
     cs.add(P->lstm_w_ih + E, E + D, w.Wcat, DH, 4 * H, D);
     cs.add(P->lstm_w_hh, H, w.Wcat + D, DH, 4 * H, H);
@@ -135,19 +170,29 @@ int attn_fwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
     API_CK(copy_segments(st, cs));
   }
 
+  if (loop_ok) {
+    API_CK(attn_loop_fwd(st, B, L, D, H, E, S, feat, w.Ws, P->lstm_w_hh, P->lstm_w_ih, P->att_U_w, P->att_U_b, P->f_beta_w,
+                         P->f_beta_b, P->att_v_w, w.QB, w.XH, w.DGQ, w.Call, w.ALPHA, w.CTX, w.BETA, w.loop_bf16, w.loop_bar));
+  } else {
   // the per-step split-K GEMMs accumulate with red.add: their outputs are zeroed here, once, instead of by a memset
-  // node in front of every GEMM (which would also cut the programmatic-dependent-launch chain of the time loop)
-  API_CK(cudaMemsetAsync(w.QB, 0, sizeof(float) * (size_t)S * B * HD, st));
-  for (int t = 0; t < S; ++t) {                                            // AttentionLanguageModule.py:72
-    float* xh = w.XH + (int64_t)t * B * DH;
-    float* qb = w.QB + (int64_t)t * B * HD;
-    float* g = w.DGQ + (int64_t)t * B * W5;
-    { WeightBScope wb; API_CK(gemm_f32(st, false, true, B, H + D, H, 1.f, xh + D, DH, w.Wub, H, qb, HD, w.bub, nullptr, true, ACT_NONE)); }
-    API_CK(attn_step_fwd(st, B, L, D, H, w.Ws, feat, qb, HD, qb + H, HD, P->att_v_w, w.ALPHA + (int64_t)t * L,
-                         (int64_t)S * L, w.CTX + (int64_t)t * B * D, w.BETA + (int64_t)t * B * D, xh, DH));
-    { WeightBScope wb; API_CK(gemm_f32(st, false, true, B, 4 * H, D + H, 1.f, xh, DH, w.Wcat, DH, g, W5, nullptr, nullptr, true, ACT_NONE)); }
-    API_CK(lstm_pointwise_fwd(st, B, H, g, W5, w.Call + (int64_t)t * B * H, w.Call + (int64_t)(t + 1) * B * H,
-                              xh + (int64_t)B * DH + D, DH, nullptr, 0));
+    // node in front of every GEMM (which would also cut the programmatic-dependent-launch chain of the time loop)
+    API_CK(cudaMemsetAsync(w.QB, 0, sizeof(float) * (size_t)S * B * HD, st));
+    const AttnRows rows = attn_rows(d, feat, w, st);
+    for (int t = 0; t < S; ++t) {                                            // AttentionLanguageModule.py:72
+      float* xh = w.XH + (int64_t)t * B * DH;
+      float* qb = w.QB + (int64_t)t * B * HD;
+      float* g = w.DGQ + (int64_t)t * B * W5;
+      { WeightBScope wb; API_CK(gemm_f32(st, false, true, B, H + D, H, 1.f, xh + D, DH, w.Wub, H, qb, HD, w.bub, nullptr, true, ACT_NONE)); }
+      if (rows.bf16)
+        API_CK(attn_step_fwd_stream(st, B, L, D, H, rows.Ws, rows.feat, qb, HD, qb + H, HD, P->att_v_w, w.ALPHA + (int64_t)t * L,
+                                    (int64_t)S * L, w.CTX + (int64_t)t * B * D, w.BETA + (int64_t)t * B * D, xh, DH, 1, true));
+      else
+        API_CK(attn_step_fwd(st, B, L, D, H, w.Ws, feat, qb, HD, qb + H, HD, P->att_v_w, w.ALPHA + (int64_t)t * L,
+                             (int64_t)S * L, w.CTX + (int64_t)t * B * D, w.BETA + (int64_t)t * B * D, xh, DH));
+      { WeightBScope wb; API_CK(gemm_f32(st, false, true, B, 4 * H, D + H, 1.f, xh, DH, w.Wcat, DH, g, W5, nullptr, nullptr, true, ACT_NONE)); }
+      API_CK(lstm_pointwise_fwd(st, B, H, g, W5, w.Call + (int64_t)t * B * H, w.Call + (int64_t)(t + 1) * B * H,
+                                xh + (int64_t)B * DH + D, DH, nullptr, 0));
+    }
   }
   if (d->dropout_p > 0.f) {                                                 // :79 dropout(h)
     if (drop_mask) {
@@ -209,6 +254,7 @@ int attn_bwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
   API_CK(cudaMemsetAsync(w.dgctx, 0, sizeof(float) * (size_t)S * B * D, st));
   API_CK(cudaMemsetAsync(w.dh_next, 0, sizeof(float) * (size_t)S * B * H, st));
 
+  const AttnRows rows = attn_rows(d, feat, w, st);      // (arena hits: the copies were made by the forward phase)
   for (int t = S - 1; t >= 0; --t) {
     float* dgc = w.dgctx + (int64_t)t * B * D;
     float* dhn = w.dh_next + (int64_t)t * B * H;                  // dh_{t-1}, consumed by reverse step t-1
@@ -220,11 +266,18 @@ int attn_bwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
     // d gctx = dgates W_ih[:, E:]
     { WeightBScope wb; API_CK(gemm_f32(st, false, false, B, D, 4 * H, 1.f, g, W5, P->lstm_w_ih + E, E + D, dgc, D, nullptr, nullptr,
                     true, ACT_NONE)); }
-    API_CK(attn_step_bwd(st, B, L, D, H, w.Ws, feat, qb, HD, P->att_v_w, w.ALPHA + (int64_t)t * L, (int64_t)S * L,
-                         w.CTX + (int64_t)t * B * D, w.BETA + (int64_t)t * B * D, dgc, D,
-                         dalphas ? dalphas + (int64_t)t * L : nullptr, (int64_t)S * L, reg_r,
-                         g + 4 * H, W5, g + 5 * H, W5, w.DE + (int64_t)t * L, (int64_t)S * L, w.dwv_part,
-                         need_dfeat ? dfeat : nullptr));
+    if (rows.bf16)
+      API_CK(attn_step_bwd_stream(st, B, L, D, H, rows.Ws, rows.feat, qb, HD, P->att_v_w, w.ALPHA + (int64_t)t * L, (int64_t)S * L,
+                                  w.CTX + (int64_t)t * B * D, w.BETA + (int64_t)t * B * D, dgc, D,
+                                  dalphas ? dalphas + (int64_t)t * L : nullptr, (int64_t)S * L, reg_r,
+                                  g + 4 * H, W5, g + 5 * H, W5, w.DE + (int64_t)t * L, (int64_t)S * L, w.dwv_part,
+                                  need_dfeat ? dfeat : nullptr, true));
+    else
+      API_CK(attn_step_bwd(st, B, L, D, H, w.Ws, feat, qb, HD, P->att_v_w, w.ALPHA + (int64_t)t * L, (int64_t)S * L,
+                           w.CTX + (int64_t)t * B * D, w.BETA + (int64_t)t * B * D, dgc, D,
+                           dalphas ? dalphas + (int64_t)t * L : nullptr, (int64_t)S * L, reg_r,
+                           g + 4 * H, W5, g + 5 * H, W5, w.DE + (int64_t)t * L, (int64_t)S * L, w.dwv_part,
+                           need_dfeat ? dfeat : nullptr));
     // dh_{t-1} = [dgates | dq | dbpre] [W_hh ; W_U ; W_beta]
     { WeightBScope wb; API_CK(gemm_f32(st, false, false, B, H, (int)W5, 1.f, g, W5, w.Wback, H, dhn, H, nullptr, nullptr, true, ACT_NONE)); }
   }
@@ -395,9 +448,13 @@ static int attn_train_phases(const alexcap_dims* d, const alexcap_attn_params* P
     const int64_t hld = w.Hd ? H : DH;
     // vocabulary projection (AttentionLanguageModule.py:79) + CustomCrossEntropyLoss + vocab backward, in L2-sized row chunks
     API_CK(count_valid(st, w.tgt_tm, SB, d->ignore_index, w.scal));
-    if (int rc = vocab_ce_chunked(st, SB, Vp, H, hout, hld, P->deep_w, P->deep_b, w.tgt_tm, w.ldV, w.logits, d->label_smoothing,
-                                  d->ignore_index, ce_denominator ? ce_denominator : w.scal, w.row_loss, G->deep_w, G->deep_b,
-                                  w.dHout, w.cs_scratch)) return rc;
+    if (w.ce_stats) {
+      if (int rc = vocab_ce_fused(st, SB, Vp, H, hout, hld, P->deep_w, P->deep_b, w.tgt_tm, w.ldV, w.ce_stats, w.row_lse,
+                                  d->label_smoothing, d->ignore_index, ce_denominator ? ce_denominator : w.scal, w.row_loss,
+                                  G->deep_w, G->deep_b, w.dHout, w.cs_scratch)) return rc;
+    } else if (int rc = vocab_ce_chunked(st, SB, Vp, H, hout, hld, P->deep_w, P->deep_b, w.tgt_tm, w.ldV, w.logits, d->label_smoothing,
+                                         d->ignore_index, ce_denominator ? ce_denominator : w.scal, w.row_loss, G->deep_w, G->deep_b,
+                                         w.dHout, w.cs_scratch)) return rc;
     API_CK(reduce_sum(st, w.row_loss, SB, w.scal + 1));
     if (reg) API_CK(attn_regulariser(st, B, S, L, d->reg_weight, w.ALPHA, w.R, w.scal + 2, w.reg_scratch));
     API_CK(finalize_loss(st, w.scal + 1, reg ? w.scal + 2 : nullptr, w.scal, loss_out, w.bad_rows, B));
@@ -510,9 +567,21 @@ int alexcap_attn_workspace_region(const alexcap_dims* d, const char* name, size_
   if (!strcmp(name, "MASK")) { p = w.MASK; n = S * B * H * 4; }
   else if (!strcmp(name, "ALPHA")) { p = w.ALPHA; n = B * S * L * 4; }
   else if (!strcmp(name, "H")) { p = w.XH; n = (S + 1) * B * (D + H) * 4; }
+  else if (!strcmp(name, "LOGITS")) { p = w.logits; n = (size_t)vocab_chunk_rows((int)(S * B), w.ldV) * w.ldV * 4; }   // absent when the CE is fused
   if (!p) return fail(ALEXCAP_E_BADARG, "alexcap_attn_workspace_region: unknown region name, or a region these dims do not have");
   *offset = (size_t)(static_cast<const char*>(p) - base); *bytes = n;
   return 0;
+}
+
+int alexcap_set_time_loop(int32_t on) {
+  const int prev = time_loop_enabled() ? 1 : 0;
+  time_loop_enabled() = on != 0;
+  return prev;
+}
+
+int alexcap_time_loop_profile(unsigned long long* host_out, int32_t max_entries) {
+  if (!host_out || max_entries <= 0) return 0;
+  return time_loop_profile_read(host_out, max_entries);
 }
 
 int alexcap_cross_entropy(const float* logits, const int32_t* tgt, int32_t N, int32_t C, int64_t ld, float label_smoothing,
@@ -573,7 +642,12 @@ int alexcap_gemm_f32(int32_t transa, int32_t transb, int32_t M, int32_t N, int32
 
 int alexcap_attn_step_fwd(int32_t B, int32_t L, int32_t D, int32_t H, const float* Ws, const float* feat, const float* q,
                           int64_t q_ld, const float* bpre, int64_t bpre_ld, const float* w_v, float* alpha,
-                          int64_t alpha_ld, float* ctx, float* beta, float* gctx, int64_t gctx_ld, void* stream) {
+                          int64_t alpha_ld, float* ctx, float* beta, float* gctx, int64_t gctx_ld, int32_t rows_bf16, void* stream) {
+  if (rows_bf16) {
+    API_CK(attn_step_fwd_stream(static_cast<cudaStream_t>(stream), B, L, D, H, Ws, feat, q, q_ld, bpre, bpre_ld, w_v, alpha, alpha_ld,
+                                ctx, beta, gctx, gctx_ld, 1, true));
+    return 0;
+  }
   API_CK(attn_step_fwd(static_cast<cudaStream_t>(stream), B, L, D, H, Ws, feat, q, q_ld, bpre, bpre_ld, w_v, alpha, alpha_ld,
                        ctx, beta, gctx, gctx_ld));
   return 0;
@@ -583,7 +657,12 @@ int alexcap_attn_step_bwd(int32_t B, int32_t L, int32_t D, int32_t H, const floa
                           int64_t q_ld, const float* w_v, const float* alpha, int64_t alpha_ld, const float* ctx,
                           const float* beta, const float* dgctx, int64_t dgctx_ld, const float* dalpha_ext, int64_t ext_ld,
                           const float* reg_r, float* dq, int64_t dq_ld, float* dbpre, int64_t dbpre_ld, float* de,
-                          int64_t de_ld, float* dwv_part, float* dfeat, void* stream) {
+                          int64_t de_ld, float* dwv_part, float* dfeat, int32_t rows_bf16, void* stream) {
+  if (rows_bf16) {
+    API_CK(attn_step_bwd_stream(static_cast<cudaStream_t>(stream), B, L, D, H, Ws, feat, q, q_ld, w_v, alpha, alpha_ld, ctx, beta,
+                                dgctx, dgctx_ld, dalpha_ext, ext_ld, reg_r, dq, dq_ld, dbpre, dbpre_ld, de, de_ld, dwv_part, dfeat, true));
+    return 0;
+  }
   API_CK(attn_step_bwd(static_cast<cudaStream_t>(stream), B, L, D, H, Ws, feat, q, q_ld, w_v, alpha, alpha_ld, ctx, beta,
                        dgctx, dgctx_ld, dalpha_ext, ext_ld, reg_r, dq, dq_ld, dbpre, dbpre_ld, de, de_ld, dwv_part, dfeat));
   return 0;

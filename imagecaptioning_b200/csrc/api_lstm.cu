@@ -30,6 +30,7 @@ struct LstmWs {
   float *G[ALEXCAP_MAX_LAYERS], *Hs[ALEXCAP_MAX_LAYERS], *Cs[ALEXCAP_MAX_LAYERS];
   float *MASK, *Hd, *logits, *row_loss, *scal, *dHout, *dA, *dB, *dh_next, *dc, *dpre_bm, *cs_scratch;
   uint8_t* arena; size_t arena_bytes;   // bf16 hi/lo operand copies of the big GEMMs (training layout only)
+  float4* ce_stats; float* row_lse;          // fused vocabulary CE: per-row partial statistics, log-sum-exp
   int64_t ldV;
   size_t bytes;
 };
@@ -53,7 +54,10 @@ LstmWs lstm_layout(const alexcap_dims* d, void* base, bool with_logits) {
   const bool drop = d->dropout_p > 0.f;
   w.MASK = drop ? a.take<float>(S * B * H) : nullptr;
   w.Hd = drop ? a.take<float>(S * B * H) : nullptr;
-  w.logits = with_logits ? a.take<float>((int64_t)vocab_chunk_rows((int)(S * B), w.ldV) * w.ldV) : nullptr;   // ONE chunk
+  const bool ce_fused = with_logits && vocab_ce_fused_ok((int)(S * B), (int)Vp, (int)H);
+  w.logits = (with_logits && !ce_fused) ? a.take<float>((int64_t)vocab_chunk_rows((int)(S * B), w.ldV) * w.ldV) : nullptr;   // ONE chunk
+  w.ce_stats = ce_fused ? a.take<float4>(S * B * gemm_ps_ce_partials((int)Vp)) : nullptr;   // fused CE: no logits anywhere
+  w.row_lse = ce_fused ? a.take<float>(S * B) : nullptr;
   w.row_loss = a.take<float>(S * B);
   w.scal = a.take<float>(64);
   w.dHout = a.take<float>(S * B * H);
@@ -215,9 +219,13 @@ int alexcap_lstm_train_fused(const alexcap_dims* d, const alexcap_lstm_params* P
   if (int rc = lstm_fwd_core(d, P, feat, gt, drop_mask, w, st)) return rc;
   const float* hout = top_out(d, w);
   API_CK(count_valid(st, w.tgt_tm, SB, d->ignore_index, w.scal));
-  if (int rc = vocab_ce_chunked(st, SB, Vp, H, hout, H, P->out_w, P->out_b, w.tgt_tm, w.ldV, w.logits, d->label_smoothing,
-                                d->ignore_index, ce_denominator ? ce_denominator : w.scal, w.row_loss, G->out_w, G->out_b,
-                                w.dHout, w.cs_scratch)) return rc;
+  if (w.ce_stats) {
+    if (int rc = vocab_ce_fused(st, SB, Vp, H, hout, H, P->out_w, P->out_b, w.tgt_tm, w.ldV, w.ce_stats, w.row_lse,
+                                d->label_smoothing, d->ignore_index, ce_denominator ? ce_denominator : w.scal, w.row_loss,
+                                G->out_w, G->out_b, w.dHout, w.cs_scratch)) return rc;
+  } else if (int rc = vocab_ce_chunked(st, SB, Vp, H, hout, H, P->out_w, P->out_b, w.tgt_tm, w.ldV, w.logits, d->label_smoothing,
+                                       d->ignore_index, ce_denominator ? ce_denominator : w.scal, w.row_loss, G->out_w, G->out_b,
+                                       w.dHout, w.cs_scratch)) return rc;
   API_CK(reduce_sum(st, w.row_loss, SB, w.scal + 1));
   API_CK(finalize_loss(st, w.scal + 1, nullptr, w.scal, loss_out, w.bad_rows, B));
   return lstm_bwd_core(d, P, feat, G, dfeat, w, st);

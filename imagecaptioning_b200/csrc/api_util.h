@@ -133,6 +133,38 @@ inline int vocab_ce_chunked(cudaStream_t st, int SB, int Vp, int H, const float*
   return 0;
 }
 
+// ---- the same block with the logits NEVER materialised (north_star item 4): the projection runs on the pre-split tcgen05
+// engine with the cross-entropy in its epilogue (gemm_ps.cu: EPI 1 = per-row online-softmax statistics straight from TMEM,
+// EPI 2 = the product recomputed and turned into d logits, written only as the bf16 operand copies the two backward GEMMs
+// read).  Used whenever the three GEMMs qualify for the pre-split engine; the chunked path above remains for the exact-fp32
+// engines (0 / 1) and for tiny shapes.
+inline bool vocab_ce_fused_ok(int SB, int Vp, int H) {
+  static const bool off = [] { const char* v = getenv("ALEXCAP_VOCAB_FUSED"); return v && v[0] == '0'; }();
+  return !off && gemm_engine() >= 2 && gemm_ps_ce_wanted(SB, Vp, H) && gemm_ps_wanted(Vp, H, SB) && gemm_ps_wanted(SB, H, Vp);
+}
+inline int vocab_ce_fused(cudaStream_t st, int SB, int Vp, int H, const float* hout, int64_t hld, const float* Wo, const float* bo,
+                          const int32_t* tgt_tm, int64_t ldV, float4* stats, float* row_lse, float eps, int ignore_index,
+                          const float* denom, float* row_loss, float* dWo, float* dbo, float* dHout, float* cs_scratch) {
+  SplitArena* arena = split_arena();
+  if (!arena) return fail(ALEXCAP_E_BADARG, "vocab_ce_fused: no operand arena");
+  const int nprod = gemm_engine() == 3 ? 3 : 1;
+  // the gradient exists only as operand copies; their arena key is the statistics buffer (never read as an fp32 matrix)
+  const float* key = reinterpret_cast<const float*>(stats);
+  uint16_t *dl_hi = nullptr, *dl_lo = nullptr;
+  int64_t dl_ld = 0;
+  if (!split_arena_reserve(arena, key, SB, Vp, ldV, nprod == 3, &dl_hi, &dl_lo, &dl_ld))
+    return fail(ALEXCAP_E_WORKSPACE, "vocab_ce_fused: operand arena too small for the d logits copies");
+  API_CK(gemm_ps_ce(st, false, SB, Vp, H, hout, hld, Wo, H, bo, tgt_tm, eps, ignore_index, denom, stats, row_lse, row_loss,
+                    nullptr, nullptr, 0, nprod, arena));
+  API_CK(gemm_ps_ce(st, true, SB, Vp, H, hout, hld, Wo, H, bo, tgt_tm, eps, ignore_index, denom, stats, row_lse, row_loss,
+                    dl_hi, dl_lo, dl_ld, nprod, arena));
+  // dW_o = dlogits^T h ; db_o = colsum(dlogits) ; dH = dlogits W_o      (all three read the copies)
+  API_CK(gemm_f32(st, true, false, Vp, H, SB, 1.f, key, ldV, hout, hld, dWo, H, nullptr, nullptr, false, ACT_NONE));
+  API_CK(col_sum_bf16(st, dl_hi, dl_lo, SB, Vp, dl_ld, dbo, false, cs_scratch));
+  API_CK(gemm_f32(st, false, false, SB, H, Vp, 1.f, key, ldV, Wo, H, dHout, H, nullptr, nullptr, false, ACT_NONE));
+  return 0;
+}
+
 // Per-step GEMMs of the time loop: B = weights (or their concatenations built at the start of the call, many kernels and at
 // least one fully-ordered node earlier), so the GEMM kernel may prefetch its B tiles before griddepcontrol.wait.
 struct WeightBScope {

@@ -44,6 +44,13 @@ struct Params {
   float* C; const float* bias; const float* bias2;
   int M, N, K; int64_t ldc; float alpha; int accumulate, act;
   int tiles_m, tiles_n, splits, kb_per_split, num_kb, n_items;
+  // fused vocabulary projection + cross-entropy epilogues (EPI = 1: statistics, EPI = 2: gradient); C is not written
+  const int32_t* tgt;           // [M] target class per row
+  float4* stats;                // EPI 1 out: [M][tiles_n * 2] partial (max, sum exp(x - max), sum x, x[target])
+  const float* row_lse;         // EPI 2 in: [M] log-sum-exp of the row
+  const float* denom;           // EPI 2 in: CE divisor (device scalar)
+  uint16_t* dl_hi; uint16_t* dl_lo; int64_t dl_ld;   // EPI 2 out: d logits as bf16 hi (+ lo) copies [M, dl_ld]
+  float eps; int ignore_index;
 };
 
 // ------------------------------------------------------------------------------------------------ split pass
@@ -136,8 +143,83 @@ __device__ __forceinline__ void store_chunk(const uint32_t* v, float* tile, cons
   __syncwarp();
 }
 
+// ---- fused vocabulary projection + CustomCrossEntropyLoss (AlexCap/AttentionLanguageModule.py:79 + AlexCap/CustomLoss.py:7-14).
+// The logits tile never leaves the SM: thread = one row of the 128-row tile, v[j] = logit of column ncol0 + j (before bias).
+// EPI 1 folds the chunk into the row's running (max, sum exp, sum x, x[target]); EPI 2 turns it into the gradient
+//   d logit = (exp(x - lse) - eps / C - (1 - eps) [n == y]) * [y != ignore] / denom
+// and writes it as the bf16 hi (+ lo = bf16(g - hi)) operand copies the two backward GEMMs read (dW_o = dlogits^T h,
+// dH = dlogits W_o): the B x T x V' logits are never materialised, in fp32 or otherwise.
+struct RowStat { float m, s, sx, xt; };
+__device__ __forceinline__ void ce_stats_chunk(const uint32_t* v, const Params& p, int ncol0, int y, RowStat& st) {
+  float x[32];
+  float mc = -INFINITY;
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    const int n = ncol0 + j;
+    const bool ok = n < p.N;
+    x[j] = ok ? fmaf(p.alpha, __uint_as_float(v[j]), __ldg(p.bias + (ok ? n : 0))) : -INFINITY;
+    mc = fmaxf(mc, x[j]);
+  }
+  if (mc == -INFINITY) return;                         // chunk entirely past the last class
+  const float mn = fmaxf(st.m, mc);
+  float acc = 0.f, sx = 0.f, xt = 0.f;
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    const int n = ncol0 + j;
+    if (n < p.N) {
+      acc += __expf(x[j] - mn);
+      sx += x[j];
+      if (n == y) xt = x[j];
+    }
+  }
+  st.s = st.s * __expf(st.m - mn) + acc;               // (exp(-inf) = 0 on the first chunk)
+  st.m = mn; st.sx += sx; st.xt += xt;
+}
+// `tile`: the warp's 32 x 33 float staging tile.  The thread that owns row `lane` of the chunk computes the 32 gradients of
+// its row and parks them in the tile; the warp then walks the tile 8 rows at a time, 4 lanes per row x 8 columns per lane, so
+// that every store instruction writes 8 contiguous 64-byte row segments (whole 32-byte sectors) of the bf16 copies -- a
+// thread-per-row store would touch 32 different rows with 16 bytes each.
+__device__ __forceinline__ void ce_grad_chunk(const uint32_t* v, const Params& p, float* tile, int mrow0, int lane, int ncol0,
+                                              int y, float lse, float scale) {
+  // scale = [y != ignore] / denom (0 for rows past M); columns >= N get 0 (pad columns of the copies up to dl_ld)
+  const float u = p.eps / (float)p.N;
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    const int n = ncol0 + j;
+    const bool ok = n < p.N;
+    const float x = fmaf(p.alpha, __uint_as_float(v[j]), __ldg(p.bias + (ok ? n : 0)));
+    float g = __expf(x - lse) - u;
+    if (n == y) g -= (1.f - p.eps);
+    tile[lane * 33 + j] = ok ? g * scale : 0.f;
+  }
+  __syncwarp();
+  const int sub = lane >> 2, cg = (lane & 3) * 8;
+  if (ncol0 + cg < p.dl_ld) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int rr = sub + 8 * i, m = mrow0 + rr;
+      if (m < p.M) {
+        float g[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) g[k] = tile[rr * 33 + cg + k];
+        uint32_t hi[4], lo[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(hi[k]) : "f"(g[2 * k + 1]), "f"(g[2 * k]));
+          const float r0 = g[2 * k] - __uint_as_float(hi[k] << 16), r1 = g[2 * k + 1] - __uint_as_float(hi[k] & 0xffff0000u);
+          asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(lo[k]) : "f"(r1), "f"(r0));
+        }
+        const int64_t off = (int64_t)m * p.dl_ld + ncol0 + cg;
+        *reinterpret_cast<uint4*>(p.dl_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+        if (p.dl_lo) *reinterpret_cast<uint4*>(p.dl_lo + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+      }
+    }
+  }
+  __syncwarp();
+}
+
 // ------------------------------------------------------------------------------------------------ kernel
-template <int BN, bool A_MN, bool B_MN, int NPROD>
+template <int BN, bool A_MN, bool B_MN, int NPROD, int EPI = 0>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_ps_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__ CUtensorMap tmAl,
                const __grid_constant__ CUtensorMap tmBh, const __grid_constant__ CUtensorMap tmBl, const Params p) {
@@ -276,6 +358,19 @@ gemm_ps_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
       mbar_wait(&tfull_bar[acc], (li >> 1) & 1);
       tcgen05_fence_after();
       const uint32_t tbase = tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(acc * BN);
+      // fused cross-entropy epilogues: this thread's row and its target
+      const int row = it.m0 + q4 * 32 + lane;
+      const bool row_ok = row < p.M;
+      int y = -1; float lse = 0.f, scale = 0.f;
+      RowStat rs{-INFINITY, 0.f, 0.f, 0.f};
+      if (EPI != 0 && row_ok) {
+        y = __ldg(p.tgt + row);
+        if (EPI == 2) {
+          lse = __ldg(p.row_lse + row);
+          const float dn = __ldg(p.denom);
+          scale = (y != p.ignore_index && dn > 0.f) ? 1.f / dn : 0.f;
+        }
+      }
 #pragma unroll 1
       for (int g = 0; g < CPW; g += 2) {
         uint32_t v0[32], v1[32];
@@ -288,9 +383,18 @@ gemm_ps_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
           __syncwarp();
           if (lane == 0) mbar_arrive(&tempty_bar[acc]);
         }
-        store_chunk(v0, tile, p, it.m0 + q4 * 32, it.n0 + c0 * 32, lane, atomic, it.split == 0);
-        store_chunk(v1, tile, p, it.m0 + q4 * 32, it.n0 + c1 * 32, lane, atomic, it.split == 0);
+        if (EPI == 0) {
+          store_chunk(v0, tile, p, it.m0 + q4 * 32, it.n0 + c0 * 32, lane, atomic, it.split == 0);
+          store_chunk(v1, tile, p, it.m0 + q4 * 32, it.n0 + c1 * 32, lane, atomic, it.split == 0);
+        } else if (EPI == 1) {
+          if (row_ok) { ce_stats_chunk(v0, p, it.n0 + c0 * 32, y, rs); ce_stats_chunk(v1, p, it.n0 + c1 * 32, y, rs); }
+        } else {
+          ce_grad_chunk(v0, p, tile, it.m0 + q4 * 32, lane, it.n0 + c0 * 32, y, lse, scale);     // (whole warp: rows past M have scale 0)
+          ce_grad_chunk(v1, p, tile, it.m0 + q4 * 32, lane, it.n0 + c1 * 32, y, lse, scale);
+        }
       }
+      if (EPI == 1 && row_ok)
+        p.stats[(int64_t)row * (p.tiles_n * 2) + (it.n0 / BN) * 2 + half] = make_float4(rs.m, rs.s, rs.sx, rs.xt);
     }
   }
 
@@ -317,11 +421,11 @@ static bool make_map_bf16(CUtensorMap* map, const uint16_t* base, int64_t inner,
   return r == CUDA_SUCCESS;
 }
 
-template <int BN, bool A_MN, bool B_MN, int NPROD>
+template <int BN, bool A_MN, bool B_MN, int NPROD, int EPI = 0>
 static cudaError_t launch(cudaStream_t st, const CUtensorMap* maps, const Params& p, int grid) {
   constexpr size_t SMEM = (size_t)RING_BYTES + EPI_BYTES + 1024 /*align*/ + 256 /*barriers*/;
   static bool configured = false;
-  auto kern = gemm_ps_kernel<BN, A_MN, B_MN, NPROD>;
+  auto kern = gemm_ps_kernel<BN, A_MN, B_MN, NPROD, EPI>;
   if (!configured) {
     ACK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
     configured = true;
@@ -394,6 +498,18 @@ bool split_arena_reserve(SplitArena* a, const float* key, int rows, int cols, in
   a->n++;
   *hi = e.hi; *lo = e.lo; *ldo_out = ldo;
   return true;
+}
+
+// bf16 (hi) copy of X out of the arena -- made now if no GEMM has split X yet.  Used to stream Ws / feat as bf16 rows through
+// the attention kernels in ALEXCAP_BF16 mode.
+cudaError_t split_arena_get_hi(cudaStream_t st, SplitArena* a, const float* X, int rows, int cols, int64_t ld, const uint16_t** hi,
+                               int64_t* ldo) {
+  if (!a) return cudaErrorMemoryAllocation;
+  ps::Split sp;
+  cudaError_t e = ps::get_split(st, a, X, rows, cols, ld, false, &sp);
+  if (e != cudaSuccess) return e;
+  *hi = sp.hi; *ldo = sp.ld;
+  return cudaSuccess;
 }
 
 bool split_arena_is_produced(const SplitArena* a, const float* p) {
@@ -475,6 +591,88 @@ cudaError_t gemm_ps_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, 
   if (with_lo) PS_DISPATCH(128, 3);
   PS_DISPATCH(128, 1);
 #undef PS_DISPATCH
+}
+
+// ------------------------------------------------------------------------------------------------ fused vocabulary CE
+namespace ps {
+
+// one warp per row: fold the row's partial statistics into lse and the masked label-smoothed loss (CustomLoss.py:7)
+//   loss_row = ((1 - eps) (lse - x[y]) + eps (lse - mean_c x[c])) / denom      (0 for ignored rows)
+__global__ void __launch_bounds__(256) ce_combine_kernel(const float4* __restrict__ stats, int np, const int32_t* __restrict__ tgt,
+                                                         int M, int C, float eps, int ignore_index, const float* __restrict__ denom,
+                                                         float* __restrict__ row_lse, float* __restrict__ row_loss) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (row >= M) return;
+  const float4* sp = stats + (int64_t)row * np;
+  float m = -INFINITY;
+  for (int i = lane; i < np; i += 32) m = fmaxf(m, sp[i].x);
+  m = warp_max(m);
+  float s = 0.f, sx = 0.f, xt = 0.f;
+  for (int i = lane; i < np; i += 32) {
+    const float4 q = sp[i];
+    if (q.x > -INFINITY) s = fmaf(q.y, expf(q.x - m), s);
+    sx += q.z; xt += q.w;
+  }
+  s = warp_sum(s); sx = warp_sum(sx); xt = warp_sum(xt);
+  if (lane == 0) {
+    const float lse = m + logf(s);
+    row_lse[row] = lse;
+    const float dn = denom[0];
+    const float inv_d = dn > 0.f ? 1.f / dn : 0.f;
+    row_loss[row] = (tgt[row] == ignore_index) ? 0.f : ((1.f - eps) * (lse - xt) + eps * (lse - sx / (float)C)) * inv_d;
+  }
+}
+
+}  // namespace ps
+
+bool gemm_ps_ce_wanted(int M, int N, int K) { return gemm_ps_wanted(M, N, K) && N >= 256; }
+int gemm_ps_ce_partials(int N) { return 2 * ceil_div(N, (N >= 1024) ? 256 : 128); }
+
+// pass 1 (want_grad = false): stats[M][gemm_ps_ce_partials(N)] from logits = A B^T + bias, then ce_combine -> row_lse, row_loss;
+// pass 2 (want_grad = true): the same product again, gradient written as bf16 copies.  A [M,K] (lda), B [N,K] (ldb), both
+// K-major (the vocabulary projection h W_o^T); operand copies come from / go to `arena` like gemm_ps_f32.
+cudaError_t gemm_ps_ce(cudaStream_t st, bool want_grad, int M, int N, int K, const float* A, int64_t lda, const float* B, int64_t ldb,
+                       const float* bias, const int32_t* tgt, float eps, int ignore_index, const float* denom, float4* stats,
+                       float* row_lse, float* row_loss, uint16_t* dl_hi, uint16_t* dl_lo, int64_t dl_ld, int nprod,
+                       SplitArena* arena) {
+  using namespace ps;
+  if (M <= 0 || N <= 0 || K <= 0) return cudaSuccess;
+  if (!arena || !get_encode() || !bias || !tgt) return cudaErrorInvalidValue;
+  const bool with_lo = (nprod == 3);
+  Split sa, sb;
+  ACK(get_split(st, arena, A, M, K, lda, with_lo, &sa));
+  ACK(get_split(st, arena, B, N, K, ldb, with_lo, &sb));
+  const int BN = (N >= 1024) ? 256 : 128;
+  Params p = {};
+  p.bias = bias; p.M = M; p.N = N; p.K = K; p.alpha = 1.f;
+  p.tiles_m = ceil_div(M, BM); p.tiles_n = ceil_div(N, BN); p.splits = 1; p.num_kb = ceil_div(K, BK); p.kb_per_split = p.num_kb;
+  p.n_items = p.tiles_m * p.tiles_n;
+  p.tgt = tgt; p.stats = stats; p.row_lse = row_lse; p.denom = denom; p.dl_hi = dl_hi; p.dl_lo = dl_lo; p.dl_ld = dl_ld;
+  p.eps = eps; p.ignore_index = ignore_index;
+  if (want_grad && (!dl_hi || (dl_ld & 7) || (with_lo && !dl_lo))) return cudaErrorInvalidValue;
+  CUtensorMap maps[4];
+  bool ok = true;
+  for (int o = 0; o < (with_lo ? 2 : 1); ++o) {
+    ok = ok && make_map_bf16(&maps[o], o ? sa.lo : sa.hi, K, M, sa.ld, BM);
+    ok = ok && make_map_bf16(&maps[2 + o], o ? sb.lo : sb.hi, K, N, sb.ld, BN);
+  }
+  if (!with_lo) { maps[1] = maps[0]; maps[3] = maps[2]; }
+  if (!ok) return cudaErrorInvalidValue;
+  int nsm = 148;
+  { int dev = 0; if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev); }
+  const int grid = p.n_items < nsm ? p.n_items : nsm;
+  cudaError_t e;
+  if (!want_grad) {
+    if (BN == 256) e = with_lo ? launch<256, false, false, 3, 1>(st, maps, p, grid) : launch<256, false, false, 1, 1>(st, maps, p, grid);
+    else e = with_lo ? launch<128, false, false, 3, 1>(st, maps, p, grid) : launch<128, false, false, 1, 1>(st, maps, p, grid);
+    ACK(e);
+    ALEXCAP_NOTE_LAUNCH();
+    ce_combine_kernel<<<ceil_div(M, 8), 256, 0, st>>>(stats, p.tiles_n * 2, tgt, M, N, eps, ignore_index, denom, row_lse, row_loss);
+    return cudaGetLastError();
+  }
+  if (BN == 256) e = with_lo ? launch<256, false, false, 3, 2>(st, maps, p, grid) : launch<256, false, false, 1, 2>(st, maps, p, grid);
+  else e = with_lo ? launch<128, false, false, 3, 2>(st, maps, p, grid) : launch<128, false, false, 1, 2>(st, maps, p, grid);
+  return e;
 }
 
 }  // namespace alexcap

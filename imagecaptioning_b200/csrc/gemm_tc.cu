@@ -19,6 +19,7 @@
 //                  the only MN-major layout tf32 operands have (LBO = 4096 B, SBO = 512 B)
 // TMA zero-fills out-of-bounds elements, so M, N and K need no padding.
 #include <cuda.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "kernels.h"
@@ -40,6 +41,7 @@ struct Params {
   float* C; const float* bias; const float* bias2;
   int M, N, K; int64_t ldc; float alpha; int accumulate, act;
   int kb_per_split, num_kb;
+  int dbg_noepi;   // debug (ALEXCAP_DBG_NOEPI=1): skip the split-K red.add stores (timing experiments only; results are wrong)
   int b_const;     // B was written long before the previous kernel (weights): its first tiles may be fetched before pdl_wait
 };
 // MN-major fp32/tf32 tiles (probed on B200, scripts/debug_tc_mn.py): boxes of {32 mn, 32 k} = 32 rows of 128 bytes,
@@ -306,7 +308,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           float x = fmaf(p.alpha, tile[r * 33 + lane], bsum);
           float* cp = p.C + (int64_t)m * p.ldc + n;
           if (atomic) {
-            atomicAdd(cp, x);      // C was zeroed (or holds the value to accumulate onto) by the launcher
+            if (!p.dbg_noepi) atomicAdd(cp, x);      // C was zeroed (or holds the value to accumulate onto) by the launcher
           } else {
             if (p.accumulate) x += *cp;
             if (p.act == ACT_TANH) x = tanhf(x);
@@ -414,6 +416,7 @@ cudaError_t gemm_tc_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, 
   p.C = C; p.bias = bias; p.bias2 = bias2; p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.alpha = alpha;
   p.accumulate = accumulate ? 1 : 0; p.act = act; p.kb_per_split = kb_per; p.num_kb = num_kb;
   p.b_const = (gemm_b_is_weight() && pdl_enabled()) ? 1 : 0;
+  { static const int noepi = [] { const char* v = getenv("ALEXCAP_DBG_NOEPI"); return (v && v[0] == '1') ? 1 : 0; }(); p.dbg_noepi = noepi; }
   dim3 grid(ceil_div(N, BN), ceil_div(M, BM), splits);
 #define TC_DISPATCH(BN_, MODE_)                                                                 \
   do {                                                                                          \

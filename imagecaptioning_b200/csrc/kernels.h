@@ -33,12 +33,23 @@ void split_arena_release(SplitArena* a, size_t mark);   // forget every copy mad
 bool gemm_ps_wanted(int M, int N, int K);
 // true when `p` is the key of copies written directly by their producer: the fp32 matrix behind it does NOT hold the data
 bool split_arena_is_produced(const SplitArena* a, const float* p);
+cudaError_t split_arena_get_hi(cudaStream_t st, SplitArena* a, const float* X, int rows, int cols, int64_t ld, const uint16_t** hi,
+                               int64_t* ldo);
 bool split_arena_reserve(SplitArena* a, const float* key, int rows, int cols, int64_t ld, bool with_lo, uint16_t** hi,
                          uint16_t** lo, int64_t* ldo_out);
 cudaError_t gemm_ps_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, float alpha,
                         const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
                         const float* bias, const float* bias2, bool accumulate, int act, int force_splits, int nprod,
                         SplitArena* arena);
+// Fused vocabulary projection + masked label-smoothed cross-entropy on the pre-split engine (gemm_ps.cu): the logits tile is
+// reduced / differentiated in the tcgen05 epilogue, straight from TMEM; logits are never written.  Two passes over the same
+// product (the second recomputes it): statistics -> (row_lse, row_loss), then the gradient as bf16 hi (+ lo) copies.
+bool gemm_ps_ce_wanted(int M, int N, int K);
+int gemm_ps_ce_partials(int N);          // float4 statistics per row the first pass writes
+cudaError_t gemm_ps_ce(cudaStream_t st, bool want_grad, int M, int N, int K, const float* A, int64_t lda, const float* B, int64_t ldb,
+                       const float* bias, const int32_t* tgt, float eps, int ignore_index, const float* denom, float4* stats,
+                       float* row_lse, float* row_loss, uint16_t* dl_hi, uint16_t* dl_lo, int64_t dl_ld, int nprod,
+                       SplitArena* arena);
 bool gemm_tc_supported(int M, int N, int K, const float* A, int64_t lda, const float* B, int64_t ldb, const float* C);
 int& gemm_engine();                      // this thread's engine (scoped overrides write it)
 void gemm_engine_set_default(int engine); // process-wide default, picked up by every thread
@@ -64,13 +75,14 @@ int& attn_engine();
 cudaError_t attn_step_fwd_stream(cudaStream_t st, int B, int L, int D, int H, const float* Ws, const float* feat,
                                  const float* q, int64_t q_ld, const float* bpre, int64_t bpre_ld, const float* wv,
                                  float* alpha, int64_t alpha_ld, float* ctx, float* beta, float* gctx, int64_t gctx_ld,
-                                 int rows_per_image);
+                                 int rows_per_image, bool rows_bf16 = false);
+// rows_bf16: Ws and feat point at bf16 rows of the same shapes (ALEXCAP_BF16 storage: half the streamed bytes; D, H % 8 == 0)
 cudaError_t attn_step_bwd_stream(cudaStream_t st, int B, int L, int D, int H, const float* Ws, const float* feat,
                                  const float* q, int64_t q_ld, const float* wv, const float* alpha, int64_t alpha_ld,
                                  const float* ctx, const float* beta, const float* dgctx, int64_t dgctx_ld,
                                  const float* dalpha_ext, int64_t ext_ld, const float* reg_r,
                                  float* dq, int64_t dq_ld, float* dbpre, int64_t dbpre_ld, float* de, int64_t de_ld,
-                                 float* dwv_part, float* dfeat);
+                                 float* dwv_part, float* dfeat, bool rows_bf16 = false);
 // dWs[b,l,h] = wv[h] * sum_t de[b,t,l] * (1 - tanh^2(Ws[b,l,h] + q[t,b,h]));  q: [S][B] rows of stride q_ld,
 // de: [B][S][L].
 cudaError_t attn_dws(cudaStream_t st, int B, int L, int H, int S, const float* Ws, const float* q, int64_t q_ld,
@@ -80,6 +92,19 @@ cudaError_t attn_dws(cudaStream_t st, int B, int L, int H, int S, const float* W
 // resid = 1 - sum_t alpha[b,t,l]; r[b,l] = -2*w*resid/(B*L); loss_reg = w*mean(resid^2) -> *loss_reg
 cudaError_t attn_regulariser(cudaStream_t st, int B, int S, int L, float weight, const float* alphas, float* r,
                              float* loss_reg, float* scratch);
+
+// ---- persistent time loop (time_loop.cu): the whole forward recurrence in one cooperative launch, recurrent weights
+// resident in shared memory, LSTM pointwise in the tcgen05 epilogue.  Supported when the weight slices fit (B <= 128,
+// H <= 512, H/4 <= #SMs ...); the caller falls back to the per-step chain otherwise.
+bool& time_loop_enabled();     // process-wide switch (default: ALEXCAP_TIME_LOOP=1 in the environment, else off)
+bool attn_loop_supported(int B, int L, int D, int H);
+size_t attn_loop_workspace_elems_bf16(int B, int S, int D, int H);      // 0 when unsupported
+cudaError_t attn_loop_fwd(cudaStream_t st, int B, int L, int D, int H, int E, int S, const float* feat, const float* Ws,
+                          const float* w_hh, const float* w_ih, const float* w_u, const float* b_u, const float* w_beta,
+                          const float* b_beta, const float* wv, float* QB, float* XH, float* DGQ, float* Call, float* ALPHA,
+                          float* CTX, float* BETA, uint16_t* bf16ws, unsigned* bar);
+
+int time_loop_profile_read(unsigned long long* host_out, int max_entries);
 
 // ---- LSTM pointwise (lstm_pointwise.cu)
 // gates [B,4H] (row stride g_ld) pre-activations -> activations in place; c_prev [B,H] -> c_out [B,H];

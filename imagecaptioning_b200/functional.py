@@ -130,9 +130,15 @@ def gemm(A, B, transa=False, transb=True, M=None, N=None, K=None, lda=None, ldb=
     return out
 
 
+def _rows_bf16(Ws, feat):
+    if Ws.dtype != feat.dtype or Ws.dtype not in (torch.float32, torch.bfloat16):
+        raise _lib.AlexcapError('Ws and feat must both be float32 or both bfloat16')
+    return int(Ws.dtype == torch.bfloat16)
+
+
 def attn_step_fwd(Ws, feat, q, bpre, w_v):
-    """One fused attention step.  Ws[B,L,H], feat[B,L,D], q[B,H], bpre[B,D], w_v[H] ->
-    (alpha[B,L], ctx[B,D], beta[B,D], gctx[B,D])."""
+    """One fused attention step.  Ws[B,L,H], feat[B,L,D] (both fp32, or both bf16 = the bf16 storage mode of the streamed
+    grids), q[B,H], bpre[B,D], w_v[H] -> (alpha[B,L], ctx[B,D], beta[B,D], gctx[B,D])."""
     lib = ensure_device(Ws.device)
     _req(Ws, feat, q, bpre, w_v)
     B, L, H = Ws.shape
@@ -142,7 +148,8 @@ def attn_step_fwd(Ws, feat, q, bpre, w_v):
     beta = torch.empty_like(ctx)
     gctx = torch.empty_like(ctx)
     check(lib.alexcap_attn_step_fwd(B, L, D, H, _ptr(Ws), _ptr(feat), _ptr(q), q.stride(0), _ptr(bpre), bpre.stride(0),
-                                    _ptr(w_v), _ptr(alpha), L, _ptr(ctx), _ptr(beta), _ptr(gctx), D, _stream()),
+                                    _ptr(w_v), _ptr(alpha), L, _ptr(ctx), _ptr(beta), _ptr(gctx), D, _rows_bf16(Ws, feat),
+                                    _stream()),
           'alexcap_attn_step_fwd')
     return alpha, ctx, beta, gctx
 
@@ -158,11 +165,11 @@ def attn_step_bwd(Ws, feat, q, w_v, alpha, ctx, beta, dgctx, dalpha_ext=None, re
     dbpre = torch.empty(B, D, dtype=torch.float32, device=dev)
     de = torch.empty(B, L, dtype=torch.float32, device=dev)
     dwv = torch.zeros(B, H, dtype=torch.float32, device=dev)
-    dfeat = torch.zeros_like(feat) if need_dfeat else None
+    dfeat = torch.zeros(feat.shape, dtype=torch.float32, device=dev) if need_dfeat else None
     check(lib.alexcap_attn_step_bwd(B, L, D, H, _ptr(Ws), _ptr(feat), _ptr(q), q.stride(0), _ptr(w_v), _ptr(alpha),
                                     alpha.stride(0), _ptr(ctx), _ptr(beta), _ptr(dgctx), dgctx.stride(0),
                                     _ptr(dalpha_ext), L, _ptr(reg_r), _ptr(dq), H, _ptr(dbpre), D, _ptr(de), L,
-                                    _ptr(dwv), _ptr(dfeat), _stream()), 'alexcap_attn_step_bwd')
+                                    _ptr(dwv), _ptr(dfeat), _rows_bf16(Ws, feat), _stream()), 'alexcap_attn_step_bwd')
     return dq, dbpre, de, dwv, dfeat
 
 
@@ -351,3 +358,10 @@ def set_gemm_engine(engine: int):
 
 def get_gemm_engine() -> int:
     return int(_lib.load().alexcap_get_gemm_engine())
+
+
+def set_time_loop(on: bool) -> bool:
+    """Forward recurrence as one persistent weight-stationary kernel (True) or as the PDL-chained per-step launches (False,
+    the default: faster at cfg2 on B200).  Set before staging a batch (the workspace layout depends on it).  Returns the
+    previous setting."""
+    return bool(_lib.load().alexcap_set_time_loop(int(bool(on))))

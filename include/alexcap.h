@@ -161,12 +161,29 @@ ALEXCAP_API int alexcap_attn_backward(const alexcap_dims* dims, const alexcap_at
                           void* workspace, size_t workspace_bytes, void* stream);
 
 /* Test / introspection hook: byte offset and size of a named region of the attention training workspace for `dims`
- * ("MASK": the [S,B,H] dropout mask the last step drew; "ALPHA": [B,S,L]; "H": [S+1,B,D+H] slots [gctx_t | h_{t-1}]).
+ * ("MASK": the [S,B,H] dropout mask the last step drew; "ALPHA": [B,S,L]; "H": [S+1,B,D+H] slots [gctx_t | h_{t-1}]; "LOGITS": the fp32 logits chunk of the NON-fused vocabulary path
+ * -- absent (ALEXCAP_E_BADARG) whenever the fused projection + cross-entropy epilogue is used, i.e. logits are never materialised).
  * Returns 0, or ALEXCAP_E_BADARG for an unknown name / a region this `dims` does not have. */
 ALEXCAP_API int alexcap_attn_workspace_region(const alexcap_dims* dims, const char* name, size_t* offset, size_t* bytes);
 
 /* m[b,:] = mean_l feat[b,l,:]  (Decoder.get_init_lstm_state, AttentionLanguageModule.py:117).  feat [B,L,D], m [B,D]. */
 ALEXCAP_API int alexcap_mean_over_L(const float* feat, int32_t B, int32_t L, int32_t D, float* m, void* stream);
+
+/* Selects how the forward recurrence of the attention decoder's training step runs (AttentionLanguageModule.py:72-82):
+ *   0 (default) = four launches per time step (query GEMM, fused attention step, gates GEMM, LSTM pointwise), chained with
+ *       programmatic dependent launch inside the caller's CUDA graph;
+ *   1 = ONE persistent cooperative kernel for all S steps (time_loop.cu): recurrent weights resident in shared memory as bf16
+ *       hi/lo pairs, the LSTM pointwise math done in the tcgen05 epilogue of the gates GEMM straight out of TMEM, the next
+ *       step's query GEMM behind a grid barrier instead of a kernel boundary.  Shapes whose weight slices do not fit
+ *       (B > 128, H > 512, ...) use 0 regardless.  Must be set BEFORE alexcap_attn_workspace_bytes is queried for a step
+ *       (the workspace carries the loop's bf16 operand buffers).  Returns the previous setting.  Process-wide.
+ * Measured at cfg2 on B200: 0 is ~4 % faster per training step; ALEXCAP_TIME_LOOP=1 sets the default. */
+ALEXCAP_API int alexcap_set_time_loop(int32_t on);
+
+/* Debug hook of the persistent time-loop kernels (time_loop.cu).  With ALEXCAP_LOOP_PROF=1 in the environment the kernels record
+ * %globaltimer stamps (ns) of CTA 0 at every phase boundary; this call synchronises the device and copies them to the HOST array
+ * host_out as [direction (0 forward, 1 backward)][step < 64][8 stamps].  Returns the number of uint64 written (0 = profiling off). */
+ALEXCAP_API int alexcap_time_loop_profile(unsigned long long* host_out, int32_t max_entries);
 
 /* ------------------------------------------------------------------ plain LSTM decoder (train) ---------- */
 ALEXCAP_API size_t alexcap_lstm_workspace_bytes(const alexcap_dims* dims);
@@ -276,12 +293,14 @@ ALEXCAP_API int alexcap_gemm_f32(int32_t transa, int32_t transb, int32_t M, int3
 
 /* One attention step, Attention.forward with W(features) precomputed (AttentionLanguageModule.py:15-22) and the
  * beta gate of Decoder.forward (:74-75) fused:  alpha[b,:] (row stride alpha_ld), ctx[B,D], beta[B,D],
- * gctx[b,:] (row stride gctx_ld) = sigmoid(bpre) * ctx.   q [B,H] (q_ld), bpre [B,D] (bpre_ld). */
+ * gctx[b,:] (row stride gctx_ld) = sigmoid(bpre) * ctx.   q [B,H] (q_ld), bpre [B,D] (bpre_ld).
+ * rows_bf16 != 0 (both step entry points): Ws and feat point at BF16 rows of the same shapes (the ALEXCAP_BF16 storage of the
+ * streamed grids, half the bytes per launch; D, H multiples of 8); everything else stays fp32. */
 ALEXCAP_API int alexcap_attn_step_fwd(int32_t B, int32_t L, int32_t D, int32_t H,
                           const float* Ws, const float* feat, const float* q, int64_t q_ld,
                           const float* bpre, int64_t bpre_ld, const float* w_v,
                           float* alpha, int64_t alpha_ld, float* ctx, float* beta,
-                          float* gctx, int64_t gctx_ld, void* stream);
+                          float* gctx, int64_t gctx_ld, int32_t rows_bf16, void* stream);
 
 /* Backward of one attention step.  In: dgctx [B,D] (ld), saved beta/ctx/alpha/q, optional extra d alpha terms
  * (dalpha_ext row stride ext_ld; reg_r [B,L]).  Out: dq [B,H] (ld), dbpre [B,D] (ld), de[b,:] (de_ld),
@@ -292,7 +311,7 @@ ALEXCAP_API int alexcap_attn_step_bwd(int32_t B, int32_t L, int32_t D, int32_t H
                           const float* dgctx, int64_t dgctx_ld,
                           const float* dalpha_ext, int64_t ext_ld, const float* reg_r,
                           float* dq, int64_t dq_ld, float* dbpre, int64_t dbpre_ld,
-                          float* de, int64_t de_ld, float* dwv_part, float* dfeat, void* stream);
+                          float* de, int64_t de_ld, float* dwv_part, float* dfeat, int32_t rows_bf16, void* stream);
 
 #ifdef __cplusplus
 }

@@ -112,6 +112,25 @@ def test_attn_step_back_to_back_is_deterministic(F_):
             assert all(torch.equal(x, y) for x, y in zip(o[:4], bfirst[:4]))
 
 
+def test_attn_step_bf16_row_storage_equals_fp32_kernel_on_rounded_rows(F_):
+    """ALEXCAP_BF16 storage of the streamed grids: with Ws / feat handed over as bf16 rows the kernels must compute exactly
+    what the fp32 kernels compute on the same (bf16-representable) values -- only the bytes per launch change.  Whole-image
+    and split-image partitions, both row widths of cfg3 (H = 1024, D = 2048)."""
+    for B, L, D, H in [(64, 49, 2048, 1024), (300, 49, 256, 128), (8, 196, 512, 512)]:
+        g = torch.Generator().manual_seed(B + 1)
+        f = lambda *s: torch.randn(*s, generator=g).to(DEV)
+        Ws, feat, q, bpre, wv, dg = f(B, L, H), f(B, L, D).relu(), f(B, H), f(B, D), f(H) / H ** 0.5, f(B, D)
+        Wb, fb = Ws.bfloat16(), feat.bfloat16()
+        ref = F_.attn_step_fwd(Wb.float(), fb.float(), q, bpre, wv)
+        got = F_.attn_step_fwd(Wb, fb, q, bpre, wv)
+        for x, y in zip(got, ref):
+            assert rel_err(x, y) < 1e-6
+        rb = F_.attn_step_bwd(Wb.float(), fb.float(), q, wv, ref[0], ref[1], ref[2], dg, need_dfeat=True)
+        gb = F_.attn_step_bwd(Wb, fb, q, wv, ref[0], ref[1], ref[2], dg, need_dfeat=True)
+        for x, y in zip(gb, rb):
+            assert rel_err(x, y) < 1e-6
+
+
 def test_make_target_matches_reference_semantics(F_):
     from oracle import restated as R
     V = 9

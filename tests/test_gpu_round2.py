@@ -9,6 +9,7 @@
 * N_valid from the captions, a fractional data-parallel CE divisor, out-of-range tokens, the graph cache key.
 """
 import math
+import os
 
 import pytest
 import torch
@@ -198,3 +199,85 @@ def test_elementwise_relative_error_of_large_entries():
         e = ((q.grad.double().cpu() - r).abs() / r.abs())[big]
         worst[k] = float(e.max())
     assert max(worst.values()) < 1e-2, worst
+
+
+@pytest.mark.parametrize('dtype', ['f32', 'bf16'])
+def test_fused_vocab_projection_ce_never_materialises_logits(dtype):
+    """north_star item 4: vocabulary projection + online-softmax CE + gradient in the tcgen05 epilogue (gemm_ps.cu EPI 1/2).
+    Shape chosen so that the three vocabulary GEMMs qualify for the pre-split engine, with a row-tile tail (S*B = 960), a
+    class tail (V' = 4003) and ragged captions (ignored rows)."""
+    from imagecaptioning_b200 import functional as F_
+    from imagecaptioning_b200.model import DecoderTrainStep
+    cfg = dict(B=60, L=16, D=64, H=256, E=64, V=4000, T=15)
+    S, Vp = cfg['T'] + 1, cfg['V'] + 3
+    p = random_attn_params(cfg, seed=12)
+    feat, gt = synth_inputs(cfg['B'], cfg['L'], cfg['D'], cfg['V'], cfg['T'], seed=13, dtype=torch.float64)
+    ref = R.attn_train_step(p, feat, gt, cfg['V'])
+    dec = build_decoder(cfg, p)
+    dec.compute_dtype = dtype
+    dec.train()
+    st = DecoderTrainStep(dec)
+    loss = st.forward_train(feat.float().to(DEV), gt.to(DEV))
+    tol = TOL if dtype == 'f32' else 2e-2
+    assert abs(float(loss) - float(ref['loss'])) < tol * float(ref['loss'])
+    assert float(st._loss[3]) == float(ref['n_valid'])
+    _check_grads({k: q.grad for k, q in dec.named_parameters()}, ref['grads'], tol)
+    # the fused path was taken: the workspace has no room for an fp32 logits matrix next to everything else it holds
+    logits_bytes = S * cfg['B'] * ((Vp + 3) // 4 * 4) * 4
+    from imagecaptioning_b200 import _lib
+    with pytest.raises(_lib.AlexcapError):                              # the layout has NO logits region at all
+        F_.attn_workspace_region(st._dims, st._ws, 'LOGITS', (1,))
+    assert st._ws.numel() < 3 * logits_bytes + (64 << 20)               # bf16 hi+lo copies of d logits only
+
+
+@pytest.fixture
+def time_loop():
+    from imagecaptioning_b200 import functional as F_
+    prev = F_.set_time_loop(True)
+    yield
+    F_.set_time_loop(prev)
+
+
+@pytest.mark.parametrize('cfg', [
+    dict(B=4, L=9, D=32, H=24, E=16, V=50, T=5),            # 6 owning CTAs, 16 query columns each, K tails (24, 32 < 64)
+    dict(B=24, L=49, D=256, H=192, E=96, V=700, T=9),       # 48 owning CTAs, two 8-column query chunks on some, none on others
+    dict(B=128, L=12, D=512, H=512, E=64, V=300, T=4),      # the cfg2 geometry: 128 CTAs, one image and 4 hidden units each
+    dict(B=37, L=20, D=128, H=128, E=32, V=90, T=6),        # more owning CTAs... fewer images than CTAs, odd batch
+], ids=['tiny', 'mid', 'cfg2geom', 'oddbatch'])
+@pytest.mark.parametrize('graph', [False, True])
+def test_persistent_time_loop_forward_vs_oracle(time_loop, cfg, graph):
+    """north_star item 3 (time_loop.cu): the whole forward recurrence in one persistent cooperative kernel -- weights resident
+    in shared memory, LSTM pointwise in the tcgen05 epilogue, next query GEMM behind a grid barrier -- against the fp64 oracle
+    (loss, every gradient, alphas), eager and replayed from a CUDA graph."""
+    from imagecaptioning_b200 import _lib
+    from imagecaptioning_b200.model import DecoderTrainStep
+    p = random_attn_params(cfg, seed=21)
+    feat, gt = synth_inputs(cfg['B'], cfg['L'], cfg['D'], cfg['V'], cfg['T'], seed=22, dtype=torch.float64)
+    ref = R.attn_train_step(p, feat, gt, cfg['V'], need_dfeat=True)
+    dec = build_decoder(cfg, p)
+    dec.train()
+    st = DecoderTrainStep(dec, use_cuda_graph=graph, need_dfeat=True)
+    lib = _lib.load()
+    for it in range(2):
+        for q in dec.parameters():
+            q.grad = None
+        n0 = lib.alexcap_launch_count()
+        loss = st.forward_train(feat.float().to(DEV), gt.to(DEV))
+        n1 = lib.alexcap_launch_count()
+    assert abs(float(loss) - float(ref['loss'])) < TOL * float(ref['loss'])
+    _check_grads({k: q.grad for k, q in dec.named_parameters()}, ref['grads'])
+    assert rel_err(st.dfeat, ref['dfeat']) < TOL
+    S = cfg['T'] + 1
+    from imagecaptioning_b200 import functional as F_
+    alphas = F_.attn_workspace_region(st._dims, st._ws, 'ALPHA', (cfg['B'], S, cfg['L']))
+    assert rel_err(alphas, ref['alphas']) < TOL
+    if not graph:
+        # the 4 * S forward launches of the chain are gone: 3 launches (weight pack, h0 split, the loop) replace them
+        F_.set_time_loop(False)
+        st2 = DecoderTrainStep(build_decoder(cfg, p).train(), need_dfeat=True)
+        st2.forward_train(feat.float().to(DEV), gt.to(DEV))
+        m0 = lib.alexcap_launch_count()
+        st2.forward_train(feat.float().to(DEV), gt.to(DEV))
+        chain = lib.alexcap_launch_count() - m0
+        F_.set_time_loop(True)
+        assert (n1 - n0) == chain - 4 * S + 3 - 1, (n1 - n0, chain)       # (-1: the weight-concatenation copy is not needed)
