@@ -406,6 +406,250 @@ gemm_ps_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
   }
 }
 
+// ------------------------------------------------------------------------------------------------ CTA-pair kernel
+// The same persistent pipeline with tcgen05 cta_group::2: the two CTAs of a cluster (an SM pair) work on ONE 256 x 256 output
+// tile.  Each CTA loads its own 128 rows of A and only ITS HALF (128 columns) of the B tile; the leader CTA issues one
+// M = 256, N = 256 MMA per k16 that reads A and B from both SMs' shared memory and writes each CTA's 128 accumulator rows
+// into that CTA's TMEM.  Per CTA and 64-deep k-block that is 16 KB (A) + 16 KB (B half) per operand copy for 128 x 256 x 64
+// MACs -- against 16 + 32 KB for the single-CTA 128 x 256 tile: a third less L2 -> shared-memory traffic per flop, which is
+// what bounds this kernel, and 3 ring stages instead of 2 in the bf16x3 mode.
+//   full_bar  (leader's): count 2 = the leader's arrive.expect_tx (bytes of BOTH CTAs) + the peer producer's remote arrive;
+//                         both CTAs' TMA loads complete_tx on it (.cta_group::2 form, peer bit of the barrier address cleared)
+//   empty_bar / tfull_bar (own, both CTAs): tcgen05.commit ... multicast::cluster with mask 0b11
+//   tempty_bar (leader's): count 2 * EPI_WARPS: the epilogue warps of both CTAs (the peer's arrive remotely)
+constexpr uint32_t PEER_MASK = 0xFEFFFFFFu;       // Sm100MmaPeerBitMask: shared::cluster address of the pair's even CTA
+constexpr int BM2 = 256, BN2 = 256;
+
+__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tma_load_2d_pair(void* smem_dst, const CUtensorMap* map, int c0, int c1, uint32_t leader_bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+      ::"r"(smem_u32(smem_dst)), "l"(map), "r"(c0), "r"(c1), "r"(leader_bar)
+      : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar_addr) : "memory");
+}
+__device__ __forceinline__ void umma_bf16_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accum) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accum)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
+}
+
+__device__ __forceinline__ Item decode_item2(const Params& p, int w) {
+  Item it;
+  it.split = w % p.splits;
+  const int t = w / p.splits;
+  it.m0 = (t % p.tiles_m) * BM2;
+  it.n0 = (t / p.tiles_m) * BN2;
+  it.kb0 = it.split * p.kb_per_split;
+  it.nkb = min(p.num_kb, it.kb0 + p.kb_per_split) - it.kb0;
+  return it;
+}
+
+template <bool A_MN, bool B_MN, int NPROD, int EPI>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
+gemm_ps2_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__ CUtensorMap tmAl,
+                const __grid_constant__ CUtensorMap tmBh, const __grid_constant__ CUtensorMap tmBl, const Params p) {
+  constexpr uint32_t A_BYTES = 128 * BK * 2, B_BYTES = 128 * BK * 2;          // per CTA: its A rows, its half of the B tile
+  constexpr uint32_t NOP = (NPROD == 3) ? 2 : 1;
+  constexpr uint32_t STAGE_BYTES = NOP * (A_BYTES + B_BYTES);
+  constexpr int STAGES = RING_BYTES / STAGE_BYTES;
+  constexpr uint32_t TMEM_COLS = 2 * BN2;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  float* epi = reinterpret_cast<float*>(smem + RING_BYTES);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + RING_BYTES + EPI_BYTES);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tfull_bar = empty_bar + STAGES;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 2); mbar_init(&empty_bar[s], 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], 2 * EPI_WARPS); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == MMA_WARP) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(TMEM_COLS));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;");
+  }
+  if (warp == TMA_WARP && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmAh) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmBh) : "memory");
+    if (NPROD == 3) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&tmAl) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&tmBl) : "memory");
+    }
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  cluster_sync_all();                              // both CTAs' barriers are initialised before anyone signals them
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_trigger();
+  pdl_wait();
+
+  if (warp == TMA_WARP) {
+    // ================================================================ TMA producer (one per CTA)
+    if (lane == 0) {
+      int s = 0; uint32_t ph = 0;
+      for (int w = cluster_id; w < p.n_items; w += n_clusters) {
+        const Item it = decode_item2(p, w);
+        const int m0 = it.m0 + 128 * (int)rank, n0 = it.n0 + 128 * (int)rank;
+        for (int i = 0; i < it.nkb; ++i) {
+          mbar_wait(&empty_bar[s], ph ^ 1);
+          uint8_t* st = smem + s * STAGE_BYTES;
+          const uint32_t lbar = smem_u32(&full_bar[s]) & PEER_MASK;          // the LEADER's barrier of this stage
+          if (leader) mbar_expect_tx(&full_bar[s], 2 * STAGE_BYTES);
+          else mbar_arrive_cluster(lbar);
+          const int k0 = (it.kb0 + i) * BK;
+#pragma unroll
+          for (uint32_t o = 0; o < NOP; ++o) {
+            const CUtensorMap* ma = o ? &tmAl : &tmAh;
+            uint8_t* sa = st + o * A_BYTES;
+            if (A_MN) {
+#pragma unroll
+              for (int j = 0; j < 2; ++j) tma_load_2d_pair(sa + j * MN_BOX_BYTES, ma, m0 + 64 * j, k0, lbar);
+            } else {
+              tma_load_2d_pair(sa, ma, k0, m0, lbar);
+            }
+            const CUtensorMap* mb = o ? &tmBl : &tmBh;
+            uint8_t* sb = st + NOP * A_BYTES + o * B_BYTES;
+            if (B_MN) {
+#pragma unroll
+              for (int j = 0; j < 2; ++j) tma_load_2d_pair(sb + j * MN_BOX_BYTES, mb, n0 + 64 * j, k0, lbar);
+            } else {
+              tma_load_2d_pair(sb, mb, k0, n0, lbar);
+            }
+          }
+          if (++s == STAGES) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else if (warp == MMA_WARP) {
+    // ================================================================ MMA issuer: the leader CTA's elected thread
+    if (leader) {
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
+                             ((uint32_t)(BN2 >> 3) << 17) | ((uint32_t)(BM2 >> 4) << 24);
+      int s = 0; uint32_t ph = 0;
+      int li = 0;
+      for (int w = cluster_id; w < p.n_items; w += n_clusters, ++li) {
+        const Item it = decode_item2(p, w);
+        const int acc = li & 1;
+        mbar_wait(&tempty_bar[acc], ((li >> 1) & 1) ^ 1);        // both CTAs' epilogues have drained this accumulator
+        tcgen05_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN2);
+        for (int i = 0; i < it.nkb; ++i) {
+          mbar_wait(&full_bar[s], ph);
+          tcgen05_fence_after();
+          if (lane == 0) {
+            const uint32_t a_hi = smem_u32(smem + s * STAGE_BYTES), a_lo = a_hi + A_BYTES;
+            const uint32_t b_hi = a_hi + NOP * A_BYTES, b_lo = b_hi + B_BYTES;
+#pragma unroll
+            for (int k = 0; k < BK / UMMA_K; ++k) {
+              const uint32_t a_off = A_MN ? k * 2048 : k * 32, b_off = B_MN ? k * 2048 : k * 32;
+              const uint64_t dah = A_MN ? make_desc(a_hi + a_off, MN_BOX_BYTES, 1024) : make_desc(a_hi + a_off, 0, 1024);
+              const uint64_t dbh = B_MN ? make_desc(b_hi + b_off, MN_BOX_BYTES, 1024) : make_desc(b_hi + b_off, 0, 1024);
+              if (NPROD == 3) {
+                const uint64_t dal = A_MN ? make_desc(a_lo + a_off, MN_BOX_BYTES, 1024) : make_desc(a_lo + a_off, 0, 1024);
+                const uint64_t dbl = B_MN ? make_desc(b_lo + b_off, MN_BOX_BYTES, 1024) : make_desc(b_lo + b_off, 0, 1024);
+                umma_bf16_pair(d_tmem, dal, dbh, idesc, (i | k) != 0);
+                umma_bf16_pair(d_tmem, dah, dbl, idesc, 1);
+                umma_bf16_pair(d_tmem, dah, dbh, idesc, 1);
+              } else {
+                umma_bf16_pair(d_tmem, dah, dbh, idesc, (i | k) != 0);
+              }
+            }
+            umma_commit_pair(&empty_bar[s]);                         // frees the stage in BOTH CTAs
+            if (i == it.nkb - 1) umma_commit_pair(&tfull_bar[acc]);  // accumulator complete, both CTAs
+          }
+          __syncwarp();
+          if (++s == STAGES) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else {
+    // ================================================================ epilogue warps (both CTAs: own 128 rows x 256 columns)
+    const int ew = warp - EPI_WARP0;
+    const int q4 = warp & 3;
+    const int half = ew >> 2;
+    constexpr int CPW = BN2 / 64;
+    float* tile = epi + ew * (32 * 33);
+    const bool atomic = p.splits > 1 || (p.accumulate && p.act == ACT_NONE && (int64_t)p.M * p.N <= (int64_t)(4 << 20));
+    const uint32_t ltempty0 = smem_u32(&tempty_bar[0]) & PEER_MASK, ltempty1 = smem_u32(&tempty_bar[1]) & PEER_MASK;
+    int li = 0;
+    for (int w = cluster_id; w < p.n_items; w += n_clusters, ++li) {
+      const Item it = decode_item2(p, w);
+      const int m0 = it.m0 + 128 * (int)rank;
+      const int acc = li & 1;
+      mbar_wait(&tfull_bar[acc], (li >> 1) & 1);
+      tcgen05_fence_after();
+      const uint32_t tbase = tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(acc * BN2);
+      const int row = m0 + q4 * 32 + lane;
+      const bool row_ok = row < p.M;
+      int y = -1; float lse = 0.f, scale = 0.f;
+      RowStat rs{-INFINITY, 0.f, 0.f, 0.f};
+      if (EPI != 0 && row_ok) {
+        y = __ldg(p.tgt + row);
+        if (EPI == 2) {
+          lse = __ldg(p.row_lse + row);
+          const float dn = __ldg(p.denom);
+          scale = (y != p.ignore_index && dn > 0.f) ? 1.f / dn : 0.f;
+        }
+      }
+#pragma unroll 1
+      for (int g = 0; g < CPW; g += 2) {
+        uint32_t v0[32], v1[32];
+        const int c0 = half * CPW + g, c1 = c0 + 1;
+        tmem_ld32(tbase + (uint32_t)(c0 * 32), v0);
+        tmem_ld32(tbase + (uint32_t)(c1 * 32), v1);
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        if (g + 2 >= CPW) {                       // last read of this accumulator: hand it back to the LEADER's MMA warp
+          tcgen05_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(acc ? ltempty1 : ltempty0);
+        }
+        if (EPI == 0) {
+          store_chunk(v0, tile, p, m0 + q4 * 32, it.n0 + c0 * 32, lane, atomic, it.split == 0);
+          store_chunk(v1, tile, p, m0 + q4 * 32, it.n0 + c1 * 32, lane, atomic, it.split == 0);
+        } else if (EPI == 1) {
+          if (row_ok) { ce_stats_chunk(v0, p, it.n0 + c0 * 32, y, rs); ce_stats_chunk(v1, p, it.n0 + c1 * 32, y, rs); }
+        } else {
+          ce_grad_chunk(v0, p, tile, m0 + q4 * 32, lane, it.n0 + c0 * 32, y, lse, scale);
+          ce_grad_chunk(v1, p, tile, m0 + q4 * 32, lane, it.n0 + c1 * 32, y, lse, scale);
+        }
+      }
+      if (EPI == 1 && row_ok)
+        p.stats[(int64_t)row * (p.tiles_n * 2) + (it.n0 / BN2) * 2 + half] = make_float4(rs.m, rs.s, rs.sx, rs.xt);
+    }
+  }
+
+  tcgen05_fence_before();
+  __syncthreads();
+  cluster_sync_all();                              // the peer may still be reading / signalling this CTA's shared memory
+  if (warp == MMA_WARP) {
+    tcgen05_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS));
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ host side
 // 2-D bf16 tensor map: inner (contiguous) extent, outer extent, row pitch ld elements, box {64, box_outer}, 128B swizzle.
 static bool make_map_bf16(CUtensorMap* map, const uint16_t* base, int64_t inner, int64_t outer, int64_t ld, int box_outer) {
@@ -432,6 +676,24 @@ static cudaError_t launch(cudaStream_t st, const CUtensorMap* maps, const Params
   }
   ALEXCAP_NOTE_LAUNCH();
   return launch_pdl(kern, dim3(grid), dim3(NUM_THREADS), SMEM, st, maps[0], maps[1], maps[2], maps[3], p);
+}
+
+template <bool A_MN, bool B_MN, int NPROD, int EPI = 0>
+static cudaError_t launch2(cudaStream_t st, const CUtensorMap* maps, const Params& p, int grid) {
+  constexpr size_t SMEM = (size_t)RING_BYTES + EPI_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+  static bool configured = false;
+  auto kern = gemm_ps2_kernel<A_MN, B_MN, NPROD, EPI>;
+  if (!configured) {
+    ACK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+    configured = true;
+  }
+  ALEXCAP_NOTE_LAUNCH();
+  return launch_pdl(kern, dim3(grid), dim3(NUM_THREADS), SMEM, st, maps[0], maps[1], maps[2], maps[3], p);
+}
+// CTA-pair (cta_group::2) tiles: ALEXCAP_PS_PAIR=1 enables / =0 disables (default below)
+static bool pair_enabled() {
+  static const bool on = [] { const char* v = getenv("ALEXCAP_PS_PAIR"); return v ? v[0] == '1' : false; }();
+  return on;
 }
 
 struct Split { uint16_t* hi; uint16_t* lo; int64_t ld; };
@@ -539,6 +801,53 @@ cudaError_t gemm_ps_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, 
   if (e == cudaSuccess) e = get_split(st, arena, B, tb ? N : K, tb ? K : N, ldb, with_lo, &sb);
   if (e != cudaSuccess) { split_arena_release(arena, mark); return e; }
 
+  int nsm = 148;
+  { int dev = 0; if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev); }
+  // ---- CTA-pair 256 x 256 tiles (cta_group::2) when the output is large enough to give every SM pair work
+  if (pair_enabled() && M >= 256 && N >= 256 && (int64_t)ceil_div(M, BM2) * ceil_div(N, BN2) >= 8) {
+    const int ncl = nsm / 2;
+    const int num_kb = ceil_div(K, BK);
+    const int tiles_m = ceil_div(M, BM2), tiles_n = ceil_div(N, BN2), tiles = tiles_m * tiles_n;
+    int splits = 1;
+    if (force_splits > 0) splits = force_splits;
+    else if (act == ACT_NONE && tiles < (2 * ncl) / 3) {
+      splits = ncl / tiles;
+      const int max_by_k = num_kb / 2 > 0 ? num_kb / 2 : 1;
+      if (splits > max_by_k) splits = max_by_k;
+      if (splits < 1) splits = 1;
+    }
+    if (act != ACT_NONE) splits = 1;
+    const int kb_per = ceil_div(num_kb, splits);
+    splits = ceil_div(num_kb, kb_per);
+    if (splits > 1 && !accumulate) ACK(cudaMemset2DAsync(C, ldc * sizeof(float), 0, (size_t)N * sizeof(float), M, st));
+    CUtensorMap maps[4];
+    bool ok = true;
+    for (int o = 0; o < (with_lo ? 2 : 1); ++o) {
+      const uint16_t* pa = o ? sa.lo : sa.hi;
+      const uint16_t* pb = o ? sb.lo : sb.hi;
+      ok = ok && (a_mn ? make_map_bf16(&maps[o], pa, M, K, sa.ld, 64) : make_map_bf16(&maps[o], pa, K, M, sa.ld, 128));
+      ok = ok && (b_mn ? make_map_bf16(&maps[2 + o], pb, N, K, sb.ld, 64) : make_map_bf16(&maps[2 + o], pb, K, N, sb.ld, 128));
+    }
+    if (!with_lo) { maps[1] = maps[0]; maps[3] = maps[2]; }
+    if (!ok) return cudaErrorInvalidValue;
+    Params p = {};
+    p.C = C; p.bias = bias; p.bias2 = bias2; p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.alpha = alpha;
+    p.accumulate = accumulate ? 1 : 0; p.act = act;
+    p.tiles_m = tiles_m; p.tiles_n = tiles_n; p.splits = splits; p.kb_per_split = kb_per; p.num_kb = num_kb;
+    p.n_items = tiles * splits;
+    const int grid = 2 * (p.n_items < ncl ? p.n_items : ncl);
+#define PS2_DISPATCH(NP_)                                                                  \
+  do {                                                                                     \
+    if (!a_mn && !b_mn) return launch2<false, false, NP_>(st, maps, p, grid);              \
+    if (!a_mn && b_mn) return launch2<false, true, NP_>(st, maps, p, grid);                \
+    if (a_mn && b_mn) return launch2<true, true, NP_>(st, maps, p, grid);                  \
+    return launch2<true, false, NP_>(st, maps, p, grid);                                   \
+  } while (0)
+    if (with_lo) PS2_DISPATCH(3);
+    PS2_DISPATCH(1);
+#undef PS2_DISPATCH
+  }
+
   static const int bn_env = [] { const char* v = getenv("ALEXCAP_PS_BN"); return v ? atoi(v) : 0; }();
   const int BN = (bn_env == 128 || bn_env == 256) ? bn_env : ((N >= 1024 && (int64_t)ceil_div(M, BM) * ceil_div(N, 256) >= 296) ? 256 : 128);
   const int num_kb = ceil_div(K, BK);
@@ -574,8 +883,6 @@ cudaError_t gemm_ps_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, 
   p.accumulate = accumulate ? 1 : 0; p.act = act;
   p.tiles_m = tiles_m; p.tiles_n = tiles_n; p.splits = splits; p.kb_per_split = kb_per; p.num_kb = num_kb;
   p.n_items = tiles * splits;
-  int nsm = 148;
-  { int dev = 0; if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev); }
   const int grid = p.n_items < nsm ? p.n_items : nsm;
 #define PS_DISPATCH(BN_, NP_)                                                              \
   do {                                                                                     \
@@ -662,6 +969,24 @@ cudaError_t gemm_ps_ce(cudaStream_t st, bool want_grad, int M, int N, int K, con
   { int dev = 0; if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev); }
   const int grid = p.n_items < nsm ? p.n_items : nsm;
   cudaError_t e;
+  if (BN == 256 && pair_enabled() && M >= 256) {
+    // CTA-pair tiles: same 256-column partition of the classes (the statistics layout does not change), 256-row tiles
+    p.tiles_m = ceil_div(M, BM2); p.n_items = p.tiles_m * p.tiles_n;
+    bool ok2 = true;
+    for (int o = 0; o < (with_lo ? 2 : 1); ++o) ok2 = ok2 && make_map_bf16(&maps[2 + o], o ? sb.lo : sb.hi, K, N, sb.ld, 128);
+    if (!with_lo) maps[3] = maps[2];
+    if (!ok2) return cudaErrorInvalidValue;
+    const int ncl = nsm / 2;
+    const int grid2 = 2 * (p.n_items < ncl ? p.n_items : ncl);
+    if (!want_grad) {
+      e = with_lo ? launch2<false, false, 3, 1>(st, maps, p, grid2) : launch2<false, false, 1, 1>(st, maps, p, grid2);
+      ACK(e);
+      ALEXCAP_NOTE_LAUNCH();
+      ce_combine_kernel<<<ceil_div(M, 8), 256, 0, st>>>(stats, p.tiles_n * 2, tgt, M, N, eps, ignore_index, denom, row_lse, row_loss);
+      return cudaGetLastError();
+    }
+    return with_lo ? launch2<false, false, 3, 2>(st, maps, p, grid2) : launch2<false, false, 1, 2>(st, maps, p, grid2);
+  }
   if (!want_grad) {
     if (BN == 256) e = with_lo ? launch<256, false, false, 3, 1>(st, maps, p, grid) : launch<256, false, false, 1, 1>(st, maps, p, grid);
     else e = with_lo ? launch<128, false, false, 3, 1>(st, maps, p, grid) : launch<128, false, false, 1, 1>(st, maps, p, grid);
