@@ -413,8 +413,12 @@ gemm_ps_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
 // into that CTA's TMEM.  Per CTA and 64-deep k-block that is 16 KB (A) + 16 KB (B half) per operand copy for 128 x 256 x 64
 // MACs -- against 16 + 32 KB for the single-CTA 128 x 256 tile: a third less L2 -> shared-memory traffic per flop, which is
 // what bounds this kernel, and 3 ring stages instead of 2 in the bf16x3 mode.
-//   full_bar  (leader's): count 2 = the leader's arrive.expect_tx (bytes of BOTH CTAs) + the peer producer's remote arrive;
-//                         both CTAs' TMA loads complete_tx on it (.cta_group::2 form, peer bit of the barrier address cleared)
+//   full_bar  (leader's): count 1 = the leader's arrive.expect_tx for the bytes of BOTH CTAs; both CTAs' TMA loads complete_tx
+//                         on it (.cta_group::2 form, peer bit of the barrier address cleared).  The peer's bytes may land before
+//                         the leader has armed the phase (the transaction count goes negative, the pending arrival keeps the
+//                         phase open); the peer cannot be a whole ring ahead because its stage is only freed by the leader's
+//                         MMA commit.  (A per-k-block remote arrive by the peer producer was measured: it stalls that thread
+//                         ~1 us per k-block and halved the bf16 rate.)
 //   empty_bar / tfull_bar (own, both CTAs): tcgen05.commit ... multicast::cluster with mask 0b11
 //   tempty_bar (leader's): count 2 * EPI_WARPS: the epilogue warps of both CTAs (the peer's arrive remotely)
 constexpr uint32_t PEER_MASK = 0xFEFFFFFFu;       // Sm100MmaPeerBitMask: shared::cluster address of the pair's even CTA
@@ -482,7 +486,7 @@ gemm_ps2_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant_
   const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 2); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], 2 * EPI_WARPS); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -518,7 +522,6 @@ gemm_ps2_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant_
           uint8_t* st = smem + s * STAGE_BYTES;
           const uint32_t lbar = smem_u32(&full_bar[s]) & PEER_MASK;          // the LEADER's barrier of this stage
           if (leader) mbar_expect_tx(&full_bar[s], 2 * STAGE_BYTES);
-          else mbar_arrive_cluster(lbar);
           const int k0 = (it.kb0 + i) * BK;
 #pragma unroll
           for (uint32_t o = 0; o < NOP; ++o) {
@@ -690,10 +693,18 @@ static cudaError_t launch2(cudaStream_t st, const CUtensorMap* maps, const Param
   ALEXCAP_NOTE_LAUNCH();
   return launch_pdl(kern, dim3(grid), dim3(NUM_THREADS), SMEM, st, maps[0], maps[1], maps[2], maps[3], p);
 }
-// CTA-pair (cta_group::2) tiles: ALEXCAP_PS_PAIR=1 enables / =0 disables (default below)
-static bool pair_enabled() {
-  static const bool on = [] { const char* v = getenv("ALEXCAP_PS_PAIR"); return v ? v[0] == '1' : false; }();
-  return on;
+// CTA-pair (cta_group::2) tiles.  ALEXCAP_PS_PAIR=0 never, =1 whenever the shape allows, default = where they measured
+// faster on B200 (profiles/r2_gemm_pair.txt): bf16x3 mode when the main loop dominates a tile (K >= 1024; at K = 512 the
+// epilogue bounds both kernels and the 256-row tiles only add M-quantisation waste); bf16 single-product mode only for
+// the split-K shapes (few output tiles, long K: dH, dW_o, the lstm dW GEMMs) -- on large outputs the pair kernel's loads
+// reach ~28 B/clk/SM against ~51 for the single-CTA kernel and it is slower.
+static bool pair_wanted(int M, int N, int K, int nprod) {
+  static const int mode = [] { const char* v = getenv("ALEXCAP_PS_PAIR"); return v ? (v[0] == '1' ? 1 : 0) : 2; }();
+  if (mode == 0 || M < 256 || N < 256) return false;
+  const int64_t tiles = (int64_t)ceil_div(M, BM2) * ceil_div(N, BN2);
+  if (tiles < 8) return false;
+  if (mode == 1) return true;
+  return nprod == 3 ? K >= 1024 : (K >= 2048 && tiles < 148);
 }
 
 struct Split { uint16_t* hi; uint16_t* lo; int64_t ld; };
@@ -804,7 +815,7 @@ cudaError_t gemm_ps_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, 
   int nsm = 148;
   { int dev = 0; if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev); }
   // ---- CTA-pair 256 x 256 tiles (cta_group::2) when the output is large enough to give every SM pair work
-  if (pair_enabled() && M >= 256 && N >= 256 && (int64_t)ceil_div(M, BM2) * ceil_div(N, BN2) >= 8) {
+  if (pair_wanted(M, N, K, nprod)) {
     const int ncl = nsm / 2;
     const int num_kb = ceil_div(K, BK);
     const int tiles_m = ceil_div(M, BM2), tiles_n = ceil_div(N, BN2), tiles = tiles_m * tiles_n;
@@ -969,7 +980,7 @@ cudaError_t gemm_ps_ce(cudaStream_t st, bool want_grad, int M, int N, int K, con
   { int dev = 0; if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev); }
   const int grid = p.n_items < nsm ? p.n_items : nsm;
   cudaError_t e;
-  if (BN == 256 && pair_enabled() && M >= 256) {
+  if (BN == 256 && pair_wanted(M, N, K, nprod)) {
     // CTA-pair tiles: same 256-column partition of the classes (the statistics layout does not change), 256-row tiles
     p.tiles_m = ceil_div(M, BM2); p.n_items = p.tiles_m * p.tiles_n;
     bool ok2 = true;

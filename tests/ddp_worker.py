@@ -47,9 +47,17 @@ def ddp_check(dev, rank, world, cfg, graph=True, seed=31, steps=3):
     loss_one = one.run_resident().clone()
     torch.cuda.synchronize()
     worst = 0.0
-    for a, b in zip(step._grads, one._grads):
+    from imagecaptioning_b200._lib import ATTN_STATE_NAMES
+    detail = {}
+    for name, a, b in zip(ATTN_STATE_NAMES, step._grads, one._grads):
+        if name == 'attention.v.bias':          # identically zero (softmax shift invariance): no scale to be relative to
+            continue
         scale = max(float(b.abs().max()), 1e-30)
-        worst = max(worst, float((a - b).abs().max()) / scale)
+        e = float((a - b).abs().max()) / scale
+        detail[name] = e
+        worst = max(worst, e)
+    if rank == 0 and worst > 1e-4:
+        sys.stderr.write('DDP_DETAIL graph=%s %s\n' % (graph, json.dumps({k: float('%.2e' % v) for k, v in detail.items()})))
     loss_rel = abs(float(loss_ddp[0]) - float(loss_one[0])) / abs(float(loss_one[0]))
     # every rank must hold the same averaged gradients
     chk = got.double().abs().sum().reshape(1)
