@@ -74,6 +74,8 @@ PROTOTYPES = {
     'alexcap_lstm_backward': (C.c_int, [_DP, _LP, _P, _P, _LP, _P, _P, _SZ, _P]),
     'alexcap_make_target': (C.c_int, [_P, _P, _P, _I32, _I32, _I32, _I32, _P]),
     'alexcap_cross_entropy': (C.c_int, [_P, _P, _I32, _I32, _I64, _F, _I32, _P, _P, _P, _P]),
+    'alexcap_cross_entropy_static_max_rows': (C.c_int32, []),
+    'alexcap_cross_entropy_static': (C.c_int, [_P, _P, _I32, _I32, _I64, _F, _I32, _P, _P, _P]),
     'alexcap_attn_decode_workspace_bytes': (_SZ, [_DP, _I32]),
     'alexcap_attn_decode_greedy': (C.c_int, [_DP, _AP, _P, _P, _P, _P, _SZ, _P]),
     'alexcap_attn_decode_beam': (C.c_int, [_DP, _AP, _P, _I32, _P, _P, _P, _P, _P, _SZ, _P]),

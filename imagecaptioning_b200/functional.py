@@ -229,6 +229,19 @@ def cross_entropy(logits2d, tgt, label_smoothing=0.1, ignore_index=0, want_grad=
     return out, dl
 
 
+def cross_entropy_static(logits2d, tgt, loss_out, dlogits=None, label_smoothing=0.1, ignore_index=0):
+    """alexcap_cross_entropy_static: the same loss and gradient with the library's file-scope device scratch instead of a
+    caller-provided one.  Allocates nothing (not here either: the caller passes loss_out [2] and, optionally, dlogits);
+    N is limited to alexcap_cross_entropy_static_max_rows(); calls that overlap on the GPU race on the shared scratch."""
+    lib = ensure_device(logits2d.device)
+    _req(logits2d, tgt, loss_out, dlogits)
+    N, Cc = logits2d.shape
+    check(lib.alexcap_cross_entropy_static(_ptr(logits2d), _ptr(tgt), N, Cc, logits2d.stride(0), label_smoothing,
+                                           ignore_index, _ptr(loss_out), _ptr(dlogits), _stream()),
+          'alexcap_cross_entropy_static')
+    return loss_out, dlogits
+
+
 # ------------------------------------------------------------------------------------------------ attention decoder
 def attn_workspace_bytes(dims: Dims) -> int:
     return int(_lib.load().alexcap_attn_workspace_bytes(C.byref(dims)))

@@ -222,6 +222,21 @@ ALEXCAP_API int alexcap_cross_entropy(const float* logits, const int32_t* tgt, i
                           float label_smoothing, int32_t ignore_index,
                           float* loss_out, float* dlogits, float* scratch, void* stream);
 
+/* alexcap_cross_entropy without the caller-provided scratch, for callers that cannot allocate device memory (code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid cudaMalloc).  NO counterpart in the reference.
+ * Same arithmetic, same kernels, same outputs as alexcap_cross_entropy; the scratch is a
+ * file-scope __device__ array inside the library (csrc/no_alloc.cu; 2 * ALEXCAP_CE_STATIC_MAX_ROWS floats = 512 KB on every
+ * GPU that loads the library, held until the process exits).  The call allocates and frees nothing.
+ *   N > ALEXCAP_CE_STATIC_MAX_ROWS is rejected with ALEXCAP_E_UNSUPPORTED (message via alexcap_last_error()).
+ *   Every call on a device shares the one array, which keeps the previous call's contents (the part a call uses is cleared
+ *   on `stream` first): calls that may OVERLAP on the GPU (different streams without an ordering between them) race --
+ *   serialise them, or use alexcap_cross_entropy with separate scratch buffers. */
+#define ALEXCAP_CE_STATIC_MAX_ROWS 65536
+ALEXCAP_API int32_t alexcap_cross_entropy_static_max_rows(void);
+ALEXCAP_API int alexcap_cross_entropy_static(const float* logits, const int32_t* tgt, int32_t N, int32_t C, int64_t ld,
+                          float label_smoothing, int32_t ignore_index,
+                          float* loss_out, float* dlogits, void* stream);
+
 /* ------------------------------------------------------------------ decoding ---------------------------
  * Decoder.forward greedy branch (AttentionLanguageModule.py:88-115), batched (the reference's own code only
  * works for B=1, :108-109).  ids [B,S] int64, alphas [B,S,L]; rows keep decoding until ALL rows emitted END
