@@ -121,6 +121,13 @@ AttnWs attn_layout(const alexcap_dims* d, void* base, bool with_logits) {
 // feat 2 * S times per training step; in bf16 mode they read bf16 copies (half the bytes per launch).  feat's copy is the one
 // the hoisted Ws GEMM made of its A operand; Ws gets one split pass per training step.  NULL pointers = stream fp32.
 struct AttnRows { const float* Ws; const float* feat; bool bf16; };
+// The streaming attention kernels take the hoisted Ws = W(features) in exponential form (ACT_EXP2C, common.cuh): one MUFU op
+// per score element instead of two in the forward, backward and dWs kernels.  Engine 0 (direct-load kernels) keeps raw Ws.
+// ALEXCAP_ATT_WS_EXP=0 switches the factoring off (A/B timing).
+static bool attn_ws_exp(int D, int H) {
+  static const bool off = [] { const char* v = getenv("ALEXCAP_ATT_WS_EXP"); return v && v[0] == '0'; }();
+  return !off && attn_engine() == 1 && attn_stream_supported(D, H);
+}
 AttnRows attn_rows(const alexcap_dims* d, const float* feat, const AttnWs& w, cudaStream_t st) {
   AttnRows r{w.Ws, feat, false};
   static const bool off = [] { const char* v = getenv("ALEXCAP_ATT_BF16_ROWS"); return v && v[0] == '0'; }();
@@ -151,13 +158,15 @@ int attn_fwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
   API_CK(gemm_f32(st, false, true, B, H, D, 1.f, w.m, D, P->init_h_w, D, w.XH + D, DH, P->init_h_b, nullptr, false, ACT_TANH));
   API_CK(gemm_f32(st, false, true, B, H, D, 1.f, w.m, D, P->init_c_w, D, w.Call, H, P->init_c_b, nullptr, false, ACT_TANH));
   // hoisted projections
-  API_CK(gemm_f32(st, false, true, B * L, H, D, 1.f, feat, D, P->att_W_w, D, w.Ws, H, P->att_W_b, nullptr, false, ACT_NONE));
+  const bool ws_exp = attn_ws_exp(D, H);
+  API_CK(gemm_f32(st, false, true, B * L, H, D, 1.f, feat, D, P->att_W_w, D, w.Ws, H, P->att_W_b, nullptr, false,
+                  ws_exp ? ACT_EXP2C : ACT_NONE));
   API_CK(gather_rows(st, P->emb_w, w.in_tm, S * B, E, w.EmbIn, E));
   API_CK(gemm_f32(st, false, true, S * B, 4 * H, E, 1.f, w.EmbIn, E, P->lstm_w_ih, E + D, w.DGQ, W5, P->lstm_b_ih,
                   P->lstm_b_hh, false, ACT_NONE));
   // The recurrence.  Default (tcgen05 engines, shapes whose recurrent weights fit in shared memory): ONE persistent kernel
   // for all S steps (time_loop.cu).  Otherwise the per-step chain below.
-  const bool loop_ok = w.loop_bf16 && gemm_engine() >= 2 && attn_engine() != 0 && attn_loop_supported(B, L, D, H);
+  const bool loop_ok = w.loop_bf16 && gemm_engine() >= 2 && ws_exp && attn_loop_supported(B, L, D, H);   // (the loop's attention body reads EXP2C(Ws))
   // concatenated weights: Wcat = [W_ih[:,E:] | W_hh] (4H x (D+H));  Wub = [W_U ; W_beta] ((H+D) x H)
   if (!loop_ok) {
     CopySegments cs;
@@ -183,9 +192,10 @@ int attn_fwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
       float* qb = w.QB + (int64_t)t * B * HD;
       float* g = w.DGQ + (int64_t)t * B * W5;
       { WeightBScope wb; API_CK(gemm_f32(st, false, true, B, H + D, H, 1.f, xh + D, DH, w.Wub, H, qb, HD, w.bub, nullptr, true, ACT_NONE)); }
-      if (rows.bf16)
+      if (rows.bf16 || ws_exp)
         API_CK(attn_step_fwd_stream(st, B, L, D, H, rows.Ws, rows.feat, qb, HD, qb + H, HD, P->att_v_w, w.ALPHA + (int64_t)t * L,
-                                    (int64_t)S * L, w.CTX + (int64_t)t * B * D, w.BETA + (int64_t)t * B * D, xh, DH, 1, true));
+                                    (int64_t)S * L, w.CTX + (int64_t)t * B * D, w.BETA + (int64_t)t * B * D, xh, DH, 1, rows.bf16,
+                                    ws_exp));
       else
         API_CK(attn_step_fwd(st, B, L, D, H, w.Ws, feat, qb, HD, qb + H, HD, P->att_v_w, w.ALPHA + (int64_t)t * L,
                              (int64_t)S * L, w.CTX + (int64_t)t * B * D, w.BETA + (int64_t)t * B * D, xh, DH));
@@ -255,6 +265,7 @@ int attn_bwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
   API_CK(cudaMemsetAsync(w.dh_next, 0, sizeof(float) * (size_t)S * B * H, st));
 
   const AttnRows rows = attn_rows(d, feat, w, st);      // (arena hits: the copies were made by the forward phase)
+  const bool ws_exp = attn_ws_exp(D, H);                // (the same decision the forward phase took for the Ws GEMM)
   for (int t = S - 1; t >= 0; --t) {
     float* dgc = w.dgctx + (int64_t)t * B * D;
     float* dhn = w.dh_next + (int64_t)t * B * H;                  // dh_{t-1}, consumed by reverse step t-1
@@ -266,12 +277,12 @@ int attn_bwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
     // d gctx = dgates W_ih[:, E:]
     { WeightBScope wb; API_CK(gemm_f32(st, false, false, B, D, 4 * H, 1.f, g, W5, P->lstm_w_ih + E, E + D, dgc, D, nullptr, nullptr,
                     true, ACT_NONE)); }
-    if (rows.bf16)
+    if (rows.bf16 || ws_exp)
       API_CK(attn_step_bwd_stream(st, B, L, D, H, rows.Ws, rows.feat, qb, HD, P->att_v_w, w.ALPHA + (int64_t)t * L, (int64_t)S * L,
                                   w.CTX + (int64_t)t * B * D, w.BETA + (int64_t)t * B * D, dgc, D,
                                   dalphas ? dalphas + (int64_t)t * L : nullptr, (int64_t)S * L, reg_r,
                                   g + 4 * H, W5, g + 5 * H, W5, w.DE + (int64_t)t * L, (int64_t)S * L, w.dwv_part,
-                                  need_dfeat ? dfeat : nullptr, true));
+                                  need_dfeat ? dfeat : nullptr, rows.bf16, ws_exp));
     else
       API_CK(attn_step_bwd(st, B, L, D, H, w.Ws, feat, qb, HD, P->att_v_w, w.ALPHA + (int64_t)t * L, (int64_t)S * L,
                            w.CTX + (int64_t)t * B * D, w.BETA + (int64_t)t * B * D, dgc, D,
@@ -302,7 +313,7 @@ int attn_bwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
                         split_arena_reserve(arena, w.dWs, B * L, H, H, gemm_engine() == 3, &d_hi, &d_lo, &d_ld);
     static const int per_sm = [] { const char* v = getenv("ALEXCAP_DWS_CTAS_PER_SM"); return v ? atoi(v) : 4; }();
     API_CK(attn_dws(st_dws, B, L, H, S, w.Ws, w.QB, HD, P->att_v_w, w.DE, direct ? nullptr : w.dWs, d_hi, d_lo, d_ld,
-                    overlap ? 148 * per_sm : 0));
+                    overlap ? 148 * per_sm : 0, ws_exp));
   }
   if (overlap) API_CK(cudaEventRecord(side.join, side.s));
   // lstm weights: dW = dgates_all^T [EmbIn | gctx | h_prev], K = S*B

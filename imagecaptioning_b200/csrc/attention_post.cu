@@ -25,7 +25,7 @@ __global__ void __launch_bounds__(256) attn_dws_kernel(int L, int H, int S, int 
                                                        const float* __restrict__ q, int64_t q_ld,
                                                        const float* __restrict__ wv, const float* __restrict__ de,
                                                        float* __restrict__ dWs, uint16_t* __restrict__ d_hi,
-                                                       uint16_t* __restrict__ d_lo, int64_t d_ld) {
+                                                       uint16_t* __restrict__ d_lo, int64_t d_ld, int ws_exp) {
   const int H4 = H >> 2, gx = (L + DWS_ROWS - 1) / DWS_ROWS, ntiles = gx * B;
   // grid-stride over (image, row group) tiles: the launcher may cap the grid so that the kernel leaves room on every SM for
   // a concurrently running GEMM (see api.cu: dWs is forked next to the lstm dW GEMMs)
@@ -37,7 +37,8 @@ __global__ void __launch_bounds__(256) attn_dws_kernel(int L, int H, int S, int 
 #pragma unroll
     for (int r = 0; r < DWS_ROWS; ++r) {
       const int l = l0 + r;
-      ew[r] = exp2c4((l < L) ? ldg4(reinterpret_cast<const float4*>(Ws) + ((int64_t)b * L + l) * H4 + c) : f4_zero());
+      const float4 wr = (l < L) ? ldg4(reinterpret_cast<const float4*>(Ws) + ((int64_t)b * L + l) * H4 + c) : f4_zero();
+      ew[r] = ws_exp ? wr : exp2c4(wr);              // (ws_exp: the hoisted GEMM already stored e^{2w})
       acc[r] = f4_zero();
     }
     for (int t = 0; t < S; ++t) {
@@ -80,12 +81,13 @@ __global__ void __launch_bounds__(256) attn_dws_kernel(int L, int H, int S, int 
 }
 
 cudaError_t attn_dws(cudaStream_t st, int B, int L, int H, int S, const float* Ws, const float* q, int64_t q_ld,
-                     const float* wv, const float* de, float* dWs, uint16_t* d_hi, uint16_t* d_lo, int64_t d_ld, int max_ctas) {
+                     const float* wv, const float* de, float* dWs, uint16_t* d_hi, uint16_t* d_lo, int64_t d_ld, int max_ctas,
+                     bool ws_exp) {
   if ((H & 3) || (q_ld & 3) || (d_hi && (d_ld & 3))) return cudaErrorInvalidValue;
   int grid = ceil_div(L, DWS_ROWS) * B;
   if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
   const int threads = (H / 4 >= 256) ? 256 : ((H / 4 + 31) / 32) * 32;
-  ALEXCAP_NOTE_LAUNCH(); attn_dws_kernel<<<grid, threads, 0, st>>>(L, H, S, B, Ws, q, q_ld, wv, de, dWs, d_hi, d_lo, d_ld);
+  ALEXCAP_NOTE_LAUNCH(); attn_dws_kernel<<<grid, threads, 0, st>>>(L, H, S, B, Ws, q, q_ld, wv, de, dWs, d_hi, d_lo, d_ld, ws_exp ? 1 : 0);
   return cudaGetLastError();
 }
 

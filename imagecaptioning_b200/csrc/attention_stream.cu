@@ -166,7 +166,7 @@ bool attn_stream_supported(int D, int H) {
 
 // ------------------------------------------------------------------------------------------ forward step
 // Stand-alone kernels: one launch per time step around the shared bodies (attention_stream.cuh).
-template <int NJ, bool FULL, bool BF>
+template <int NJ, bool FULL, bool BF, bool EW>
 __global__ void __launch_bounds__(SA_THREADS, 1) attn_fwd_stream_kernel(const SAttnFwdP a) {
   extern __shared__ __align__(128) float sm[];
   if (threadIdx.x == 0) attn_ring_init(sm, a.NST, a.stage_floats);
@@ -175,10 +175,10 @@ __global__ void __launch_bounds__(SA_THREADS, 1) attn_fwd_stream_kernel(const SA
   pdl_wait();
   Cursor k{0, 0u};
   int kg = 0;
-  attn_fwd_body<NJ, FULL, SA_NC, BF>(a, sm, (int)blockIdx.x, k, kg);
+  attn_fwd_body<NJ, FULL, SA_NC, BF, EW>(a, sm, (int)blockIdx.x, k, kg);
 }
 
-template <bool ALLWHOLE, bool BF>
+template <bool ALLWHOLE, bool BF, bool EW>
 __global__ void __launch_bounds__(SA_THREADS, 1) attn_bwd_stream_kernel(const SAttnBwdP a) {
   extern __shared__ __align__(128) float sm[];
   if (threadIdx.x == 0) attn_ring_init(sm, a.NST, a.stage_floats);
@@ -187,7 +187,7 @@ __global__ void __launch_bounds__(SA_THREADS, 1) attn_bwd_stream_kernel(const SA
   pdl_wait();
   Cursor k{0, 0u};
   int kg = 0;
-  attn_bwd_body<ALLWHOLE, BF>(a, sm, (int)blockIdx.x, k, kg);
+  attn_bwd_body<ALLWHOLE, BF, EW>(a, sm, (int)blockIdx.x, k, kg);
 }
 
 static size_t fwd_fixed_smem(int D, int seg_pad, int maxseg) {
@@ -197,7 +197,7 @@ static size_t fwd_fixed_smem(int D, int seg_pad, int maxseg) {
 cudaError_t attn_step_fwd_stream(cudaStream_t st, int B, int L, int D, int H, const float* Ws, const float* feat,
                                  const float* q, int64_t q_ld, const float* bpre, int64_t bpre_ld, const float* wv,
                                  float* alpha, int64_t alpha_ld, float* ctx, float* beta, float* gctx, int64_t gctx_ld,
-                                 int rows_per_image, bool rows_bf16) {
+                                 int rows_per_image, bool rows_bf16, bool ws_exp) {
   if (!attn_stream_supported(D, H) || (q_ld & 3) || (bpre_ld & 3) || (gctx_ld & 3)) return cudaErrorInvalidValue;
   if (rows_bf16 && ((D & 7) || (H & 7))) return cudaErrorInvalidValue;      // 16-byte bulk copies of bf16 rows
   if (B <= 0 || L <= 0) return cudaSuccess;
@@ -213,26 +213,30 @@ cudaError_t attn_step_fwd_stream(cudaStream_t st, int B, int L, int D, int H, co
               B, L, D, H, rows_per_image < 1 ? 1 : rows_per_image, g.rp, g.RH, g.RD, g.NST, g.stage_floats, g.maxseg, seg_pad,
               slot_floats, env_int("ALEXCAP_ATT_DRY", 0), l2_fraction()};
   a.bf16 = rows_bf16 ? 1 : 0;
+  a.ws_exp = ws_exp ? 1 : 0;
   const size_t smem = (size_t)g.NST * g.stage_floats * 4 + fwd_fixed_smem(D, seg_pad, g.maxseg);
   const int nj = ceil_div(H, 128);
-#define LAUNCH_FWD_K(NJ, FULL, BF)                                                          \
+#define LAUNCH_FWD_K(NJ, FULL, BF, EW)                                                      \
   do {                                                                                      \
-    ACK(set_smem(attn_fwd_stream_kernel<NJ, FULL, BF>, smem));                              \
+    ACK(set_smem(attn_fwd_stream_kernel<NJ, FULL, BF, EW>, smem));                          \
     ALEXCAP_NOTE_LAUNCH();                                                                  \
-    ACK(launch_pdl(attn_fwd_stream_kernel<NJ, FULL, BF>, dim3(g.nCTA), dim3(SA_THREADS), smem, st, a));   \
+    ACK(launch_pdl(attn_fwd_stream_kernel<NJ, FULL, BF, EW>, dim3(g.nCTA), dim3(SA_THREADS), smem, st, a));   \
     return cudaGetLastError();                                                              \
   } while (0)
+#define LAUNCH_FWD_E(NJ, FULL, BF)                                                          \
+  do { if (ws_exp) LAUNCH_FWD_K(NJ, FULL, BF, true); LAUNCH_FWD_K(NJ, FULL, BF, false); } while (0)
 #define LAUNCH_FWD(NJ)                                                                      \
   do {                                                                                      \
-    if (H == 128 * NJ) { if (rows_bf16) LAUNCH_FWD_K(NJ, true, true); LAUNCH_FWD_K(NJ, true, false); }   \
-    if (rows_bf16) LAUNCH_FWD_K(NJ, false, true);                                           \
-    LAUNCH_FWD_K(NJ, false, false);                                                         \
+    if (H == 128 * NJ) { if (rows_bf16) LAUNCH_FWD_E(NJ, true, true); LAUNCH_FWD_E(NJ, true, false); }   \
+    if (rows_bf16) LAUNCH_FWD_E(NJ, false, true);                                           \
+    LAUNCH_FWD_E(NJ, false, false);                                                         \
   } while (0)
   if (nj <= 1) LAUNCH_FWD(1);
   else if (nj <= 2) LAUNCH_FWD(2);
   else if (nj <= 4) LAUNCH_FWD(4);
   else LAUNCH_FWD(8);
 #undef LAUNCH_FWD_K
+#undef LAUNCH_FWD_E
 #undef LAUNCH_FWD
 }
 
@@ -248,7 +252,7 @@ cudaError_t attn_step_bwd_stream(cudaStream_t st, int B, int L, int D, int H, co
                                  const float* ctx, const float* beta, const float* dgctx, int64_t dgctx_ld,
                                  const float* dalpha_ext, int64_t ext_ld, const float* reg_r,
                                  float* dq, int64_t dq_ld, float* dbpre, int64_t dbpre_ld, float* de, int64_t de_ld,
-                                 float* dwv_part, float* dfeat, bool rows_bf16) {
+                                 float* dwv_part, float* dfeat, bool rows_bf16, bool ws_exp) {
   if (!attn_stream_supported(D, H) || (q_ld & 3) || (dgctx_ld & 3) || (dq_ld & 3) || (dbpre_ld & 3))
     return cudaErrorInvalidValue;
   if (rows_bf16 && ((D & 7) || (H & 7))) return cudaErrorInvalidValue;
@@ -267,15 +271,19 @@ cudaError_t attn_step_bwd_stream(cudaStream_t st, int B, int L, int D, int H, co
               B, L, D, H, g.rp, g.RH, g.RD, g.NST, g.stage_floats, g.maxseg, seg_pad, rp_pad, slot_floats, l2_fraction()};
   const size_t smem = (size_t)g.NST * g.stage_floats * 4 + bwd_fixed_smem(D, H, seg_pad, rp_pad, g.maxseg);
   a.bf16 = rows_bf16 ? 1 : 0;
-#define LAUNCH_BWD(AW, BF)                                                                  \
+  a.ws_exp = ws_exp ? 1 : 0;
+#define LAUNCH_BWD_K(AW, BF, EW)                                                            \
   do {                                                                                      \
-    ACK(set_smem(attn_bwd_stream_kernel<AW, BF>, smem));                                    \
+    ACK(set_smem(attn_bwd_stream_kernel<AW, BF, EW>, smem));                                \
     ALEXCAP_NOTE_LAUNCH();                                                                  \
-    return launch_pdl(attn_bwd_stream_kernel<AW, BF>, dim3(g.nCTA), dim3(SA_THREADS), smem, st, a);   \
+    return launch_pdl(attn_bwd_stream_kernel<AW, BF, EW>, dim3(g.nCTA), dim3(SA_THREADS), smem, st, a);   \
   } while (0)
+#define LAUNCH_BWD(AW, BF)                                                                  \
+  do { if (ws_exp) LAUNCH_BWD_K(AW, BF, true); LAUNCH_BWD_K(AW, BF, false); } while (0)
   if (g.rp % L == 0) { if (rows_bf16) LAUNCH_BWD(true, true); LAUNCH_BWD(true, false); }
   if (rows_bf16) LAUNCH_BWD(false, true);
   LAUNCH_BWD(false, false);
+#undef LAUNCH_BWD_K
 #undef LAUNCH_BWD
 }
 

@@ -124,6 +124,18 @@ __device__ __forceinline__ void attn_ring_init(float* sm, int NST, int stage_flo
   pipe::mbar_fence_init();
 }
 
+// r = 1 / (1 + e^{2(w + q)}) (tanh = 1 - 2 r).  EW = false: w is the raw pre-activation, qv = C q (ex2 + rcp per element).
+// EW = true: w is EXP2C(Ws) as stored by the hoisted GEMM, qv = EXP2C(q): one FMA + ONE MUFU (common.cuh, exp2c).
+template <bool EW>
+__device__ __forceinline__ float r_of(float w, float qv) {
+  return EW ? rcp_ftz(fmaf(w, qv, 1.f)) : tanh_r(fmaf(w, TANH_C, qv));
+}
+template <bool EW>
+__device__ __forceinline__ float4 q_stage(const float4 t) {
+  return EW ? make_float4(exp2c(t.x), exp2c(t.y), exp2c(t.z), exp2c(t.w))
+            : make_float4(TANH_C * t.x, TANH_C * t.y, TANH_C * t.z, TANH_C * t.w);
+}
+
 // ------------------------------------------------------------------------------------------ forward step
 struct SAttnFwdP {
   const float* Ws; const float* feat; const float* q; int64_t q_ld; const float* bpre; int64_t bpre_ld;
@@ -135,6 +147,7 @@ struct SAttnFwdP {
   // that finalises a whole image: the A operand of the persistent time loop's gates GEMM (time_loop.cu)
   uint16_t* gctx_hi = nullptr; uint16_t* gctx_lo = nullptr; int64_t gb_ld = 0;
   int bf16 = 0;       // Ws / feat point at bf16 rows (same shapes): selects the BF instantiation
+  int ws_exp = 0;     // Ws holds EXP2C(W(features)) instead of the pre-activation: selects the EW instantiation
 };
 
 // Scratch slot of (CTA c, its j-th segment): [0]=local max, [1]=local sum, [4 .. 4+D) unnormalised partial context.
@@ -144,7 +157,7 @@ struct SAttnFwdP {
 // caller keeps them across calls; the ring's mbarriers must have been initialised by the caller (attn_ring_init).
 // Only the SA_THREADS threads of the attention roles may enter (warps 0..SA_CWARPS-1 consumers, warp SA_CWARPS producer).
 // NC: float4 column chunks per consumer thread in the context pass (D <= 4 * SA_GTHREADS * NC).
-template <int NJ, bool FULL, int NC, bool BF = false>
+template <int NJ, bool FULL, int NC, bool BF = false, bool EW = false>
 __device__ __forceinline__ void attn_fwd_body(const SAttnFwdP& a, float* sm, const int cta, Cursor& k, int& kg) {
   const int L = a.L, D = a.D, H4 = a.H >> 2, D4 = D >> 2, RH = a.RH, RD = a.RD;
   Ring ring;
@@ -211,7 +224,7 @@ __device__ __forceinline__ void attn_fwd_body(const SAttnFwdP& a, float* sm, con
       for (int j = 0; j < NJ; ++j) {
         const int f = lane + 32 * j;
         const float4 t = (FULL || f < H4) ? qs[f] : f4_zero();
-        q4[j] = make_float4(TANH_C * t.x, TANH_C * t.y, TANH_C * t.z, TANH_C * t.w);
+        q4[j] = q_stage<EW>(t);
       }
       for (int cc = tid; cc < D4; cc += SA_CTHREADS) reinterpret_cast<float4*>(bp_s)[cc] = qs[H4 + cc];
     }
@@ -235,12 +248,12 @@ __device__ __forceinline__ void attn_fwd_body(const SAttnFwdP& a, float* sm, con
           const int f = lane + 32 * j;
           if (FULL || f < H4) {
             const float4 w0 = ld_row4<BF>(st, rr * H4 + f);
-            s0 = fmaf(v4[j].x, tanh_r(fmaf(w0.x, TANH_C, q4[j].x)), s0); s0 = fmaf(v4[j].y, tanh_r(fmaf(w0.y, TANH_C, q4[j].y)), s0);
-            s0 = fmaf(v4[j].z, tanh_r(fmaf(w0.z, TANH_C, q4[j].z)), s0); s0 = fmaf(v4[j].w, tanh_r(fmaf(w0.w, TANH_C, q4[j].w)), s0);
+            s0 = fmaf(v4[j].x, r_of<EW>(w0.x, q4[j].x), s0); s0 = fmaf(v4[j].y, r_of<EW>(w0.y, q4[j].y), s0);
+            s0 = fmaf(v4[j].z, r_of<EW>(w0.z, q4[j].z), s0); s0 = fmaf(v4[j].w, r_of<EW>(w0.w, q4[j].w), s0);
             if (has2) {
               const float4 w1 = ld_row4<BF>(st, rr2 * H4 + f);
-              s1 = fmaf(v4[j].x, tanh_r(fmaf(w1.x, TANH_C, q4[j].x)), s1); s1 = fmaf(v4[j].y, tanh_r(fmaf(w1.y, TANH_C, q4[j].y)), s1);
-              s1 = fmaf(v4[j].z, tanh_r(fmaf(w1.z, TANH_C, q4[j].z)), s1); s1 = fmaf(v4[j].w, tanh_r(fmaf(w1.w, TANH_C, q4[j].w)), s1);
+              s1 = fmaf(v4[j].x, r_of<EW>(w1.x, q4[j].x), s1); s1 = fmaf(v4[j].y, r_of<EW>(w1.y, q4[j].y), s1);
+              s1 = fmaf(v4[j].z, r_of<EW>(w1.z, q4[j].z), s1); s1 = fmaf(v4[j].w, r_of<EW>(w1.w, q4[j].w), s1);
             }
           }
         }
@@ -421,11 +434,12 @@ struct SAttnBwdP {
   int B, L, D, H, rp, RH, RD, NST, stage_floats, maxseg, seg_pad, rp_pad, slot_floats;
   float l2_frac;
   int bf16 = 0;       // Ws / feat point at bf16 rows (same shapes): selects the BF instantiation
+  int ws_exp = 0;     // Ws holds EXP2C(W(features)) (see r_of): selects the EW instantiation
 };
 
 // Scratch slot: [0] = partial dot, [1] = ref_s, [4 + i*H .. ) i = 0..3 : X1, X2, Y1, Y2.
 // ALLWHOLE: every image lives in one CTA (rp % L == 0): the split-path accumulators x2 / y2 are never needed.
-template <bool ALLWHOLE, bool BF = false>
+template <bool ALLWHOLE, bool BF = false, bool EW = false>
 __device__ __forceinline__ void attn_bwd_body(const SAttnBwdP& a, float* sm, const int cta, Cursor& k, int& kg) {
   const int L = a.L, D = a.D, H = a.H, H4 = H >> 2, D4 = D >> 2, RH = a.RH, RD = a.RD;
   Ring ring;
@@ -579,14 +593,14 @@ __device__ __forceinline__ void attn_bwd_body(const SAttnBwdP& a, float* sm, con
     // with tc = tanh(Ws[b,0,h] + q_h) the sums run over (t_l - tc) and (tc^2 - t_l^2), which are SMALL whenever t varies
     // little along l -- the case in which the textbook form sum_l de_l (1 - t_l^2) cancels catastrophically in fp32.
     float4 qq = (g < G && f < H4) ? reinterpret_cast<const float4*>(q_s)[f] : f4_zero();
-    qq = make_float4(TANH_C * qq.x, TANH_C * qq.y, TANH_C * qq.z, TANH_C * qq.w);
+    qq = q_stage<EW>(qq);
     // In terms of r = 1 / (2^z + 1) (t = 1 - 2r), rc = r of the reference row, dr = r - rc:
     //   t - tc = -2 dr ;  tc^2 - t^2 = 4 dr (tc - dr)      -> 9 instructions per element, the factors applied after the loop
     float4 rc = f4_zero(), tc = f4_zero();
     if (g < G && f < H4) {
       const float4 w0 = reinterpret_cast<const float4*>(w0_s)[f];
-      rc.x = tanh_r(fmaf(w0.x, TANH_C, qq.x)); rc.y = tanh_r(fmaf(w0.y, TANH_C, qq.y));
-      rc.z = tanh_r(fmaf(w0.z, TANH_C, qq.z)); rc.w = tanh_r(fmaf(w0.w, TANH_C, qq.w));
+      rc.x = r_of<EW>(w0.x, qq.x); rc.y = r_of<EW>(w0.y, qq.y);
+      rc.z = r_of<EW>(w0.z, qq.z); rc.w = r_of<EW>(w0.w, qq.w);
       tc = make_float4(fmaf(-2.f, rc.x, 1.f), fmaf(-2.f, rc.y, 1.f), fmaf(-2.f, rc.z, 1.f), fmaf(-2.f, rc.w, 1.f));
     }
     // Packed fp32x2 arithmetic (FFMA2 / FADD2 / FMUL2): per element pair 6 packed instructions + 4 MUFU.  Accumulated per
@@ -606,12 +620,17 @@ __device__ __forceinline__ void attn_bwd_body(const SAttnBwdP& a, float* sm, con
           const float al = al_s[r0 + rr], ad = al * (da_s[r0 + rr] - ref);
           const f32x2 ad2 = pk2(ad, ad);
           const float4 w = ld_row4<BF>(st, rr * H4 + f);
-          float e0, e1, e2, e3;
-          upk2(fma2(pk2(w.x, w.y), c2, qa), e0, e1);
-          upk2(fma2(pk2(w.z, w.w), c2, qb), e2, e3);
           float d0, d1, d2, d3;
-          upk2(add2(pk2(ex2_ftz(e0), ex2_ftz(e1)), one2), d0, d1);
-          upk2(add2(pk2(ex2_ftz(e2), ex2_ftz(e3)), one2), d2, d3);
+          if (EW) {                                  // w = EXP2C(Ws), q = EXP2C(q): 1 + e^{2(w+q)} is one packed FMA
+            upk2(fma2(pk2(w.x, w.y), qa, one2), d0, d1);
+            upk2(fma2(pk2(w.z, w.w), qb, one2), d2, d3);
+          } else {
+            float e0, e1, e2, e3;
+            upk2(fma2(pk2(w.x, w.y), c2, qa), e0, e1);
+            upk2(fma2(pk2(w.z, w.w), c2, qb), e2, e3);
+            upk2(add2(pk2(ex2_ftz(e0), ex2_ftz(e1)), one2), d0, d1);
+            upk2(add2(pk2(ex2_ftz(e2), ex2_ftz(e3)), one2), d2, d3);
+          }
           const f32x2 dra = add2(pk2(rcp_ftz(d0), rcp_ftz(d1)), nra), drb = add2(pk2(rcp_ftz(d2), rcp_ftz(d3)), nrb);
           ya = fma2(ad2, dra, ya); yb = fma2(ad2, drb, yb);
           za = fma2(mul2(ad2, dra), dra, za); zb = fma2(mul2(ad2, drb), drb, zb);

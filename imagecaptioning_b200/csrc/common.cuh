@@ -90,6 +90,23 @@ __device__ __forceinline__ float block_max(float v, float* scratch) {
 
 __device__ __forceinline__ float sigmoid_f(float x) { return 1.f / (1.f + expf(-x)); }
 
+// Exponential-factored tanh (attention scores): tanh(w + q) = 1 - 2 r, r = 1 / (1 + e^{2w} e^{2q}).  EXP2C(x) = 2^(clamp(C x,
+// +-60)) with C = 2 log2(e) is what the hoisted Ws = W(features) GEMM stores (activation ACT_EXP2C) and what the per-step
+// kernels make of q, so an element costs ONE MUFU op (rcp) instead of two.  The clamp keeps the product of the two factors
+// finite and away from 0 * inf; it only changes a result when |w| or |q| exceeds 20.8 AND they nearly cancel.
+__device__ __forceinline__ float exp2c(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(fminf(fmaxf(2.8853900817779268f * x, -60.f), 60.f)));
+  return y;
+}
+// epilogue activations of the GEMM engines (enum Act in kernels.h: 1 = tanh, 2 = relu, 3 = exp2c)
+__device__ __forceinline__ float act_apply(float x, int act) {
+  if (act == 1) return tanhf(x);
+  if (act == 2) return fmaxf(x, 0.f);
+  if (act == 3) return exp2c(x);
+  return x;
+}
+
 __device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }
 
 __device__ __forceinline__ float4 f4_zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }

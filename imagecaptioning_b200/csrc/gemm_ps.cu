@@ -134,8 +134,7 @@ __device__ __forceinline__ void store_chunk(const uint32_t* v, float* tile, cons
         atomicAdd(cp, x);            // C was zeroed (or holds the value to accumulate onto) by the launcher
       } else {
         if (p.accumulate) x += *cp;
-        if (p.act == ACT_TANH) x = tanhf(x);
-        else if (p.act == ACT_RELU) x = fmaxf(x, 0.f);
+        x = act_apply(x, p.act);
         *cp = x;
       }
     }

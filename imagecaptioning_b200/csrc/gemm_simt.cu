@@ -178,8 +178,7 @@ sgemm_kernel(const GemmP p) {
           }
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            if (p.act == ACT_TANH) v[j] = tanhf(v[j]);
-            else if (p.act == ACT_RELU) v[j] = fmaxf(v[j], 0.f);
+            v[j] = act_apply(v[j], p.act);
           }
           *reinterpret_cast<float4*>(cp) = make_float4(v[0], v[1], v[2], v[3]);
         } else {
@@ -188,8 +187,7 @@ sgemm_kernel(const GemmP p) {
             if (n + j < p.N) {
               float x = v[j];
               if (p.accumulate) x += cp[j];
-              if (p.act == ACT_TANH) x = tanhf(x);
-              else if (p.act == ACT_RELU) x = fmaxf(x, 0.f);
+              x = act_apply(x, p.act);
               cp[j] = x;
             }
           }

@@ -311,8 +311,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             if (!p.dbg_noepi) atomicAdd(cp, x);      // C was zeroed (or holds the value to accumulate onto) by the launcher
           } else {
             if (p.accumulate) x += *cp;
-            if (p.act == ACT_TANH) x = tanhf(x);
-            else if (p.act == ACT_RELU) x = fmaxf(x, 0.f);
+            x = act_apply(x, p.act);
             *cp = x;
           }
         }

@@ -5,7 +5,7 @@
 
 namespace alexcap {
 
-enum Act { ACT_NONE = 0, ACT_TANH = 1, ACT_RELU = 2 };
+enum Act { ACT_NONE = 0, ACT_TANH = 1, ACT_RELU = 2, ACT_EXP2C = 3 };   // (applied by act_apply, common.cuh)
 
 // C[M,N] = act(alpha * op(A) op(B) + bias + bias2) (+ C).  See alexcap_gemm_f32 in alexcap.h.
 cudaError_t gemm_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, float alpha,
@@ -75,19 +75,20 @@ int& attn_engine();
 cudaError_t attn_step_fwd_stream(cudaStream_t st, int B, int L, int D, int H, const float* Ws, const float* feat,
                                  const float* q, int64_t q_ld, const float* bpre, int64_t bpre_ld, const float* wv,
                                  float* alpha, int64_t alpha_ld, float* ctx, float* beta, float* gctx, int64_t gctx_ld,
-                                 int rows_per_image, bool rows_bf16 = false);
+                                 int rows_per_image, bool rows_bf16 = false, bool ws_exp = false);
+// ws_exp: Ws holds EXP2C(W(features)) (GEMM activation ACT_EXP2C; common.cuh) -- one MUFU op per score element instead of two
 // rows_bf16: Ws and feat point at bf16 rows of the same shapes (ALEXCAP_BF16 storage: half the streamed bytes; D, H % 8 == 0)
 cudaError_t attn_step_bwd_stream(cudaStream_t st, int B, int L, int D, int H, const float* Ws, const float* feat,
                                  const float* q, int64_t q_ld, const float* wv, const float* alpha, int64_t alpha_ld,
                                  const float* ctx, const float* beta, const float* dgctx, int64_t dgctx_ld,
                                  const float* dalpha_ext, int64_t ext_ld, const float* reg_r,
                                  float* dq, int64_t dq_ld, float* dbpre, int64_t dbpre_ld, float* de, int64_t de_ld,
-                                 float* dwv_part, float* dfeat, bool rows_bf16 = false);
+                                 float* dwv_part, float* dfeat, bool rows_bf16 = false, bool ws_exp = false);
 // dWs[b,l,h] = wv[h] * sum_t de[b,t,l] * (1 - tanh^2(Ws[b,l,h] + q[t,b,h]));  q: [S][B] rows of stride q_ld,
 // de: [B][S][L].
 cudaError_t attn_dws(cudaStream_t st, int B, int L, int H, int S, const float* Ws, const float* q, int64_t q_ld,
                      const float* wv, const float* de, float* dWs, uint16_t* d_hi = nullptr, uint16_t* d_lo = nullptr,
-                     int64_t d_ld = 0, int max_ctas = 0);
+                     int64_t d_ld = 0, int max_ctas = 0, bool ws_exp = false);
 // d_hi / d_lo: bf16 copies [B*L, d_ld] written as well as / instead of dWs (may be NULL); max_ctas > 0 caps the grid
 // resid = 1 - sum_t alpha[b,t,l]; r[b,l] = -2*w*resid/(B*L); loss_reg = w*mean(resid^2) -> *loss_reg
 cudaError_t attn_regulariser(cudaStream_t st, int B, int S, int L, float weight, const float* alphas, float* r,

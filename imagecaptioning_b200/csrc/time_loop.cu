@@ -241,7 +241,7 @@ attn_loop_fwd_kernel(const __grid_constant__ CUtensorMap tmHh, const __grid_cons
           a.ctx = p.CTX + (int64_t)t * B * D; a.beta = p.BETA + (int64_t)t * B * D;
           a.gctx = p.XH + (int64_t)t * B * p.DH;
           a.gctx_hi = p.Gb_hi + (int64_t)t * B * D; a.gctx_lo = p.Gb_lo + (int64_t)t * B * D;
-          attn_fwd_body<NJ, FULL, 1>(a, sm, cta, ak, akg);
+          attn_fwd_body<NJ, FULL, 1, false, true>(a, sm, cta, ak, akg);      // Ws in exponential form (ACT_EXP2C)
         }
         if (p.prof) __syncthreads();
         TL_STAMP(3);
