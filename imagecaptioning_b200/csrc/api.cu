@@ -42,7 +42,7 @@ namespace {
 // ------------------------------------------------------------------------------------------ attention workspace
 struct AttnWs {
   int32_t *in_bm, *tgt_bm, *in_tm, *tgt_tm, *bad_rows;
-  float *m, *XH, *Call, *Ws, *EmbIn, *DGQ, *QB, *BETA, *CTX, *ALPHA, *DE;
+  float *m, *XH, *Call, *Ws, *EmbIn, *DGQ, *XG, *QB, *BETA, *CTX, *ALPHA, *DE;
   float *Wcat, *Wub, *bub, *Wback;
   float *MASK, *Hd;
   float *logits, *row_loss, *scal;   // scal: [0]=n_valid [1]=ce_sum [2]=reg
@@ -54,6 +54,13 @@ struct AttnWs {
   int64_t ldV;
   size_t bytes;
 };
+
+// ALEXCAP_LSTM_Q_FUSED=1: fuse the LSTM cell into the next step's query GEMM (see attn_fwd_core); read once per process,
+// because the workspace layout (XG) depends on it.
+static bool cell_fusion_enabled() {
+  static const bool on = [] { const char* v = getenv("ALEXCAP_LSTM_Q_FUSED"); return v && v[0] == '1'; }();
+  return on;
+}
 
 AttnWs attn_layout(const alexcap_dims* d, void* base, bool with_logits) {
   AttnWs w;
@@ -69,6 +76,7 @@ AttnWs attn_layout(const alexcap_dims* d, void* base, bool with_logits) {
   w.Ws = a.take<float>(B * L * H);
   w.EmbIn = a.take<float>(S * B * E);
   w.DGQ = a.take<float>(S * B * W5);
+  w.XG = cell_fusion_enabled() ? a.take<float>(S * B * 4 * H) : nullptr;   // gate PRE-activations of the fused cell + query GEMM (attn_fwd_core)
   w.QB = a.take<float>(S * B * (H + D));
   w.BETA = a.take<float>(S * B * D);
   w.CTX = a.take<float>(S * B * D);
@@ -162,11 +170,21 @@ int attn_fwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
   API_CK(gemm_f32(st, false, true, B * L, H, D, 1.f, feat, D, P->att_W_w, D, w.Ws, H, P->att_W_b, nullptr, false,
                   ws_exp ? ACT_EXP2C : ACT_NONE));
   API_CK(gather_rows(st, P->emb_w, w.in_tm, S * B, E, w.EmbIn, E));
-  API_CK(gemm_f32(st, false, true, S * B, 4 * H, E, 1.f, w.EmbIn, E, P->lstm_w_ih, E + D, w.DGQ, W5, P->lstm_b_ih,
-                  P->lstm_b_hh, false, ACT_NONE));
   // The recurrence.  Default (tcgen05 engines, shapes whose recurrent weights fit in shared memory): ONE persistent kernel
   // for all S steps (time_loop.cu).  Otherwise the per-step chain below.
   const bool loop_ok = w.loop_bf16 && gemm_engine() >= 2 && ws_exp && attn_loop_supported(B, L, D, H);   // (the loop's attention body reads EXP2C(Ws))
+  // Per-step chain, north_star (3), opt-in (ALEXCAP_LSTM_Q_FUSED=1): the LSTM cell of step t is computed by the converter
+  // warps of step t+1's query / beta GEMM (gemm_tc_lstm_f32) -- three launches per step instead of four.  The gate
+  // PRE-activations then live in XG (the hoisted embedding part + the gates GEMM), the activations the backward pass reads
+  // go to DGQ as before.  Measured at cfg2: 2.006 ms vs 1.993 ms for the separate launches -- every one of the 8 column
+  // tiles has to repeat the cell math of its 128 x 32 k-block (4.2 us of gate loads + MUFU on the GEMM's critical path)
+  // which costs what the removed kernel boundary saves -- so the default stays the four-launch chain.
+  const bool cell_fused = !loop_ok && cell_fusion_enabled() && (gemm_engine() == 2 || gemm_engine() == 3) && pdl_enabled() &&
+                          gemm_tc_lstm_supported(B, H + D, H);
+  const int64_t GL = cell_fused ? 4 * (int64_t)H : W5;                 // row pitch of the gate pre-activations
+  float* const gates_pre = cell_fused ? w.XG : w.DGQ;
+  API_CK(gemm_f32(st, false, true, S * B, 4 * H, E, 1.f, w.EmbIn, E, P->lstm_w_ih, E + D, gates_pre, GL, P->lstm_b_ih,
+                  P->lstm_b_hh, false, ACT_NONE));
   // concatenated weights: Wcat = [W_ih[:,E:] | W_hh] (4H x (D+H));  Wub = [W_U ; W_beta] ((H+D) x H)
   if (!loop_ok) {
     CopySegments cs;
@@ -191,17 +209,26 @@ int attn_fwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
       float* xh = w.XH + (int64_t)t * B * DH;
       float* qb = w.QB + (int64_t)t * B * HD;
       float* g = w.DGQ + (int64_t)t * B * W5;
+      float* gp = gates_pre + (int64_t)t * B * GL;
+      if (t == 0 || !cell_fused)     // (fused: q_t / bpre_t were produced together with the cell of step t-1)
       { WeightBScope wb; API_CK(gemm_f32(st, false, true, B, H + D, H, 1.f, xh + D, DH, w.Wub, H, qb, HD, w.bub, nullptr, true, ACT_NONE)); }
       if (rows.bf16 || ws_exp)
         API_CK(attn_step_fwd_stream(st, B, L, D, H, rows.Ws, rows.feat, qb, HD, qb + H, HD, P->att_v_w, w.ALPHA + (int64_t)t * L,
                                     (int64_t)S * L, w.CTX + (int64_t)t * B * D, w.BETA + (int64_t)t * B * D, xh, DH, 1, rows.bf16,
-                                    ws_exp));
+                                    ws_exp, true));
       else
         API_CK(attn_step_fwd(st, B, L, D, H, w.Ws, feat, qb, HD, qb + H, HD, P->att_v_w, w.ALPHA + (int64_t)t * L,
                              (int64_t)S * L, w.CTX + (int64_t)t * B * D, w.BETA + (int64_t)t * B * D, xh, DH));
-      { WeightBScope wb; API_CK(gemm_f32(st, false, true, B, 4 * H, D + H, 1.f, xh, DH, w.Wcat, DH, g, W5, nullptr, nullptr, true, ACT_NONE)); }
-      API_CK(lstm_pointwise_fwd(st, B, H, g, W5, w.Call + (int64_t)t * B * H, w.Call + (int64_t)(t + 1) * B * H,
-                                xh + (int64_t)B * DH + D, DH, nullptr, 0));
+      { WeightBScope wb; API_CK(gemm_f32(st, false, true, B, 4 * H, D + H, 1.f, xh, DH, w.Wcat, DH, gp, GL, nullptr, nullptr, true, ACT_NONE)); }
+      float* c_t = w.Call + (int64_t)t * B * H;
+      float* h_next = xh + (int64_t)B * DH + D;                              // the h columns of step t+1's [gctx | h] row
+      if (cell_fused && t + 1 < S) {
+        const LstmA la{gp, GL, c_t, c_t + (int64_t)B * H, h_next, DH, g, W5};
+        API_CK(gemm_tc_lstm_f32(st, B, H + D, H, la, w.Wub, H, qb + (int64_t)B * HD, HD, w.bub, gemm_engine() == 2 ? 1 : 2));
+      } else {
+        API_CK(lstm_pointwise_fwd(st, B, H, gp, GL, c_t, c_t + (int64_t)B * H, h_next, DH, nullptr, 0,
+                                  cell_fused ? g : nullptr, W5));
+      }
     }
   }
   if (d->dropout_p > 0.f) {                                                 // :79 dropout(h)
@@ -282,7 +309,7 @@ int attn_bwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
                                   w.CTX + (int64_t)t * B * D, w.BETA + (int64_t)t * B * D, dgc, D,
                                   dalphas ? dalphas + (int64_t)t * L : nullptr, (int64_t)S * L, reg_r,
                                   g + 4 * H, W5, g + 5 * H, W5, w.DE + (int64_t)t * L, (int64_t)S * L, w.dwv_part,
-                                  need_dfeat ? dfeat : nullptr, rows.bf16, ws_exp));
+                                  need_dfeat ? dfeat : nullptr, rows.bf16, ws_exp, true));
     else
       API_CK(attn_step_bwd(st, B, L, D, H, w.Ws, feat, qb, HD, P->att_v_w, w.ALPHA + (int64_t)t * L, (int64_t)S * L,
                            w.CTX + (int64_t)t * B * D, w.BETA + (int64_t)t * B * D, dgc, D,

@@ -64,6 +64,23 @@ const Tune& tune_override() {
   return t;
 }
 
+// debug: device buffer (>= 528 u64) receiving CTA 0's phase time stamps, address given in ALEXCAP_ATT_PROF_PTR (scripts/attn_prof.py)
+unsigned long long* prof_ptr() {
+  static unsigned long long* p = [] {
+    const char* v = getenv("ALEXCAP_ATT_PROF_PTR");
+    return v ? reinterpret_cast<unsigned long long*>(strtoull(v, nullptr, 0)) : nullptr;
+  }();
+  return p;
+}
+
+// ALEXCAP_ATT_PREFETCH=1: fetch row pieces before griddepcontrol.wait where the caller says the rows are complete.  Measured:
+// no gain on the step (cfg2 2.0537 vs 2.0554 ms, cfg3 5.9095 vs 5.8980) -- the passes are bound by the ~72 GB/s per-SM
+// ingest while 128 SMs stream at once, not by the first pieces' latency -- so it stays off.
+bool prefetch_before_wait() {
+  static const bool on = [] { const char* v = getenv("ALEXCAP_ATT_PREFETCH"); return v && v[0] == '1'; }();
+  return on;
+}
+
 int sm_count() {
   static int n = 0;
   if (!n) {
@@ -169,25 +186,35 @@ bool attn_stream_supported(int D, int H) {
 template <int NJ, bool FULL, bool BF, bool EW>
 __global__ void __launch_bounds__(SA_THREADS, 1) attn_fwd_stream_kernel(const SAttnFwdP a) {
   extern __shared__ __align__(128) float sm[];
+  if (a.prof && blockIdx.x == 0 && threadIdx.x == 0) a.prof[0] = sa_gtime();
   if (threadIdx.x == 0) attn_ring_init(sm, a.NST, a.stage_floats);
   __syncthreads();
-  pdl_trigger();
-  pdl_wait();
+  pdl_trigger();                      // (griddepcontrol.wait is executed inside the body: a.pdl)
   Cursor k{0, 0u};
   int kg = 0;
   attn_fwd_body<NJ, FULL, SA_NC, BF, EW>(a, sm, (int)blockIdx.x, k, kg);
+  if (a.prof && blockIdx.x == 0 && threadIdx.x == 0) {        // debug timeline: (entry, body entry, end) of every launch
+    const unsigned long long n = a.prof[7]++ & 63ull;
+    unsigned long long* tl = a.prof + 16 + 4 * n;
+    tl[0] = a.prof[0]; tl[1] = a.prof[1]; tl[2] = sa_gtime();
+  }
 }
 
 template <bool ALLWHOLE, bool BF, bool EW>
 __global__ void __launch_bounds__(SA_THREADS, 1) attn_bwd_stream_kernel(const SAttnBwdP a) {
   extern __shared__ __align__(128) float sm[];
+  if (a.prof && blockIdx.x == 0 && threadIdx.x == 0) a.prof[0] = sa_gtime();
   if (threadIdx.x == 0) attn_ring_init(sm, a.NST, a.stage_floats);
   __syncthreads();
-  pdl_trigger();
-  pdl_wait();
+  pdl_trigger();                      // (griddepcontrol.wait is executed inside the body: a.pdl)
   Cursor k{0, 0u};
   int kg = 0;
   attn_bwd_body<ALLWHOLE, BF, EW>(a, sm, (int)blockIdx.x, k, kg);
+  if (a.prof && blockIdx.x == 0 && threadIdx.x == 0) {
+    const unsigned long long n = a.prof[7]++ & 63ull;
+    unsigned long long* tl = a.prof + 8 + 256 + 4 * n;          // (a.prof = buffer + 8 for the backward kernel)
+    tl[0] = a.prof[0]; tl[1] = a.prof[1]; tl[2] = sa_gtime();
+  }
 }
 
 static size_t fwd_fixed_smem(int D, int seg_pad, int maxseg) {
@@ -197,7 +224,7 @@ static size_t fwd_fixed_smem(int D, int seg_pad, int maxseg) {
 cudaError_t attn_step_fwd_stream(cudaStream_t st, int B, int L, int D, int H, const float* Ws, const float* feat,
                                  const float* q, int64_t q_ld, const float* bpre, int64_t bpre_ld, const float* wv,
                                  float* alpha, int64_t alpha_ld, float* ctx, float* beta, float* gctx, int64_t gctx_ld,
-                                 int rows_per_image, bool rows_bf16, bool ws_exp) {
+                                 int rows_per_image, bool rows_bf16, bool ws_exp, bool static_ready) {
   if (!attn_stream_supported(D, H) || (q_ld & 3) || (bpre_ld & 3) || (gctx_ld & 3)) return cudaErrorInvalidValue;
   if (rows_bf16 && ((D & 7) || (H & 7))) return cudaErrorInvalidValue;      // 16-byte bulk copies of bf16 rows
   if (B <= 0 || L <= 0) return cudaSuccess;
@@ -214,6 +241,8 @@ cudaError_t attn_step_fwd_stream(cudaStream_t st, int B, int L, int D, int H, co
               slot_floats, env_int("ALEXCAP_ATT_DRY", 0), l2_fraction()};
   a.bf16 = rows_bf16 ? 1 : 0;
   a.ws_exp = ws_exp ? 1 : 0;
+  a.pdl = (static_ready && prefetch_before_wait()) ? 2 : 1;
+  a.prof = prof_ptr();
   const size_t smem = (size_t)g.NST * g.stage_floats * 4 + fwd_fixed_smem(D, seg_pad, g.maxseg);
   const int nj = ceil_div(H, 128);
 #define LAUNCH_FWD_K(NJ, FULL, BF, EW)                                                      \
@@ -252,7 +281,7 @@ cudaError_t attn_step_bwd_stream(cudaStream_t st, int B, int L, int D, int H, co
                                  const float* ctx, const float* beta, const float* dgctx, int64_t dgctx_ld,
                                  const float* dalpha_ext, int64_t ext_ld, const float* reg_r,
                                  float* dq, int64_t dq_ld, float* dbpre, int64_t dbpre_ld, float* de, int64_t de_ld,
-                                 float* dwv_part, float* dfeat, bool rows_bf16, bool ws_exp) {
+                                 float* dwv_part, float* dfeat, bool rows_bf16, bool ws_exp, bool static_ready) {
   if (!attn_stream_supported(D, H) || (q_ld & 3) || (dgctx_ld & 3) || (dq_ld & 3) || (dbpre_ld & 3))
     return cudaErrorInvalidValue;
   if (rows_bf16 && ((D & 7) || (H & 7))) return cudaErrorInvalidValue;
@@ -272,6 +301,8 @@ cudaError_t attn_step_bwd_stream(cudaStream_t st, int B, int L, int D, int H, co
   const size_t smem = (size_t)g.NST * g.stage_floats * 4 + bwd_fixed_smem(D, H, seg_pad, rp_pad, g.maxseg);
   a.bf16 = rows_bf16 ? 1 : 0;
   a.ws_exp = ws_exp ? 1 : 0;
+  a.pdl = (static_ready && prefetch_before_wait()) ? 2 : 1;
+  a.prof = prof_ptr() ? prof_ptr() + 8 : nullptr;
 #define LAUNCH_BWD_K(AW, BF, EW)                                                            \
   do {                                                                                      \
     ACK(set_smem(attn_bwd_stream_kernel<AW, BF, EW>, smem));                                \

@@ -82,8 +82,22 @@ __device__ __forceinline__ void hdr_set(Header& hd, int i, const void* p, int64_
 // Producer: for every image segment of this CTA's row range stream [header] [X0 rows] [X1 rows] (R0- / R1-row pieces).
 // esz: bytes per element of the X0 / X1 rows (4, or 2 in bf16-storage mode).
 // `k` is the producer's ring cursor: a persistent caller (time_loop.cu) keeps it across calls.
+// `defer` (stand-alone kernels launched with programmatic dependent launch, static rows known to be complete): the header is
+// the only member that depends on the preceding kernel, so its stage is reserved in ring order but its copies are ISSUED only
+// after griddepcontrol.wait -- the row pieces that fill the rest of the ring are fetched while the predecessor still runs.
 __device__ __forceinline__ void produce(const Ring& ring, Cursor& k, int64_t row0, int64_t row1, int L, int R0, int R1, int rpi,
-                                        const Header& hd, const void* X0, int n0, const void* X1, int n1, int esz) {
+                                        const Header& hd, const void* X0, int n0, const void* X1, int n1, int esz,
+                                        bool defer = false) {
+  bool pending = false;                              // the first header's copies have not been issued yet
+  Cursor kh{0, 0u};
+  int hb = 0, since = 0;
+  auto issue_header = [&](const Cursor& kc, int b) {
+    int off = 0;                                     // bytes (every member is a multiple of 16 bytes)
+    for (int i = 0; i < hd.count; ++i) {
+      pipe::bulk_g2s(reinterpret_cast<char*>(ring.stage(kc)) + off, hd.p[i] + (int64_t)b * hd.ld[i], (uint32_t)hd.n[i], &ring.full[kc.s]);
+      off += hd.n[i];
+    }
+  };
   for (int64_t lo = row0; lo < row1;) {
     const int b = (int)(lo / L);
     int64_t hi = (int64_t)(b + 1) * L;
@@ -94,11 +108,8 @@ __device__ __forceinline__ void produce(const Ring& ring, Cursor& k, int64_t row
       uint32_t bytes = 0;
       for (int i = 0; i < hd.count; ++i) bytes += (uint32_t)hd.n[i];
       ring.begin(k, bytes);
-      int off = 0;                                   // bytes (every member is a multiple of 16 bytes)
-      for (int i = 0; i < hd.count; ++i) {
-        pipe::bulk_g2s(reinterpret_cast<char*>(ring.stage(k)) + off, hd.p[i] + (int64_t)b * hd.ld[i], (uint32_t)hd.n[i], &ring.full[k.s]);
-        off += hd.n[i];
-      }
+      if (defer && lo == row0) { pending = true; kh = k; hb = b; since = 0; }
+      else issue_header(k, b);
       k.next(ring.NST);
     }
     for (int pass = 0; pass < 2; ++pass) {
@@ -106,12 +117,18 @@ __device__ __forceinline__ void produce(const Ring& ring, Cursor& k, int64_t row
       const int n = pass ? n1 : n0;
       const int R = pass ? R1 : R0;
       for (int r0 = 0; r0 < nl; r0 += R, k.next(ring.NST)) {
+        if (pending && ++since >= ring.NST) {        // the ring is full: the next stage is the header's own
+          pdl_wait();
+          issue_header(kh, hb);
+          pending = false;
+        }
         const int rows = min(R, nl - r0);
         const uint32_t bytes = (uint32_t)rows * (uint32_t)n * (uint32_t)esz;
         ring.begin(k, bytes);
         ring.copy_rows(k, reinterpret_cast<const float*>(X + (src_row + r0) * n * esz), bytes);
       }
     }
+    if (pending) { pdl_wait(); issue_header(kh, hb); pending = false; }
     lo = hi;
   }
 }
@@ -123,6 +140,14 @@ __device__ __forceinline__ void attn_ring_init(float* sm, int NST, int stage_flo
   for (int s = 0; s < NST; ++s) { pipe::mbar_init(&full[s], 1); pipe::mbar_init(&empty[s], SA_GWARPS); }
   pipe::mbar_fence_init();
 }
+
+// debug (ALEXCAP_ATT_PROF_PTR=<device address of >= 16 u64>): %globaltimer stamps of CTA 0 at the phase boundaries
+__device__ __forceinline__ unsigned long long sa_gtime() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+#define SA_STAMP(slot) do { if (a.prof && cta == 0 && threadIdx.x == 0) a.prof[slot] = sa_gtime(); } while (0)
 
 // r = 1 / (1 + e^{2(w + q)}) (tanh = 1 - 2 r).  EW = false: w is the raw pre-activation, qv = C q (ex2 + rcp per element).
 // EW = true: w is EXP2C(Ws) as stored by the hoisted GEMM, qv = EXP2C(q): one FMA + ONE MUFU (common.cuh, exp2c).
@@ -148,6 +173,9 @@ struct SAttnFwdP {
   uint16_t* gctx_hi = nullptr; uint16_t* gctx_lo = nullptr; int64_t gb_ld = 0;
   int bf16 = 0;       // Ws / feat point at bf16 rows (same shapes): selects the BF instantiation
   int ws_exp = 0;     // Ws holds EXP2C(W(features)) instead of the pre-activation: selects the EW instantiation
+  int pdl = 0;        // 0: no griddepcontrol.wait in the body (persistent caller); 1: every thread waits at body entry;
+                      // 2: as 1, but the producer prefetches Ws pieces BEFORE its wait (see produce(): `defer`)
+  unsigned long long* prof = nullptr;
 };
 
 // Scratch slot of (CTA c, its j-th segment): [0]=local max, [1]=local sum, [4 .. 4+D) unnormalised partial context.
@@ -183,12 +211,15 @@ __device__ __forceinline__ void attn_fwd_body(const SAttnFwdP& a, float* sm, con
       hdr_set(hd, 1, a.bpre, a.bpre_ld, D, 4);
       hd.count = 2;
       if (a.l2_frac > 0.f) { ring.policy = pipe::l2_policy_evict_last(a.l2_frac); ring.hinted = true; }
-      produce(ring, k, row0, row1, L, RH, RD, a.rpi, hd, a.Ws, a.H, a.feat, D, BF ? 2 : 4);
+      if (a.pdl == 1) pdl_wait();
+      produce(ring, k, row0, row1, L, RH, RD, a.rpi, hd, a.Ws, a.H, a.feat, D, BF ? 2 : 4, a.pdl == 2);
     }
     return;
   }
+  if (a.pdl) pdl_wait();
 
   // ================================================================ consumers
+  SA_STAMP(1);
   const int grp = warp / SA_GWARPS, gw = warp % SA_GWARPS, gtid = tid % SA_GTHREADS;
   // e[l] = sum_h v_h tanh(z_h) = sum_h v_h - 2 sum_h v_h r_h with r = 1/(2^(C z)+1): the constant drops out of the
   // softmax, so the score kept is  sum_h (-2 v_h) r_h  (5 instructions and 2 MUFU per element).
@@ -232,6 +263,7 @@ __device__ __forceinline__ void attn_fwd_body(const SAttnFwdP& a, float* sm, con
     if (kg == grp && lane == 0) ring.release(k);
     k.next(ring.NST); kg = (kg + 1 == SA_NG) ? 0 : kg + 1;
 
+    SA_STAMP(2);
     // ---- pass 1: e[l] = w_v . tanh(Ws[b,l,:] + q[b,:])     two rows per warp in flight   (AttentionLanguageModule.py:18-19)
     for (int r0 = 0; r0 < nl; r0 += RH, k.next(ring.NST), kg = (kg + 1 == SA_NG) ? 0 : kg + 1) {
       if (kg != grp) continue;
@@ -268,6 +300,7 @@ __device__ __forceinline__ void attn_fwd_body(const SAttnFwdP& a, float* sm, con
     }
     pipe::named_sync(1, SA_CTHREADS);
 
+    SA_STAMP(3);
     // ---- local softmax statistics                                              (:20, split over the segments)
     float mx = -INFINITY;
     for (int i = tid; i < nl; i += SA_CTHREADS) mx = fmaxf(mx, es[i]);
@@ -284,6 +317,7 @@ __device__ __forceinline__ void attn_fwd_body(const SAttnFwdP& a, float* sm, con
     for (int i = tid; i < nl; i += SA_CTHREADS) a.alpha[(int64_t)b * a.alpha_ld + l0 + i] = whole ? es[i] * inv_local : es[i];
     if (!whole && tid == 0) { slot[0] = mx; slot[1] = sum; }
 
+    SA_STAMP(4);
     // ---- pass 2: unnormalised partial context  sum_{own l} p[l] * feat[b,l,:]                           (:21)
     float4 acc[NC];
 #pragma unroll
@@ -308,6 +342,7 @@ __device__ __forceinline__ void attn_fwd_body(const SAttnFwdP& a, float* sm, con
       __syncwarp();
       if (lane == 0) ring.release(k);
     }
+    SA_STAMP(5);
     // reduce over the consumer groups and the row sub-groups inside each
 #pragma unroll
     for (int ci = 0; ci < NC; ++ci) red[ci * SA_CTHREADS + tid] = acc[ci];
@@ -343,6 +378,7 @@ __device__ __forceinline__ void attn_fwd_body(const SAttnFwdP& a, float* sm, con
       }
     }
     pipe::named_sync(1, SA_CTHREADS);             // es / red are reused by the next segment
+    SA_STAMP(6);
   }
   const int nsegs = j_seg;
 
@@ -435,6 +471,8 @@ struct SAttnBwdP {
   float l2_frac;
   int bf16 = 0;       // Ws / feat point at bf16 rows (same shapes): selects the BF instantiation
   int ws_exp = 0;     // Ws holds EXP2C(W(features)) (see r_of): selects the EW instantiation
+  int pdl = 0;        // as SAttnFwdP::pdl (2: feat pieces are prefetched before the producer's griddepcontrol.wait)
+  unsigned long long* prof = nullptr;
 };
 
 // Scratch slot: [0] = partial dot, [1] = ref_s, [4 + i*H .. ) i = 0..3 : X1, X2, Y1, Y2.
@@ -472,11 +510,14 @@ __device__ __forceinline__ void attn_bwd_body(const SAttnBwdP& a, float* sm, con
       hdr_set(hd, 4, a.Ws, (int64_t)L * H, H, BF ? 2 : 4);            // Ws[b,0,:]: the reference row of pass D
       hd.count = 5;
       if (a.l2_frac > 0.f) { ring.policy = pipe::l2_policy_evict_last(a.l2_frac); ring.hinted = true; }
-      produce(ring, k, row0, row1, L, RD, RH, 1, hd, a.feat, D, a.Ws, H, BF ? 2 : 4);     // feat pieces, then Ws pieces     // feat pieces, then Ws pieces
+      if (a.pdl == 1) pdl_wait();
+      produce(ring, k, row0, row1, L, RD, RH, 1, hd, a.feat, D, a.Ws, H, BF ? 2 : 4, a.pdl == 2);     // feat pieces, then Ws pieces
     }
     return;
   }
+  if (a.pdl) pdl_wait();
 
+  SA_STAMP(1);
   const int grp = warp / SA_GWARPS, gw = warp % SA_GWARPS, gtid = tid % SA_GTHREADS;
   const bool wide = H4 >= SA_GTHREADS;        // H4 <= 256 (H <= 1024)
   const int G = wide ? 1 : SA_GTHREADS / H4;
@@ -501,6 +542,12 @@ __device__ __forceinline__ void attn_bwd_body(const SAttnBwdP& a, float* sm, con
     const bool whole = (l0 == 0 && nl == L);      // the image lives in this CTA alone: finalise locally
     if (tid == 0) segb[j_seg] = whole ? -1 : b;
 
+    // upstream d alpha terms of this thread's rows (added after pass B): loaded now, so their latency is off the per-piece path
+    float up0 = 0.f;
+    if (tid < nl) {
+      if (a.ext) up0 += __ldg(a.ext + (int64_t)b * a.ext_ld + l0 + tid);
+      if (a.reg_r) up0 += __ldg(a.reg_r + (int64_t)b * L + l0 + tid);
+    }
     // ---- A: header piece -> q_s, dctx_s;  gate backward  gctx = beta*ctx, beta = sigmoid(bpre)   (AttentionLanguageModule.py:74-75)
     ring.wait_full(k);
     {
@@ -527,6 +574,7 @@ __device__ __forceinline__ void attn_bwd_body(const SAttnBwdP& a, float* sm, con
     if (kg == grp && lane == 0) ring.release(k);
     k.next(ring.NST); kg = (kg + 1 == SA_NG) ? 0 : kg + 1;
 
+    SA_STAMP(2);
     // ---- B: d alpha[l] = dctx . feat[b,l,:] (+ upstream terms);  dfeat += alpha[l] * dctx        (:21)
     // (Centring the dot product -- dctx . (feat_l - ctx) -- was measured: no accuracy gain, 40 % more pass-B instructions.)
     float4* dfb = a.dfeat ? reinterpret_cast<float4*>(a.dfeat) + ((int64_t)b * L + l0) * D4 : nullptr;
@@ -564,22 +612,27 @@ __device__ __forceinline__ void attn_bwd_body(const SAttnBwdP& a, float* sm, con
         { float u0, u1; pipe::upk2(p0, u0, u1); d0 = u0 + u1; pipe::upk2(p1, u0, u1); d1 = u0 + u1; }
         d0 = warp_sum(d0); d1 = warp_sum(d1);
         if (lane == 0) {
-          if (a.ext) { d0 += __ldg(a.ext + (int64_t)b * a.ext_ld + l0 + i0); if (has2) d1 += __ldg(a.ext + (int64_t)b * a.ext_ld + l0 + i1); }
-          if (a.reg_r) { d0 += __ldg(a.reg_r + (int64_t)b * L + l0 + i0); if (has2) d1 += __ldg(a.reg_r + (int64_t)b * L + l0 + i1); }
           da_s[i0] = d0;
           if (has2) da_s[i1] = d1;
-          if (!whole) {                                   // raw d alpha; the finaliser turns it into d e
-            a.de[(int64_t)b * a.de_ld + l0 + i0] = d0;
-            if (has2) a.de[(int64_t)b * a.de_ld + l0 + i1] = d1;
-          }
         }
       }
       __syncwarp();
       if (lane == 0) ring.release(k);
     }
     pipe::named_sync(1, SA_CTHREADS);
+    SA_STAMP(3);
     float part = 0.f, asum = 0.f;
-    for (int i = tid; i < nl; i += SA_CTHREADS) { part = fmaf(al_s[i], da_s[i], part); asum += al_s[i]; }
+    for (int i = tid; i < nl; i += SA_CTHREADS) {
+      float dv = da_s[i];
+      if (i == tid) dv += up0;
+      else {
+        if (a.ext) dv += __ldg(a.ext + (int64_t)b * a.ext_ld + l0 + i);
+        if (a.reg_r) dv += __ldg(a.reg_r + (int64_t)b * L + l0 + i);
+      }
+      da_s[i] = dv;                                        // (each element is owned by the one thread that reads it below)
+      if (!whole) a.de[(int64_t)b * a.de_ld + l0 + i] = dv;   // raw d alpha; the finaliser turns it into d e
+      part = fmaf(al_s[i], dv, part); asum += al_s[i];
+    }
     part = pipe::group_sum(part, scratch, SA_CWARPS, 1);
     asum = pipe::group_sum(asum, scratch, SA_CWARPS, 1);
     const float ref = whole ? part : (asum > 0.f ? part / asum : 0.f);    // whole image: ref == dot (sum alpha = 1)
@@ -587,6 +640,7 @@ __device__ __forceinline__ void attn_bwd_body(const SAttnBwdP& a, float* sm, con
     if (whole)                                            // de = alpha (dalpha - dot)                            (:20)
       for (int i = tid; i < nl; i += SA_CTHREADS) a.de[(int64_t)b * a.de_ld + i] = al_s[i] * (da_s[i] - part);
 
+    SA_STAMP(4);
     // ---- D: score backward partial sums, thread-per-column over the segment's Ws rows               (:18-19)
     float4 x1 = f4_zero(), x2 = f4_zero(), y1 = f4_zero(), y2 = f4_zero();
     // sum_l de_l = 0 over the image, so any per-(image, h) constant may be subtracted from t_l and from t_l^2:
@@ -655,6 +709,7 @@ __device__ __forceinline__ void attn_bwd_body(const SAttnBwdP& a, float* sm, con
         y2 = make_float4(-2.f * Y.x, -2.f * Y.y, -2.f * Y.z, -2.f * Y.w);
       }
     }
+    SA_STAMP(5);
     // reduce over the consumer groups and the row sub-groups inside each
     red[tid] = x1; red[SA_CTHREADS + tid] = x2; red[2 * SA_CTHREADS + tid] = y1; red[3 * SA_CTHREADS + tid] = y2;
     pipe::named_sync(1, SA_CTHREADS);
@@ -679,6 +734,7 @@ __device__ __forceinline__ void attn_bwd_body(const SAttnBwdP& a, float* sm, con
       }
     }
     pipe::named_sync(1, SA_CTHREADS);             // smem vectors are reused by the next segment
+    SA_STAMP(6);
   }
   const int nsegs = j_seg;
 

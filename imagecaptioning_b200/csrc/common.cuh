@@ -90,6 +90,20 @@ __device__ __forceinline__ float block_max(float v, float* scratch) {
 
 __device__ __forceinline__ float sigmoid_f(float x) { return 1.f / (1.f + expf(-x)); }
 
+// Two-MUFU sigmoid / tanh (ex2.approx + rcp.approx): ~2e-7 absolute error, saturating correctly (e -> inf gives rcp = 0).
+__device__ __forceinline__ float sigmoid_fast(float x) {
+  float e, r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-1.4426950408889634f * x));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(e + 1.f));
+  return r;
+}
+__device__ __forceinline__ float tanh_fast2(float x) {
+  float e, r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(2.8853900817779268f * x));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(e + 1.f));
+  return fmaf(-2.f, r, 1.f);
+}
+
 // Exponential-factored tanh (attention scores): tanh(w + q) = 1 - 2 r, r = 1 / (1 + e^{2w} e^{2q}).  EXP2C(x) = 2^(clamp(C x,
 // +-60)) with C = 2 log2(e) is what the hoisted Ws = W(features) GEMM stores (activation ACT_EXP2C) and what the per-step
 // kernels make of q, so an element costs ONE MUFU op (rcp) instead of two.  The clamp keeps the product of the two factors

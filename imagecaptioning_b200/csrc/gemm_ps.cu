@@ -51,6 +51,7 @@ struct Params {
   const float* denom;           // EPI 2 in: CE divisor (device scalar)
   uint16_t* dl_hi; uint16_t* dl_lo; int64_t dl_ld;   // EPI 2 out: d logits as bf16 hi (+ lo) copies [M, dl_ld]
   float eps; int ignore_index;
+  int vec4;                     // C rows allow 16-byte accesses (C 16-byte aligned, ldc % 4 == 0, N % 4 == 0): vector red.add
 };
 
 // ------------------------------------------------------------------------------------------------ split pass
@@ -117,6 +118,31 @@ __device__ __forceinline__ void store_chunk(const uint32_t* v, float* tile, cons
 #pragma unroll
   for (int j = 0; j < 32; ++j) tile[lane * 33 + j] = __uint_as_float(v[j]);
   __syncwarp();
+  if (atomic && p.vec4) {
+    // 16-byte vector atomics (red.global.add.v4.f32): lane = (row lane / 8 of a 4-row group, 4 columns lane % 8), 8
+    // instructions of 4 rows x 128 bytes instead of 32 scalar red.add per thread -- split-K epilogues are bound by the red
+    // issue rate.  The pitch-33 tile is read conflict-free (bank = row + 4 * column group + e).
+    const int cg = lane & 7, nv = ncol0 + 4 * cg;
+    if (nv < p.N) {                                   // (N % 4 == 0: a column group is inside or outside as a whole)
+      float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (first_split) {
+        if (p.bias) { const float4 t4 = __ldg(reinterpret_cast<const float4*>(p.bias + nv)); b4.x += t4.x; b4.y += t4.y; b4.z += t4.z; b4.w += t4.w; }
+        if (p.bias2) { const float4 t4 = __ldg(reinterpret_cast<const float4*>(p.bias2 + nv)); b4.x += t4.x; b4.y += t4.y; b4.z += t4.z; b4.w += t4.w; }
+      }
+#pragma unroll
+      for (int rr = 0; rr < 8; ++rr) {
+        const int r = rr * 4 + (lane >> 3), m = mrow0 + r;
+        if (m < p.M) {
+          const float* tr = tile + r * 33 + 4 * cg;
+          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p.C + (int64_t)m * p.ldc + nv),
+                       "f"(fmaf(p.alpha, tr[0], b4.x)), "f"(fmaf(p.alpha, tr[1], b4.y)), "f"(fmaf(p.alpha, tr[2], b4.z)),
+                       "f"(fmaf(p.alpha, tr[3], b4.w)) : "memory");
+        }
+      }
+    }
+    __syncwarp();
+    return;
+  }
   const int n = ncol0 + lane;
   if (n < p.N) {
     float bsum = 0.f;
@@ -697,6 +723,10 @@ static cudaError_t launch2(cudaStream_t st, const CUtensorMap* maps, const Param
 // epilogue bounds both kernels and the 256-row tiles only add M-quantisation waste); bf16 single-product mode only for
 // the split-K shapes (few output tiles, long K: dH, dW_o, the lstm dW GEMMs) -- on large outputs the pair kernel's loads
 // reach ~28 B/clk/SM against ~51 for the single-CTA kernel and it is slower.
+static bool ps_vec4_on() {       // ALEXCAP_PS_RED_V4=0: scalar red.add (A/B timing)
+  static const bool on = [] { const char* v = getenv("ALEXCAP_PS_RED_V4"); return !(v && v[0] == '0'); }();
+  return on;
+}
 static bool pair_wanted(int M, int N, int K, int nprod) {
   static const int mode = [] { const char* v = getenv("ALEXCAP_PS_PAIR"); return v ? (v[0] == '1' ? 1 : 0) : 2; }();
   if (mode == 0 || M < 256 || N < 256) return false;
@@ -843,6 +873,7 @@ cudaError_t gemm_ps_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, 
     Params p = {};
     p.C = C; p.bias = bias; p.bias2 = bias2; p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.alpha = alpha;
     p.accumulate = accumulate ? 1 : 0; p.act = act;
+    p.vec4 = (ps_vec4_on() && aligned16(C) && (ldc & 3) == 0 && (N & 3) == 0) ? 1 : 0;
     p.tiles_m = tiles_m; p.tiles_n = tiles_n; p.splits = splits; p.kb_per_split = kb_per; p.num_kb = num_kb;
     p.n_items = tiles * splits;
     const int grid = 2 * (p.n_items < ncl ? p.n_items : ncl);
@@ -891,6 +922,7 @@ cudaError_t gemm_ps_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, 
   Params p;
   p.C = C; p.bias = bias; p.bias2 = bias2; p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.alpha = alpha;
   p.accumulate = accumulate ? 1 : 0; p.act = act;
+  p.vec4 = (ps_vec4_on() && aligned16(C) && (ldc & 3) == 0 && (N & 3) == 0) ? 1 : 0;
   p.tiles_m = tiles_m; p.tiles_n = tiles_n; p.splits = splits; p.kb_per_split = kb_per; p.num_kb = num_kb;
   p.n_items = tiles * splits;
   const int grid = p.n_items < nsm ? p.n_items : nsm;

@@ -43,6 +43,10 @@ struct Params {
   int kb_per_split, num_kb;
   int dbg_noepi;   // debug (ALEXCAP_DBG_NOEPI=1): skip the split-K red.add stores (timing experiments only; results are wrong)
   int b_const;     // B was written long before the previous kernel (weights): its first tiles may be fetched before pdl_wait
+  int red_v4;      // accumulate with red.global.add.v4.f32 (16-byte vector atomics): a quarter of the red instructions
+  int bulk_red;    // split-K / accumulate epilogue through shared memory + cp.reduce.async.bulk (.add.f32) instead of red.add
+  unsigned long long* prof;   // debug (ALEXCAP_TC_PROF_PTR): phase time stamps of CTA (0,0,0) of the LA kernels
+  LstmA la;        // LA kernels: the A operand is the LSTM cell output computed from these (see kernels.h)
 };
 // MN-major fp32/tf32 tiles (probed on B200, scripts/debug_tc_mn.py): boxes of {32 mn, 32 k} = 32 rows of 128 bytes,
 // TMA swizzle 128B_ATOM_32B, UMMA layout SWIZZLE_128B_BASE32B: LBO = 4096 (next 32-wide mn block), SBO = 512 (next group
@@ -89,11 +93,76 @@ __device__ __forceinline__ void split_tf32(uint32_t x, uint32_t& hi, uint32_t& l
   lo = (__float_as_uint(r) + 0x1000u) & 0xffffe000u;
 }
 
+// A tile of the fused LSTM -> GEMM kernels: thread t owns (row r = t / 4, 8 hidden units pch = t % 4) of the 128 x 32
+// k-block at (m0, k0); `ld` phase = global loads into registers, `st` phase = cell math, optional global stores (the CTAs of
+// the first column tile), bf16 hi (+ lo) chunks in the converter's k-chunk-major layout.
+struct CellRegs { float4 v[10]; };     // i, f, g, o, c_prev: two float4 each
+__device__ __forceinline__ void lstm_a_load(const Params& p, int m0, int k0, int t, CellRegs& x) {
+  const int r = t >> 2, pch = t & 3, m = m0 + r, u = k0 + pch * 8;      // 4 lanes cover one 128-byte row segment
+  const int H = p.K;
+  if (m < p.M && u < H) {
+    const float* g = p.la.g + (int64_t)m * p.la.g_ld + u;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      x.v[2 * q] = *reinterpret_cast<const float4*>(g + (int64_t)q * H);
+      x.v[2 * q + 1] = *reinterpret_cast<const float4*>(g + (int64_t)q * H + 4);
+    }
+    const float* c = p.la.c_prev + (int64_t)m * H + u;
+    x.v[8] = *reinterpret_cast<const float4*>(c);
+    x.v[9] = *reinterpret_cast<const float4*>(c + 4);
+  }
+}
+template <bool WITH_LO>
+__device__ __forceinline__ void lstm_a_store(const Params& p, int m0, int k0, int t, CellRegs& x, uint8_t* dst, uint8_t* dst_lo,
+                                             bool writer) {
+  const int r = t >> 2, pch = t & 3, m = m0 + r, u = k0 + pch * 8;      // 4 lanes cover one 128-byte row segment
+  const int H = p.K;
+  float h[8];
+  if (m < p.M && u < H) {
+    float* gi = &x.v[0].x; float* gf = &x.v[2].x; float* gg = &x.v[4].x; float* go = &x.v[6].x; float* cp = &x.v[8].x;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {          // the cell of lstm_fwd_kernel (lstm_pointwise.cu) with two-MUFU sigmoid / tanh: this
+      // CTA's 4096 cells sit on the critical path of the GEMM (libm tanhf / expf / division: 8 us; these: ~2 us)
+      gi[j] = sigmoid_fast(gi[j]); gf[j] = sigmoid_fast(gf[j]); gg[j] = tanh_fast2(gg[j]); go[j] = sigmoid_fast(go[j]);
+      cp[j] = fmaf(gf[j], cp[j], gi[j] * gg[j]);
+      h[j] = go[j] * tanh_fast2(cp[j]);
+    }
+    if (writer) {
+      float* a = p.la.acts + (int64_t)m * p.la.acts_ld + u;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        *reinterpret_cast<float4*>(a + (int64_t)q * H) = x.v[2 * q];
+        *reinterpret_cast<float4*>(a + (int64_t)q * H + 4) = x.v[2 * q + 1];
+      }
+      float* c = p.la.c_out + (int64_t)m * H + u;
+      *reinterpret_cast<float4*>(c) = x.v[8];
+      *reinterpret_cast<float4*>(c + 4) = x.v[9];
+      float* ho = p.la.h_out + (int64_t)m * p.la.h_ld + u;
+      *reinterpret_cast<float4*>(ho) = make_float4(h[0], h[1], h[2], h[3]);
+      *reinterpret_cast<float4*>(ho + 4) = make_float4(h[4], h[5], h[6], h[7]);
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) h[j] = 0.f;
+  }
+  uint4 o;
+  o.x = pack_bf16(h[0], h[1]); o.y = pack_bf16(h[2], h[3]); o.z = pack_bf16(h[4], h[5]); o.w = pack_bf16(h[6], h[7]);
+  if (WITH_LO) {
+    uint4 l;
+#define LO_PAIR(W, A, B) l.W = pack_bf16(A - __uint_as_float(o.W << 16), B - __uint_as_float(o.W & 0xffff0000u))
+    LO_PAIR(x, h[0], h[1]); LO_PAIR(y, h[2], h[3]); LO_PAIR(z, h[4], h[5]); LO_PAIR(w, h[6], h[7]);
+#undef LO_PAIR
+    *reinterpret_cast<uint4*>(dst_lo + pch * (BM * 16) + r * 16) = l;
+  }
+  *reinterpret_cast<uint4*>(dst + pch * (BM * 16) + r * 16) = o;
+}
+
 // ------------------------------------------------------------------------------------------------ kernel
 // MODE 0: 3xTF32 (fp32-grade accuracy).  MODE 1: bf16 operands, fp32 accumulate (the mixed-precision configs): the
 // converter warps round the fp32 tile to bf16 and re-lay it out K-major / no-swizzle (core matrices of 8 rows x 16 bytes)
 // in the slot the 3xTF32 path uses for the `lo` tile; one kind::f16 MMA per 16 k replaces three kind::tf32 per 8 k.
-template <int BN, bool A_MN, bool B_MN, int STAGES, int MODE>
+// LA (MODE >= 1, K-major A): no A tiles are loaded; the converter warps compute them (lstm_a_load / lstm_a_store).
+template <int BN, bool A_MN, bool B_MN, int STAGES, int MODE, bool LA = false>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const Params p) {
   constexpr uint32_t A_BYTES = BM * BK * 4, B_BYTES = BN * BK * 4;
@@ -109,6 +178,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+#define TC_STAMP(slot)                                                                                              \
+  do {                                                                                                              \
+    if (LA && p.prof && threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) {                \
+      unsigned long long t_;                                                                                        \
+      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_));                                                         \
+      p.prof[slot] = t_;                                                                                            \
+    }                                                                                                               \
+  } while (0)
+  TC_STAMP(0);
   const int kb0 = blockIdx.z * p.kb_per_split;
   const int kb1 = min(p.num_kb, kb0 + p.kb_per_split);
   const int nkb = kb1 - kb0;     // >= 1 by construction
@@ -141,7 +219,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if (npre > 0 && warp == TMA_WARP && lane == 0) {
     for (int i = 0; i < npre; ++i) {
       uint8_t* sb = smem + i * STAGE_BYTES + 2 * A_BYTES;
-      mbar_expect_tx(&full_bar[i], A_BYTES + B_BYTES);
+      mbar_expect_tx(&full_bar[i], (LA ? 0u : A_BYTES) + B_BYTES);
       const int k0 = (kb0 + i) * BK;
       if (B_MN) {
 #pragma unroll
@@ -152,6 +230,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
   }
   pdl_wait();         // everything above overlapped the previous kernel's tail; its results are visible from here on
+  TC_STAMP(1);
 
   if (warp == TMA_WARP) {
     // ================================================================ TMA producer
@@ -162,11 +241,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const bool pre = i < npre;                       // B tile already in flight, barrier already armed
         if (!pre) {
           mbar_wait(&empty_bar[s], ph ^ 1);
-          mbar_expect_tx(&full_bar[s], A_BYTES + B_BYTES);
+          mbar_expect_tx(&full_bar[s], (LA ? 0u : A_BYTES) + B_BYTES);
         }
         uint8_t* st = smem + s * STAGE_BYTES;
         const int k0 = (kb0 + i) * BK;
-        if (A_MN) {
+        if (LA) {
+        } else if (A_MN) {
 #pragma unroll
           for (int j = 0; j < BM / 32; ++j) tma_load_2d(st + j * 4096, &tmA, m0 + 32 * j, k0, &full_bar[s]);
         } else {
@@ -239,11 +319,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     for (int i = 0; i < nkb; ++i) {
       const int s = i % STAGES;
       const uint32_t ph = (i / STAGES) & 1;
+      CellRegs cell;
+      if (LA) lstm_a_load(p, m0, (kb0 + i) * BK, t, cell);      // (in flight while the weight tile lands)
       mbar_wait(&full_bar[s], ph);
+      TC_STAMP(2);
       uint8_t* st = smem + s * STAGE_BYTES;
       if (MODE >= 1) {
         // bf16 tiles live in the `lo` slot: hi in its first half, (MODE 2) the bf16 residual in its second half
-        convert_bf16<BM, A_MN, MODE == 2>(st, st + A_BYTES, st + A_BYTES + A_BYTES / 2, t);
+        if (LA) lstm_a_store<MODE == 2>(p, m0, (kb0 + i) * BK, t, cell, st + A_BYTES, st + A_BYTES + A_BYTES / 2, blockIdx.x == 0);
+        else convert_bf16<BM, A_MN, MODE == 2>(st, st + A_BYTES, st + A_BYTES + A_BYTES / 2, t);
         convert_bf16<BN, B_MN, MODE == 2>(st + 2 * A_BYTES, st + 2 * A_BYTES + B_BYTES, st + 2 * A_BYTES + B_BYTES + B_BYTES / 2, t);
       } else {
       // elementwise, so it is oblivious to the swizzle: same byte offset in the hi and lo tiles
@@ -267,17 +351,71 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
       fence_proxy_async();            // generic-proxy writes -> visible to the tensor core (async proxy)
       mbar_arrive(&conv_bar[s]);
+      TC_STAMP(3);
     }
 
     // ---- epilogue: TMEM -> registers -> smem transpose -> coalesced global
     mbar_wait(tmem_full_bar, 0);
+    TC_STAMP(4);
     tcgen05_fence_after();
     float* tile = reinterpret_cast<float*>(smem) + warp * (32 * 33);   // stage memory is idle now (all MMAs retired)
     const bool first_split = (blockIdx.z == 0);
     // accumulate without an activation: red.add instead of load->add->store (see gemm_ps.cu: serialised dependent loads)
     const bool atomic = gridDim.z > 1 || (p.accumulate && p.act == ACT_NONE && (int64_t)p.M * p.N <= (int64_t)(4 << 20));
-#pragma unroll 1
     const int q4 = warp & 3;                       // TMEM lane quarter this warp may read (warp id mod 4)
+    if (atomic && p.bulk_red) {
+      // Accumulating epilogue without per-element atomics: the CTA's [128 x BN] tile is parked in shared memory (row pitch
+      // BN + 4 floats: 16-byte stores of 32 different rows spread over all banks) and every row leaves as ONE bulk
+      // reduction (cp.reduce.async.bulk ... .add.f32, performed by the TMA unit at L2): 128 instructions per CTA instead of
+      // 128 x BN / 32 warp-wide red.add, whose issue rate is what bounded the epilogue (3.4 us for a 128 x 128 tile).
+      constexpr int PITCH = BN + 4;
+      float* ctile = reinterpret_cast<float*>(smem);
+      for (int cc = (warp >> 2); cc < BN / 32; cc += CONV_WARPS / 4) {
+        uint32_t v[32];
+        const uint32_t taddr = tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(cc * 32);
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+            "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+            "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+            : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+              "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+              "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+              "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+            : "r"(taddr));
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        float* row = ctile + (q4 * 32 + lane) * PITCH + cc * 32;
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          float4 o;
+          float* po = &o.x;
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int n = n0 + cc * 32 + j + e;
+            float bsum = 0.f;
+            if (first_split && n < p.N) {
+              if (p.bias) bsum += __ldg(p.bias + n);
+              if (p.bias2) bsum += __ldg(p.bias2 + n);
+            }
+            po[e] = fmaf(p.alpha, __uint_as_float(v[j + e]), bsum);
+          }
+          *reinterpret_cast<float4*>(row + j) = o;
+        }
+      }
+      tcgen05_fence_before();
+      fence_proxy_async();                                    // generic-proxy smem writes -> the bulk copies' async-proxy reads
+      asm volatile("bar.sync 1, %0;" ::"n"(CONV_THREADS) : "memory");
+      if (t < BM) {
+        const int m = m0 + t;
+        const int ncols = min(BN, p.N - n0);
+        if (m < p.M && ncols > 0 && !p.dbg_noepi) {
+          asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;"
+                       ::"l"(p.C + (int64_t)m * p.ldc + n0), "r"(smem_u32(ctile + t * PITCH)), "r"((uint32_t)ncols * 4u) : "memory");
+        }
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+      }
+    } else
+#pragma unroll 1
     for (int cc = (warp >> 2); cc < BN / 32; cc += CONV_WARPS / 4) {
       uint32_t v[32];
       const uint32_t taddr = tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(cc * 32);
@@ -291,6 +429,37 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
           : "r"(taddr));
       asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+      if (atomic && p.red_v4) {
+        // 16-byte vector atomics: the warp's 32 x 32 chunk goes through a pitch-36 tile (16-byte stores and loads both
+        // conflict-free) and leaves as 8 instructions of 4 rows x 128 bytes instead of 32 scalar red.add per thread --
+        // the epilogue of these latency-bound GEMMs is bound by the red ISSUE rate (~14 clk per warp-wide red).
+        float* t36 = reinterpret_cast<float*>(smem) + warp * (32 * 36);
+#pragma unroll
+        for (int j = 0; j < 32; j += 4)
+          *reinterpret_cast<float4*>(t36 + lane * 36 + j) =
+              make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
+        __syncwarp();
+        const int cg = lane & 7, nv = n0 + cc * 32 + 4 * cg;
+        float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (first_split && nv < p.N) {             // (N % 4 == 0: a column group is inside or outside as a whole)
+          if (p.bias) { const float4 t4 = __ldg(reinterpret_cast<const float4*>(p.bias + nv)); b4.x += t4.x; b4.y += t4.y; b4.z += t4.z; b4.w += t4.w; }
+          if (p.bias2) { const float4 t4 = __ldg(reinterpret_cast<const float4*>(p.bias2 + nv)); b4.x += t4.x; b4.y += t4.y; b4.z += t4.z; b4.w += t4.w; }
+        }
+        if (nv < p.N) {
+#pragma unroll
+          for (int rr = 0; rr < 8; ++rr) {
+            const int r = rr * 4 + (lane >> 3), m = m0 + q4 * 32 + r;
+            if (m < p.M && !p.dbg_noepi) {
+              const float4 x = *reinterpret_cast<const float4*>(t36 + r * 36 + 4 * cg);
+              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p.C + (int64_t)m * p.ldc + nv),
+                           "f"(fmaf(p.alpha, x.x, b4.x)), "f"(fmaf(p.alpha, x.y, b4.y)), "f"(fmaf(p.alpha, x.z, b4.z)),
+                           "f"(fmaf(p.alpha, x.w, b4.w)) : "memory");
+            }
+          }
+        }
+        __syncwarp();
+        continue;
+      }
 #pragma unroll
       for (int j = 0; j < 32; ++j) tile[lane * 33 + j] = __uint_as_float(v[j]);   // thread = row, j = column
       __syncwarp();
@@ -319,6 +488,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       __syncwarp();
     }
     tcgen05_fence_before();
+    TC_STAMP(5);
   }
 
   __syncthreads();
@@ -346,12 +516,20 @@ static bool make_map(CUtensorMap* map, const float* base, int64_t inner, int64_t
   return r == CUDA_SUCCESS;
 }
 
-template <int BN, bool A_MN, bool B_MN, int MODE>
+// the bulk-reduction epilogue (ALEXCAP_TC_BULK_RED=1) needs 16-byte aligned row segments.  OFF by default: measured slower
+// than red.add on the cfg2 step (2.106 vs 2.078 ms) -- the CTA has to wait for its bulk group before it may exit, which puts
+// the L2 round trip that fire-and-forget red.add hides back on the kernel's critical path.
+static bool bulk_red_ok(const float* C, int64_t ldc, int N) {
+  static const bool on = [] { const char* v = getenv("ALEXCAP_TC_BULK_RED"); return v && v[0] == '1'; }();
+  return on && aligned16(C) && (ldc & 3) == 0 && (N & 3) == 0;
+}
+
+template <int BN, bool A_MN, bool B_MN, int MODE, bool LA = false>
 static cudaError_t launch(cudaStream_t st, const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, dim3 grid) {
   constexpr int STAGES = (BN == 128) ? 3 : 4;
   constexpr size_t SMEM = (size_t)STAGES * (2 * BM * BK * 4 + 2 * BN * BK * 4) + 1024 /*align*/ + 256 /*barriers*/;
   static bool configured = false;
-  auto kern = gemm_tc_kernel<BN, A_MN, B_MN, STAGES, MODE>;
+  auto kern = gemm_tc_kernel<BN, A_MN, B_MN, STAGES, MODE, LA>;
   if (!configured) {
     ACK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
     configured = true;
@@ -415,6 +593,10 @@ cudaError_t gemm_tc_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, 
   p.C = C; p.bias = bias; p.bias2 = bias2; p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.alpha = alpha;
   p.accumulate = accumulate ? 1 : 0; p.act = act; p.kb_per_split = kb_per; p.num_kb = num_kb;
   p.b_const = (gemm_b_is_weight() && pdl_enabled()) ? 1 : 0;
+  p.prof = nullptr;
+  p.bulk_red = bulk_red_ok(C, ldc, N) ? 1 : 0;
+  { static const int v4 = [] { const char* v = getenv("ALEXCAP_TC_RED_V4"); return (v && v[0] == '0') ? 0 : 1; }();
+    p.red_v4 = (v4 && aligned16(C) && (ldc & 3) == 0 && (N & 3) == 0) ? 1 : 0; }
   { static const int noepi = [] { const char* v = getenv("ALEXCAP_DBG_NOEPI"); return (v && v[0] == '1') ? 1 : 0; }(); p.dbg_noepi = noepi; }
   dim3 grid(ceil_div(N, BN), ceil_div(M, BM), splits);
 #define TC_DISPATCH(BN_, MODE_)                                                                 \
@@ -435,6 +617,60 @@ cudaError_t gemm_tc_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, 
   if (BN == 128) TC_DISPATCH(128, 0);
   TC_DISPATCH(64, 0);
 #undef TC_DISPATCH
+}
+
+// Fused LSTM cell -> GEMM (kernels.h: LstmA).  128-column tiles, split-K down to ONE k-block (32 hidden units) per CTA when the
+// output grid is small: every column tile repeats the cell math of its k-blocks, so the fusion is only taken when that
+// repetition is spread thin (<= 2 k-blocks per CTA).
+bool gemm_tc_lstm_supported(int M, int N, int H) {
+  using namespace tc;
+  if (M <= 0 || N <= 0 || H <= 0 || (H & 7) || get_encode() == nullptr) return false;
+  const int num_kb = ceil_div(H, BK);
+  const int tiles = ceil_div(M, BM) * ceil_div(N, 128);
+  int splits = 148 / tiles;
+  if (splits > num_kb) splits = num_kb;
+  if (splits < 1) splits = 1;
+  return ceil_div(num_kb, splits) <= 2;
+}
+
+cudaError_t gemm_tc_lstm_f32(cudaStream_t st, int M, int N, int H, const LstmA& la, const float* B, int64_t ldb, float* C,
+                             int64_t ldc, const float* bias, int mode) {
+  using namespace tc;
+  if (M <= 0 || N <= 0 || H <= 0) return cudaSuccess;
+  if ((H & 7) || (ldb & 3) || (la.g_ld & 3) || (la.h_ld & 3) || (la.acts_ld & 3) || !aligned16(B) || !aligned16(la.g) ||
+      !aligned16(la.c_prev) || !aligned16(la.c_out) || !aligned16(la.h_out) || !aligned16(la.acts) || get_encode() == nullptr ||
+      (mode != 1 && mode != 2))
+    return cudaErrorNotSupported;
+  constexpr int BN = 128;
+  const int num_kb = ceil_div(H, BK);
+  const int tiles = ceil_div(M, BM) * ceil_div(N, BN);
+  int splits = 148 / tiles;
+  if (splits > num_kb) splits = num_kb;
+  if (splits < 1) splits = 1;
+  int kb_per = ceil_div(num_kb, splits);
+  if (kb_per > 2) return cudaErrorNotSupported;
+  splits = ceil_div(num_kb, kb_per);
+  CUtensorMap mapB;
+  if (!make_map(&mapB, B, H, N, ldb, BN, false)) return cudaErrorInvalidValue;
+  Params p;
+  p.C = C; p.bias = bias; p.bias2 = nullptr; p.M = M; p.N = N; p.K = H; p.ldc = ldc; p.alpha = 1.f;
+  p.accumulate = 1; p.act = ACT_NONE; p.kb_per_split = kb_per; p.num_kb = num_kb;
+  p.b_const = pdl_enabled() ? 1 : 0;
+  p.dbg_noepi = 0;
+  p.la = la;
+  p.bulk_red = bulk_red_ok(C, ldc, N) ? 1 : 0;
+  { static const int v4 = [] { const char* v = getenv("ALEXCAP_TC_RED_V4"); return (v && v[0] == '0') ? 0 : 1; }();
+    p.red_v4 = (v4 && aligned16(C) && (ldc & 3) == 0 && (N & 3) == 0) ? 1 : 0; }
+  {
+    static unsigned long long* prof = [] {
+      const char* v = getenv("ALEXCAP_TC_PROF_PTR");
+      return v ? reinterpret_cast<unsigned long long*>(strtoull(v, nullptr, 0)) : nullptr;
+    }();
+    p.prof = prof;
+  }
+  dim3 grid(ceil_div(N, BN), ceil_div(M, BM), splits);
+  if (mode == 2) return launch<BN, false, false, 2, true>(st, mapB, mapB, p, grid);
+  return launch<BN, false, false, 1, true>(st, mapB, mapB, p, grid);
 }
 
 }  // namespace alexcap

@@ -19,6 +19,18 @@ cudaError_t gemm_simt_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K
 cudaError_t gemm_tc_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, float alpha,
                         const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
                         const float* bias, const float* bias2, bool accumulate, int act, int force_splits, int mode = 0);
+// Fused LSTM cell -> next GEMM (gemm_tc.cu, north_star 3): C[M,N] += cell(g, c_prev) B^T where the A operand h = o * tanh(c)
+// is computed by the kernel's converter warps from the gate pre-activations instead of being loaded: the LSTM pointwise pass
+// and the GEMM that consumes its h (the next step's attention query / beta projection) are ONE launch.
+//   g [M, 4H] (row stride g_ld): gate pre-activations i|f|g|o (read only);  c_prev [M, H]
+//   written by the CTAs of the first column tile: acts [M, 4H] (row stride acts_ld: the gate ACTIVATIONS the backward pass
+//   reads -- a different buffer than g, other CTAs still read g), c_out [M, H], h_out [M, H] (row stride h_ld)
+struct LstmA { const float* g; int64_t g_ld; const float* c_prev; float* c_out; float* h_out; int64_t h_ld; float* acts; int64_t acts_ld; };
+// K = H (H % 8 == 0), B = weights [N, H] row-major (ldb), C pre-initialised (accumulated with red.add), bias added once.
+// Returns cudaErrorNotSupported when the shape would make too many CTAs repeat the cell math (caller: separate launches).
+bool gemm_tc_lstm_supported(int M, int N, int H);
+cudaError_t gemm_tc_lstm_f32(cudaStream_t st, int M, int N, int H, const LstmA& la, const float* B, int64_t ldb, float* C,
+                             int64_t ldc, const float* bias, int mode);
 // Pre-split engine (gemm_ps.cu): operands split once in HBM into bf16 hi (+ lo) copies that live in a bump arena (cached
 // per source pointer until released), then a persistent TMA -> tcgen05 kernel.  nprod: 1 = bf16, 3 = bf16x3.
 // Returns cudaErrorMemoryAllocation when the arena cannot hold the copies (the caller falls back to gemm_tc_f32).
@@ -75,7 +87,9 @@ int& attn_engine();
 cudaError_t attn_step_fwd_stream(cudaStream_t st, int B, int L, int D, int H, const float* Ws, const float* feat,
                                  const float* q, int64_t q_ld, const float* bpre, int64_t bpre_ld, const float* wv,
                                  float* alpha, int64_t alpha_ld, float* ctx, float* beta, float* gctx, int64_t gctx_ld,
-                                 int rows_per_image, bool rows_bf16 = false, bool ws_exp = false);
+                                 int rows_per_image, bool rows_bf16 = false, bool ws_exp = false, bool static_ready = false);
+// static_ready: Ws / feat were complete before the kernel that precedes this launch in the stream started (true inside the
+// time loops): the producer may fetch row pieces before griddepcontrol.wait; only q / bpre (dgctx) wait for the predecessor
 // ws_exp: Ws holds EXP2C(W(features)) (GEMM activation ACT_EXP2C; common.cuh) -- one MUFU op per score element instead of two
 // rows_bf16: Ws and feat point at bf16 rows of the same shapes (ALEXCAP_BF16 storage: half the streamed bytes; D, H % 8 == 0)
 cudaError_t attn_step_bwd_stream(cudaStream_t st, int B, int L, int D, int H, const float* Ws, const float* feat,
@@ -83,7 +97,7 @@ cudaError_t attn_step_bwd_stream(cudaStream_t st, int B, int L, int D, int H, co
                                  const float* ctx, const float* beta, const float* dgctx, int64_t dgctx_ld,
                                  const float* dalpha_ext, int64_t ext_ld, const float* reg_r,
                                  float* dq, int64_t dq_ld, float* dbpre, int64_t dbpre_ld, float* de, int64_t de_ld,
-                                 float* dwv_part, float* dfeat, bool rows_bf16 = false, bool ws_exp = false);
+                                 float* dwv_part, float* dfeat, bool rows_bf16 = false, bool ws_exp = false, bool static_ready = false);
 // dWs[b,l,h] = wv[h] * sum_t de[b,t,l] * (1 - tanh^2(Ws[b,l,h] + q[t,b,h]));  q: [S][B] rows of stride q_ld,
 // de: [B][S][L].
 cudaError_t attn_dws(cudaStream_t st, int B, int L, int H, int S, const float* Ws, const float* q, int64_t q_ld,
@@ -111,7 +125,8 @@ int time_loop_profile_read(unsigned long long* host_out, int max_entries);
 // gates [B,4H] (row stride g_ld) pre-activations -> activations in place; c_prev [B,H] -> c_out [B,H];
 // h written to h_out (row stride h_ld) and optionally h_out2 (row stride h2_ld).
 cudaError_t lstm_pointwise_fwd(cudaStream_t st, int B, int H, float* gates, int64_t g_ld, const float* c_prev,
-                               float* c_out, float* h_out, int64_t h_ld, float* h_out2, int64_t h2_ld);
+                               float* c_out, float* h_out, int64_t h_ld, float* h_out2, int64_t h2_ld, float* acts_out = nullptr,
+                               int64_t acts_ld = 0);   // acts_out: write the gate activations there instead of over `gates`
 // gates hold activations (i,f,g,o) -> overwritten with d(pre-activations).  dh = dh_a + dh_b (either may be NULL;
 // dh_a scaled by mask_a if given).  dc_io [B,H]: in = dc from step t+1, out = dc for step t-1.
 cudaError_t lstm_pointwise_bwd(cudaStream_t st, int B, int H, float* gates, int64_t g_ld, const float* c_t,

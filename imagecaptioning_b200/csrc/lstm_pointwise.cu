@@ -1,6 +1,8 @@
 // lstm_pointwise.cu -- LSTM cell pointwise math, forward and backward (gate order i,f,g,o as torch.nn.LSTMCell /
 // nn.LSTM: AlexCap/AttentionLanguageModule.py:58,78 ; AlexCap/LanguageModule.py:46,104-105).
-// The gate pre-activations come from the GEMMs; these kernels are elementwise and negligible in bytes.
+// The gate pre-activations come from the GEMMs; these kernels are elementwise and negligible in bytes -- but they sit on the
+// serial chain of every time step, so sigmoid / tanh are the two-MUFU forms of common.cuh (~2e-7 absolute error) rather than
+// libm's expf / tanhf / IEEE division (4 cells per thread of those are ~450 dependent instructions).
 #include "common.cuh"
 #include "kernels.h"
 
@@ -9,7 +11,8 @@ namespace alexcap {
 __global__ void __launch_bounds__(256) lstm_fwd_kernel(int B, int H, float* __restrict__ gates, int64_t g_ld,
                                                        const float* __restrict__ c_prev, float* __restrict__ c_out,
                                                        float* __restrict__ h_out, int64_t h_ld,
-                                                       float* __restrict__ h_out2, int64_t h2_ld) {
+                                                       float* __restrict__ h_out2, int64_t h2_ld,
+                                                       float* __restrict__ acts_out, int64_t acts_ld) {
   const int H4 = H >> 2;
   const int64_t n = (int64_t)B * H4;
   pdl_trigger();
@@ -21,11 +24,12 @@ __global__ void __launch_bounds__(256) lstm_fwd_kernel(int B, int H, float* __re
     const float4 cp = reinterpret_cast<const float4*>(c_prev + (int64_t)b * H)[c];
     float4 cn, hn;
 #define CELL(x)                                                        \
-    gi.x = sigmoid_f(gi.x); gf.x = sigmoid_f(gf.x); gg.x = tanhf(gg.x); go.x = sigmoid_f(go.x); \
-    cn.x = fmaf(gf.x, cp.x, gi.x * gg.x); hn.x = go.x * tanhf(cn.x);
+    gi.x = sigmoid_fast(gi.x); gf.x = sigmoid_fast(gf.x); gg.x = tanh_fast2(gg.x); go.x = sigmoid_fast(go.x); \
+    cn.x = fmaf(gf.x, cp.x, gi.x * gg.x); hn.x = go.x * tanh_fast2(cn.x);
     CELL(x) CELL(y) CELL(z) CELL(w)
 #undef CELL
-    g[c] = gi; g[H4 + c] = gf; g[2 * H4 + c] = gg; g[3 * H4 + c] = go;
+    float4* ga = acts_out ? reinterpret_cast<float4*>(acts_out + (int64_t)b * acts_ld) : g;   // (default: activations in place)
+    ga[c] = gi; ga[H4 + c] = gf; ga[2 * H4 + c] = gg; ga[3 * H4 + c] = go;
     reinterpret_cast<float4*>(c_out + (int64_t)b * H)[c] = cn;
     reinterpret_cast<float4*>(h_out + (int64_t)b * h_ld)[c] = hn;
     if (h_out2) reinterpret_cast<float4*>(h_out2 + (int64_t)b * h2_ld)[c] = hn;
@@ -33,12 +37,14 @@ __global__ void __launch_bounds__(256) lstm_fwd_kernel(int B, int H, float* __re
 }
 
 cudaError_t lstm_pointwise_fwd(cudaStream_t st, int B, int H, float* gates, int64_t g_ld, const float* c_prev,
-                               float* c_out, float* h_out, int64_t h_ld, float* h_out2, int64_t h2_ld) {
-  if ((H & 3) || (g_ld & 3) || (h_ld & 3) || (h_out2 && (h2_ld & 3))) return cudaErrorInvalidValue;
+                               float* c_out, float* h_out, int64_t h_ld, float* h_out2, int64_t h2_ld, float* acts_out,
+                               int64_t acts_ld) {
+  if ((H & 3) || (g_ld & 3) || (h_ld & 3) || (h_out2 && (h2_ld & 3)) || (acts_out && (acts_ld & 3))) return cudaErrorInvalidValue;
   const int64_t n = (int64_t)B * (H / 4);
   const int blocks = (int)((n + 255) / 256);
   ALEXCAP_NOTE_LAUNCH();
-  return launch_pdl(lstm_fwd_kernel, dim3(blocks), dim3(256), 0, st, B, H, gates, g_ld, c_prev, c_out, h_out, h_ld, h_out2, h2_ld);
+  return launch_pdl(lstm_fwd_kernel, dim3(blocks), dim3(256), 0, st, B, H, gates, g_ld, c_prev, c_out, h_out, h_ld, h_out2, h2_ld,
+                    acts_out, acts_ld);
 }
 
 __global__ void __launch_bounds__(256) lstm_bwd_kernel(int B, int H, float* __restrict__ gates, int64_t g_ld,
@@ -61,7 +67,7 @@ __global__ void __launch_bounds__(256) lstm_bwd_kernel(int B, int H, float* __re
       dh += v;
     }
     if (dh_b) dh += dh_b[(int64_t)b * dhb_ld + h];
-    const float tc = tanhf(c_t[(int64_t)b * H + h]);
+    const float tc = tanh_fast2(c_t[(int64_t)b * H + h]);
     const float d_o = dh * tc * go * (1.f - go);
     const float dc = dc_io[(int64_t)b * H + h] + dh * go * (1.f - tc * tc);
     const float d_i = dc * gg * gi * (1.f - gi);
