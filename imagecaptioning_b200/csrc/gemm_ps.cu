@@ -51,7 +51,7 @@ struct Params {
   const float* denom;           // EPI 2 in: CE divisor (device scalar)
   uint16_t* dl_hi; uint16_t* dl_lo; int64_t dl_ld;   // EPI 2 out: d logits as bf16 hi (+ lo) copies [M, dl_ld]
   float eps; int ignore_index;
-  int vec4;                     // C rows allow 16-byte accesses (C 16-byte aligned, ldc % 4 == 0, N % 4 == 0): vector red.add
+  int vec4;                     // C rows allow 16-byte accesses (C 16-byte aligned, ldc % 4 == 0, N % 4 == 0): vector red.add / stores
 };
 
 // ------------------------------------------------------------------------------------------------ split pass
@@ -118,10 +118,11 @@ __device__ __forceinline__ void store_chunk(const uint32_t* v, float* tile, cons
 #pragma unroll
   for (int j = 0; j < 32; ++j) tile[lane * 33 + j] = __uint_as_float(v[j]);
   __syncwarp();
-  if (atomic && p.vec4) {
-    // 16-byte vector atomics (red.global.add.v4.f32): lane = (row lane / 8 of a 4-row group, 4 columns lane % 8), 8
-    // instructions of 4 rows x 128 bytes instead of 32 scalar red.add per thread -- split-K epilogues are bound by the red
-    // issue rate.  The pitch-33 tile is read conflict-free (bank = row + 4 * column group + e).
+  if (p.vec4) {
+    // 16-byte accesses: lane = (row lane / 8 of a 4-row group, 4 columns lane % 8) -> 8 instructions of 4 rows x 128 bytes
+    // instead of 32 of 1 row x 128 bytes.  Split-K / accumulate: red.global.add.v4.f32 (the epilogue of the split-K GEMMs is
+    // bound by the red issue rate); plain outputs: st.global.v4.  The pitch-33 tile is read conflict-free
+    // (bank = row + 4 * column group + e).
     const int cg = lane & 7, nv = ncol0 + 4 * cg;
     if (nv < p.N) {                                   // (N % 4 == 0: a column group is inside or outside as a whole)
       float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -129,14 +130,23 @@ __device__ __forceinline__ void store_chunk(const uint32_t* v, float* tile, cons
         if (p.bias) { const float4 t4 = __ldg(reinterpret_cast<const float4*>(p.bias + nv)); b4.x += t4.x; b4.y += t4.y; b4.z += t4.z; b4.w += t4.w; }
         if (p.bias2) { const float4 t4 = __ldg(reinterpret_cast<const float4*>(p.bias2 + nv)); b4.x += t4.x; b4.y += t4.y; b4.z += t4.z; b4.w += t4.w; }
       }
+      const bool plain = !atomic && !p.accumulate && p.act == ACT_NONE;
 #pragma unroll
       for (int rr = 0; rr < 8; ++rr) {
         const int r = rr * 4 + (lane >> 3), m = mrow0 + r;
         if (m < p.M) {
           const float* tr = tile + r * 33 + 4 * cg;
-          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p.C + (int64_t)m * p.ldc + nv),
-                       "f"(fmaf(p.alpha, tr[0], b4.x)), "f"(fmaf(p.alpha, tr[1], b4.y)), "f"(fmaf(p.alpha, tr[2], b4.z)),
-                       "f"(fmaf(p.alpha, tr[3], b4.w)) : "memory");
+          float4 x = make_float4(fmaf(p.alpha, tr[0], b4.x), fmaf(p.alpha, tr[1], b4.y), fmaf(p.alpha, tr[2], b4.z), fmaf(p.alpha, tr[3], b4.w));
+          float4* cp = reinterpret_cast<float4*>(p.C + (int64_t)m * p.ldc + nv);
+          if (atomic) {
+            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(cp), "f"(x.x), "f"(x.y), "f"(x.z), "f"(x.w) : "memory");
+          } else if (plain) {
+            *cp = x;
+          } else {
+            if (p.accumulate) { const float4 c = *cp; x.x += c.x; x.y += c.y; x.z += c.z; x.w += c.w; }
+            x.x = act_apply(x.x, p.act); x.y = act_apply(x.y, p.act); x.z = act_apply(x.z, p.act); x.w = act_apply(x.w, p.act);
+            *cp = x;
+          }
         }
       }
     }
