@@ -729,10 +729,11 @@ static cudaError_t launch2(cudaStream_t st, const CUtensorMap* maps, const Param
   return launch_pdl(kern, dim3(grid), dim3(NUM_THREADS), SMEM, st, maps[0], maps[1], maps[2], maps[3], p);
 }
 // CTA-pair (cta_group::2) tiles.  ALEXCAP_PS_PAIR=0 never, =1 whenever the shape allows, default = where they measured
-// faster on B200 (profiles/r2_gemm_pair.txt): bf16x3 mode when the main loop dominates a tile (K >= 1024; at K = 512 the
-// epilogue bounds both kernels and the 256-row tiles only add M-quantisation waste); bf16 single-product mode only for
-// the split-K shapes (few output tiles, long K: dH, dW_o, the lstm dW GEMMs) -- on large outputs the pair kernel's loads
-// reach ~28 B/clk/SM against ~51 for the single-CTA kernel and it is slower.
+// faster on B200 with the 16-byte epilogue (profiles/r2m_gemm_epilogue.txt; with the scalar epilogue of
+// profiles/r2_gemm_pair.txt the epilogue bounded both kernels at K = 512 and the pair tiles only paid off from K = 1024):
+// bf16x3 mode from K >= 512 (cfg2 vocabulary projection 62.5 -> 54.0 us, Ws projection 43.6 -> 35.0 us), bf16
+// single-product mode from K >= 1024 (cfg3 vocabulary projection 178 -> 166 us = 1077 TFLOP/s, dH 37 -> 26 us; at K = 512
+// the single-CTA kernel is still ahead, 35.5 vs 38.6 us).
 static bool ps_vec4_on() {       // ALEXCAP_PS_RED_V4=0: scalar red.add (A/B timing)
   static const bool on = [] { const char* v = getenv("ALEXCAP_PS_RED_V4"); return !(v && v[0] == '0'); }();
   return on;
@@ -743,7 +744,10 @@ static bool pair_wanted(int M, int N, int K, int nprod) {
   const int64_t tiles = (int64_t)ceil_div(M, BM2) * ceil_div(N, BN2);
   if (tiles < 8) return false;
   if (mode == 1) return true;
-  return nprod == 3 ? K >= 1024 : (K >= 2048 && tiles < 148);
+  static const int k3 = [] { const char* v = getenv("ALEXCAP_PS_PAIR_K3"); return v ? atoi(v) : 512; }();
+  static const int k1 = [] { const char* v = getenv("ALEXCAP_PS_PAIR_K1"); return v ? atoi(v) : 1024; }();
+  if (nprod == 3) return K >= k3;
+  return k1 > 0 ? K >= k1 : (K >= 2048 && tiles < 148);      // (ALEXCAP_PS_PAIR_K1=0: the round-2 rule, for A/B timing)
 }
 
 struct Split { uint16_t* hi; uint16_t* lo; int64_t ld; };

@@ -25,4 +25,6 @@ for name, ta, tb, M, N, K in shapes:
     C = torch.empty(M, N, device=dev)
     F_.gemm(A, B, transa=ta, transb=tb, out=C, engine=300)
     us = t(lambda: F_.gemm(A, B, transa=ta, transb=tb, out=C, engine=500))
-    print(f'{os.environ.get("TAG", "")} {name} M={M} N={N} K={K}  e500 {us:8.1f} us  {2.0 * M * N * K / us / 1e6:7.1f} TF/s', flush=True)
+    F_.gemm(A, B, transa=ta, transb=tb, out=C, engine=400)
+    us1 = t(lambda: F_.gemm(A, B, transa=ta, transb=tb, out=C, engine=600))
+    print(f'{os.environ.get("TAG", "")} {name} M={M} N={N} K={K}  e500 {us:8.1f} us  {2.0 * M * N * K / us / 1e6:7.1f} TF/s   e600 {us1:8.1f} us {2.0 * M * N * K / us1 / 1e6:7.1f} TF/s', flush=True)
