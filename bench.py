@@ -162,6 +162,7 @@ def dominant_kernel_roofline(c, dev, pk):
     nsets = 2 if B * L * (H + D) * esz * 2 > 140e6 else max(2, int(160e6 // (B * L * (H + D) * esz)) + 1)
     for _ in range(nsets):
         Ws_, ft_ = torch.randn(B, L, H, generator=g).to(dev), torch.randn(B, L, D, generator=g).relu().to(dev)
+        Ws_ = F_.ws_exp_form(Ws_)            # the form the training step streams: e^(2 Ws) (one MUFU op per score element)
         if c['dtype'] == 'bf16':             # the storage type the training step streams in this mode
             Ws_, ft_ = Ws_.bfloat16(), ft_.bfloat16()
         sets.append((Ws_, ft_))
@@ -169,19 +170,19 @@ def dominant_kernel_roofline(c, dev, pk):
     bp = torch.randn(S, B, D, generator=g).to(dev)
     dg = torch.randn(S, B, D, generator=g).to(dev)
     wv = (torch.randn(H, generator=g) / H ** 0.5).to(dev)
-    outs = [[F_.attn_step_fwd(Ws, feat, q[t], bp[t], wv) for t in range(S)] for Ws, feat in sets]
+    outs = [[F_.attn_step_fwd(Ws, feat, q[t], bp[t], wv, ws_exp=True) for t in range(S)] for Ws, feat in sets]
     state = {'t': 0, 'n': 1}
 
     def fwd():
         t = state['t'] = (state['t'] + 1) % S
         Ws, feat = sets[t % state['n']]
-        F_.attn_step_fwd(Ws, feat, q[t], bp[t], wv)
+        F_.attn_step_fwd(Ws, feat, q[t], bp[t], wv, ws_exp=True)
 
     def bwd():
         t = state['t'] = (state['t'] + 1) % S
         Ws, feat = sets[t % state['n']]
         a, cx, be, _ = outs[t % state['n']][t]
-        F_.attn_step_bwd(Ws, feat, q[t], wv, a, cx, be, dg[t])
+        F_.attn_step_bwd(Ws, feat, q[t], wv, a, cx, be, dg[t], ws_exp=True)
 
     res = {}
     for name, fn in (('fwd', fwd), ('bwd', bwd)):
@@ -201,7 +202,7 @@ def dominant_kernel_roofline(c, dev, pk):
                     l2_warm=dict(achieved=round(achw, 1), frac=round(achw / pk['hbm'], 4), ms_per_launch=round(warm, 5)))
     out = block('attn_bwd_stream_kernel', w['attn_bwd_bytes_per_launch'], *res['bwd'], NCU_TRAFFIC.get('attn_bwd') if is2 else None)
     out['forward'] = block('attn_fwd_stream_kernel', w['attn_fwd_bytes_per_launch'], *res['fwd'], NCU_TRAFFIC.get('attn_fwd') if is2 else None)
-    out['share_of_step'] = 'backward 18.9 %, forward 15.2 % of the cfg2 step (profiles/r1i_step_breakdown.txt)'
+    out['share_of_step'] = 'backward 16.8 %, forward 15.5 % of the cfg2 step (profiles/r2m_step_breakdown.txt: ncu launch list, serialised)'
     out['note'] = ('achieved = cold (launches alternate over %d distinct Ws/feat sets, %.0f MB each: no L2 reuse); l2_warm = one set '
                    're-read by every launch (part of it hits the 126 MB L2)' % (nsets, B * L * (H + D) * esz / 1e6))
     return out
@@ -261,13 +262,16 @@ def gemm_roofline(c, dev, pk):
     ms_split = time_graph_events(lambda: F_.gemm(A, W, transa=False, transb=True, out=C, engine=400 if bf16 else 300), 8, 6)
     ms_conv = time_graph_events(lambda: F_.gemm(A, W, transa=False, transb=True, out=C, engine=100 if bf16 else 200), 8, 6)
     tf = 2.0 * M * N * K / (ms * 1e-3) / 1e12
-    return dict(kernel='ps::gemm_ps_kernel', bound='tensor', achieved=round(tf, 1), peak=pk['bf16'], unit='TFLOP/s',
+    pair = M >= 256 and N >= 256 and K >= (1024 if bf16 else 512)           # gemm_ps.cu: pair_wanted()
+    return dict(kernel='ps::gemm_ps2_kernel (CTA-pair 256x256 tiles, cta_group::2)' if pair else 'ps::gemm_ps_kernel', bound='tensor', achieved=round(tf, 1), peak=pk['bf16'], unit='TFLOP/s',
                 frac=round(tf / pk['bf16'], 4), traffic=NCU_TRAFFIC.get('gemm_ps_logits') if (c is CONFIGS['cfg2']) else None,
                 ms_per_launch=round(ms, 5), shape=[M, N, K],
                 mma_per_product=1 if bf16 else 3, issued_frac=round((1 if bf16 else 3) * tf / pk['bf16'], 4),
                 with_split_ms=round(ms_split, 5), convert_in_kernel_ms=round(ms_conv, 5), peak_source=pk['src'],
-                note='operands pre-split into bf16 hi/lo copies in HBM, kernel = TMA -> smem -> tcgen05.mma only; bound by '
-                     'L2 -> shared-memory operand traffic of 128-wide tiles (~10 TB/s), not by the tensor pipe; '
+                note='operands pre-split into bf16 hi/lo copies in HBM, kernel = TMA -> smem -> tcgen05.mma only, 16-byte '
+                     'vector epilogue; inside the training step the same projection runs with the fused cross-entropy '
+                     'epilogues (no logits stored): ncu sm__pipe_tensor_cycles_active 55.5 % / 50.7 % '
+                     '(profiles/r2m_ncu_summary.txt); traffic = the round-1 capture of the plain projection; '
                      'convert_in_kernel_ms = the per-step small-GEMM engine (tc::gemm_tc_kernel) on the same shape')
 
 

@@ -681,9 +681,9 @@ int alexcap_gemm_f32(int32_t transa, int32_t transb, int32_t M, int32_t N, int32
 int alexcap_attn_step_fwd(int32_t B, int32_t L, int32_t D, int32_t H, const float* Ws, const float* feat, const float* q,
                           int64_t q_ld, const float* bpre, int64_t bpre_ld, const float* w_v, float* alpha,
                           int64_t alpha_ld, float* ctx, float* beta, float* gctx, int64_t gctx_ld, int32_t rows_bf16, void* stream) {
-  if (rows_bf16) {
+  if (rows_bf16) {       // bit 0: bf16 rows; bit 1: Ws holds 2^(clamp(2 log2(e) Ws)) (the training step's exponential form)
     API_CK(attn_step_fwd_stream(static_cast<cudaStream_t>(stream), B, L, D, H, Ws, feat, q, q_ld, bpre, bpre_ld, w_v, alpha, alpha_ld,
-                                ctx, beta, gctx, gctx_ld, 1, true));
+                                ctx, beta, gctx, gctx_ld, 1, (rows_bf16 & 1) != 0, (rows_bf16 & 2) != 0));
     return 0;
   }
   API_CK(attn_step_fwd(static_cast<cudaStream_t>(stream), B, L, D, H, Ws, feat, q, q_ld, bpre, bpre_ld, w_v, alpha, alpha_ld,
@@ -698,7 +698,8 @@ int alexcap_attn_step_bwd(int32_t B, int32_t L, int32_t D, int32_t H, const floa
                           int64_t de_ld, float* dwv_part, float* dfeat, int32_t rows_bf16, void* stream) {
   if (rows_bf16) {
     API_CK(attn_step_bwd_stream(static_cast<cudaStream_t>(stream), B, L, D, H, Ws, feat, q, q_ld, w_v, alpha, alpha_ld, ctx, beta,
-                                dgctx, dgctx_ld, dalpha_ext, ext_ld, reg_r, dq, dq_ld, dbpre, dbpre_ld, de, de_ld, dwv_part, dfeat, true));
+                                dgctx, dgctx_ld, dalpha_ext, ext_ld, reg_r, dq, dq_ld, dbpre, dbpre_ld, de, de_ld, dwv_part, dfeat,
+                                (rows_bf16 & 1) != 0, (rows_bf16 & 2) != 0));
     return 0;
   }
   API_CK(attn_step_bwd(static_cast<cudaStream_t>(stream), B, L, D, H, Ws, feat, q, q_ld, w_v, alpha, alpha_ld, ctx, beta,

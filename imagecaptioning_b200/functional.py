@@ -136,9 +136,15 @@ def _rows_bf16(Ws, feat):
     return int(Ws.dtype == torch.bfloat16)
 
 
-def attn_step_fwd(Ws, feat, q, bpre, w_v):
+def ws_exp_form(Ws):
+    """The form the training step keeps W(features) in for the streaming attention kernels: 2^(clamp(2 log2(e) Ws, +-60))
+    = e^(2 Ws) (csrc/common.cuh: exp2c).  Pass the result with ws_exp=True to attn_step_fwd / attn_step_bwd."""
+    return torch.exp2((2.8853900817779268 * Ws.float()).clamp(-60.0, 60.0)).to(Ws.dtype)
+
+
+def attn_step_fwd(Ws, feat, q, bpre, w_v, ws_exp=False):
     """One fused attention step.  Ws[B,L,H], feat[B,L,D] (both fp32, or both bf16 = the bf16 storage mode of the streamed
-    grids), q[B,H], bpre[B,D], w_v[H] -> (alpha[B,L], ctx[B,D], beta[B,D], gctx[B,D])."""
+    grids), q[B,H], bpre[B,D], w_v[H] -> (alpha[B,L], ctx[B,D], beta[B,D], gctx[B,D]).  ws_exp: Ws is ws_exp_form(Ws)."""
     lib = ensure_device(Ws.device)
     _req(Ws, feat, q, bpre, w_v)
     B, L, H = Ws.shape
@@ -148,13 +154,13 @@ def attn_step_fwd(Ws, feat, q, bpre, w_v):
     beta = torch.empty_like(ctx)
     gctx = torch.empty_like(ctx)
     check(lib.alexcap_attn_step_fwd(B, L, D, H, _ptr(Ws), _ptr(feat), _ptr(q), q.stride(0), _ptr(bpre), bpre.stride(0),
-                                    _ptr(w_v), _ptr(alpha), L, _ptr(ctx), _ptr(beta), _ptr(gctx), D, _rows_bf16(Ws, feat),
-                                    _stream()),
+                                    _ptr(w_v), _ptr(alpha), L, _ptr(ctx), _ptr(beta), _ptr(gctx), D,
+                                    _rows_bf16(Ws, feat) | (2 if ws_exp else 0), _stream()),
           'alexcap_attn_step_fwd')
     return alpha, ctx, beta, gctx
 
 
-def attn_step_bwd(Ws, feat, q, w_v, alpha, ctx, beta, dgctx, dalpha_ext=None, reg_r=None, need_dfeat=False):
+def attn_step_bwd(Ws, feat, q, w_v, alpha, ctx, beta, dgctx, dalpha_ext=None, reg_r=None, need_dfeat=False, ws_exp=False):
     """Backward of one attention step -> (dq[B,H], dbpre[B,D], de[B,L], dwv_part[B,H], dfeat or None)."""
     lib = ensure_device(Ws.device)
     _req(Ws, feat, q, w_v, alpha, ctx, beta, dgctx, dalpha_ext, reg_r)
@@ -169,7 +175,8 @@ def attn_step_bwd(Ws, feat, q, w_v, alpha, ctx, beta, dgctx, dalpha_ext=None, re
     check(lib.alexcap_attn_step_bwd(B, L, D, H, _ptr(Ws), _ptr(feat), _ptr(q), q.stride(0), _ptr(w_v), _ptr(alpha),
                                     alpha.stride(0), _ptr(ctx), _ptr(beta), _ptr(dgctx), dgctx.stride(0),
                                     _ptr(dalpha_ext), L, _ptr(reg_r), _ptr(dq), H, _ptr(dbpre), D, _ptr(de), L,
-                                    _ptr(dwv), _ptr(dfeat), _rows_bf16(Ws, feat), _stream()), 'alexcap_attn_step_bwd')
+                                    _ptr(dwv), _ptr(dfeat), _rows_bf16(Ws, feat) | (2 if ws_exp else 0), _stream()),
+          'alexcap_attn_step_bwd')
     return dq, dbpre, de, dwv, dfeat
 
 

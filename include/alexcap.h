@@ -309,8 +309,10 @@ ALEXCAP_API int alexcap_gemm_f32(int32_t transa, int32_t transb, int32_t M, int3
 /* One attention step, Attention.forward with W(features) precomputed (AttentionLanguageModule.py:15-22) and the
  * beta gate of Decoder.forward (:74-75) fused:  alpha[b,:] (row stride alpha_ld), ctx[B,D], beta[B,D],
  * gctx[b,:] (row stride gctx_ld) = sigmoid(bpre) * ctx.   q [B,H] (q_ld), bpre [B,D] (bpre_ld).
- * rows_bf16 != 0 (both step entry points): Ws and feat point at BF16 rows of the same shapes (the ALEXCAP_BF16 storage of the
- * streamed grids, half the bytes per launch; D, H multiples of 8); everything else stays fp32. */
+ * rows_bf16 (both step entry points) is a bit field.  Bit 0: Ws and feat point at BF16 rows of the same shapes (the
+ * ALEXCAP_BF16 storage of the streamed grids, half the bytes per launch; D, H multiples of 8); everything else stays fp32.
+ * Bit 1: Ws holds 2^(clamp(2 log2(e) W(features), +-60)) = e^(2 Ws) instead of the pre-activation -- the form the training
+ * entry points keep it in (one MUFU op per score element: tanh(w + q) = 1 - 2 / (1 + e^(2w) e^(2q))); streaming kernels only. */
 ALEXCAP_API int alexcap_attn_step_fwd(int32_t B, int32_t L, int32_t D, int32_t H,
                           const float* Ws, const float* feat, const float* q, int64_t q_ld,
                           const float* bpre, int64_t bpre_ld, const float* w_v,

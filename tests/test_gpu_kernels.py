@@ -160,6 +160,29 @@ def test_cross_entropy_value_and_grad(F_, N, C):
     assert rel_err(dl, xr.grad) < 1e-5
 
 
+@pytest.mark.parametrize('B,L,D,H', [(6, 49, 64, 96), (130, 20, 128, 512), (160, 33, 64, 40)])
+def test_attn_step_exponential_ws_form_equals_plain_kernels(F_, B, L, D, H):
+    """The training step hands the streaming kernels e^(2 Ws) instead of Ws (rows_bf16 bit 1: one MUFU op per score element):
+    same alpha / ctx / gctx and the same backward outputs as the plain instantiation on the same inputs, whole and split images."""
+    g = torch.Generator().manual_seed(B + L)
+    Ws = (torch.randn(B, L, H, generator=g) * 1.5).to(DEV)
+    feat = torch.randn(B, L, D, generator=g).relu().to(DEV)
+    q = (torch.randn(B, H, generator=g) * 1.5).to(DEV)
+    bpre = torch.randn(B, D, generator=g).to(DEV)
+    wv = (torch.randn(H, generator=g) / H ** 0.5 * 3).to(DEV)
+    We = F_.ws_exp_form(Ws)
+    a0 = F_.attn_step_fwd(Ws, feat, q, bpre, wv)
+    a1 = F_.attn_step_fwd(We, feat, q, bpre, wv, ws_exp=True)
+    for x, y in zip(a0, a1):
+        assert rel_err(y, x) < 1e-5
+    dg = torch.randn(B, D, generator=g).to(DEV)
+    r = (torch.randn(B, L, generator=g) * 0.1).to(DEV)
+    b0 = F_.attn_step_bwd(Ws, feat, q, wv, a0[0], a0[1], a0[2], dg, None, r)
+    b1 = F_.attn_step_bwd(We, feat, q, wv, a0[0], a0[1], a0[2], dg, None, r, ws_exp=True)
+    for x, y in zip(b0[:4], b1[:4]):
+        assert rel_err(y, x) < 2e-5
+
+
 def test_non_cuda_tensor_is_refused(F_):
     from imagecaptioning_b200._lib import AlexcapError
     with pytest.raises(AlexcapError):
