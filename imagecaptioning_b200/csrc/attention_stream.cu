@@ -81,6 +81,13 @@ bool prefetch_before_wait() {
   return on;
 }
 
+// Static header members (backward: q, beta, ctx, the reference row of Ws) copied before griddepcontrol.wait, only d gctx after
+// it (ALEXCAP_ATT_HDR_SPLIT=0 disables).
+bool header_split() {
+  static const bool on = [] { const char* v = getenv("ALEXCAP_ATT_HDR_SPLIT"); return !(v && v[0] == '0'); }();
+  return on;
+}
+
 int sm_count() {
   static int n = 0;
   if (!n) {
@@ -241,7 +248,7 @@ cudaError_t attn_step_fwd_stream(cudaStream_t st, int B, int L, int D, int H, co
               slot_floats, env_int("ALEXCAP_ATT_DRY", 0), l2_fraction()};
   a.bf16 = rows_bf16 ? 1 : 0;
   a.ws_exp = ws_exp ? 1 : 0;
-  a.pdl = (static_ready && prefetch_before_wait()) ? 2 : 1;
+  a.pdl = !static_ready ? 1 : (prefetch_before_wait() ? 2 : (header_split() ? 3 : 1));
   a.prof = prof_ptr();
   const size_t smem = (size_t)g.NST * g.stage_floats * 4 + fwd_fixed_smem(D, seg_pad, g.maxseg);
   const int nj = ceil_div(H, 128);
@@ -301,7 +308,7 @@ cudaError_t attn_step_bwd_stream(cudaStream_t st, int B, int L, int D, int H, co
   const size_t smem = (size_t)g.NST * g.stage_floats * 4 + bwd_fixed_smem(D, H, seg_pad, rp_pad, g.maxseg);
   a.bf16 = rows_bf16 ? 1 : 0;
   a.ws_exp = ws_exp ? 1 : 0;
-  a.pdl = (static_ready && prefetch_before_wait()) ? 2 : 1;
+  a.pdl = !static_ready ? 1 : (prefetch_before_wait() ? 2 : (header_split() ? 3 : 1));
   a.prof = prof_ptr() ? prof_ptr() + 8 : nullptr;
 #define LAUNCH_BWD_K(AW, BF, EW)                                                            \
   do {                                                                                      \

@@ -74,7 +74,8 @@ struct Ring {
 
 // Small per-image vectors that open every segment (the "header piece"): up to 5 rows copied back to back.  Byte-addressed:
 // a member may be fp32 or bf16 (the reference row of Ws in bf16-storage mode).
-struct Header { const char* p[5]; int64_t ld[5]; int n[5]; int count; };     // p: base, ld: bytes per image, n: bytes to copy
+struct Header { const char* p[5]; int64_t ld[5]; int n[5]; int count; unsigned dyn = 0x1fu; };   // p: base, ld: bytes per image, n: bytes to copy
+// dyn: bit i set = member i is written by the kernel that precedes this launch (the others were final long before it)
 __device__ __forceinline__ void hdr_set(Header& hd, int i, const void* p, int64_t ld_elems, int n_elems, int esz) {
   hd.p[i] = static_cast<const char*>(p); hd.ld[i] = ld_elems * esz; hd.n[i] = n_elems * esz;
 }
@@ -82,19 +83,26 @@ __device__ __forceinline__ void hdr_set(Header& hd, int i, const void* p, int64_
 // Producer: for every image segment of this CTA's row range stream [header] [X0 rows] [X1 rows] (R0- / R1-row pieces).
 // esz: bytes per element of the X0 / X1 rows (4, or 2 in bf16-storage mode).
 // `k` is the producer's ring cursor: a persistent caller (time_loop.cu) keeps it across calls.
-// `defer` (stand-alone kernels launched with programmatic dependent launch, static rows known to be complete): the header is
-// the only member that depends on the preceding kernel, so its stage is reserved in ring order but its copies are ISSUED only
-// after griddepcontrol.wait -- the row pieces that fill the rest of the ring are fetched while the predecessor still runs.
+// `defer` (stand-alone kernels launched with programmatic dependent launch; the caller guarantees that everything but the
+// header members flagged in `hd.dyn` was complete before the PRECEDING kernel started):
+//   1: the first header's stage is armed and its static members are copied at once; griddepcontrol.wait follows and only then
+//      the dynamic members (backward: d gctx) and the row pieces -- the latency of the static copies hides under the
+//      predecessor's tail;
+//   2: as 1, and the row pieces that fill the rest of the ring are also fetched before the wait (experiment, see
+//      attention_stream.cu: prefetch_before_wait).
 __device__ __forceinline__ void produce(const Ring& ring, Cursor& k, int64_t row0, int64_t row1, int L, int R0, int R1, int rpi,
                                         const Header& hd, const void* X0, int n0, const void* X1, int n1, int esz,
-                                        bool defer = false) {
-  bool pending = false;                              // the first header's copies have not been issued yet
+                                        int defer = 0) {
+  bool pending = false;                              // the first header's dynamic copies have not been issued yet
   Cursor kh{0, 0u};
   int hb = 0, since = 0;
-  auto issue_header = [&](const Cursor& kc, int b) {
+  // which: 0 = the static members, 1 = the dynamic members, 2 = all
+  auto issue_header = [&](const Cursor& kc, int b, int which) {
     int off = 0;                                     // bytes (every member is a multiple of 16 bytes)
     for (int i = 0; i < hd.count; ++i) {
-      pipe::bulk_g2s(reinterpret_cast<char*>(ring.stage(kc)) + off, hd.p[i] + (int64_t)b * hd.ld[i], (uint32_t)hd.n[i], &ring.full[kc.s]);
+      const int dyn = (int)((hd.dyn >> i) & 1u);
+      if (which == 2 || which == dyn)
+        pipe::bulk_g2s(reinterpret_cast<char*>(ring.stage(kc)) + off, hd.p[i] + (int64_t)b * hd.ld[i], (uint32_t)hd.n[i], &ring.full[kc.s]);
       off += hd.n[i];
     }
   };
@@ -108,8 +116,13 @@ __device__ __forceinline__ void produce(const Ring& ring, Cursor& k, int64_t row
       uint32_t bytes = 0;
       for (int i = 0; i < hd.count; ++i) bytes += (uint32_t)hd.n[i];
       ring.begin(k, bytes);
-      if (defer && lo == row0) { pending = true; kh = k; hb = b; since = 0; }
-      else issue_header(k, b);
+      if (defer && lo == row0) {
+        issue_header(k, b, 0);
+        if (defer == 1) { pdl_wait(); issue_header(k, b, 1); }
+        else { pending = true; kh = k; hb = b; since = 0; }
+      } else {
+        issue_header(k, b, 2);
+      }
       k.next(ring.NST);
     }
     for (int pass = 0; pass < 2; ++pass) {
@@ -119,7 +132,7 @@ __device__ __forceinline__ void produce(const Ring& ring, Cursor& k, int64_t row
       for (int r0 = 0; r0 < nl; r0 += R, k.next(ring.NST)) {
         if (pending && ++since >= ring.NST) {        // the ring is full: the next stage is the header's own
           pdl_wait();
-          issue_header(kh, hb);
+          issue_header(kh, hb, 1);
           pending = false;
         }
         const int rows = min(R, nl - r0);
@@ -128,7 +141,7 @@ __device__ __forceinline__ void produce(const Ring& ring, Cursor& k, int64_t row
         ring.copy_rows(k, reinterpret_cast<const float*>(X + (src_row + r0) * n * esz), bytes);
       }
     }
-    if (pending) { pdl_wait(); issue_header(kh, hb); pending = false; }
+    if (pending) { pdl_wait(); issue_header(kh, hb, 1); pending = false; }
     lo = hi;
   }
 }
@@ -174,7 +187,7 @@ struct SAttnFwdP {
   int bf16 = 0;       // Ws / feat point at bf16 rows (same shapes): selects the BF instantiation
   int ws_exp = 0;     // Ws holds EXP2C(W(features)) instead of the pre-activation: selects the EW instantiation
   int pdl = 0;        // 0: no griddepcontrol.wait in the body (persistent caller); 1: every thread waits at body entry;
-                      // 2: as 1, but the producer prefetches Ws pieces BEFORE its wait (see produce(): `defer`)
+                      // 2 / 3: the consumers wait at body entry, the producer inside produce() (`defer` = 2 / 1)
   unsigned long long* prof = nullptr;
 };
 
@@ -212,7 +225,7 @@ __device__ __forceinline__ void attn_fwd_body(const SAttnFwdP& a, float* sm, con
       hd.count = 2;
       if (a.l2_frac > 0.f) { ring.policy = pipe::l2_policy_evict_last(a.l2_frac); ring.hinted = true; }
       if (a.pdl == 1) pdl_wait();
-      produce(ring, k, row0, row1, L, RH, RD, a.rpi, hd, a.Ws, a.H, a.feat, D, BF ? 2 : 4, a.pdl == 2);
+      produce(ring, k, row0, row1, L, RH, RD, a.rpi, hd, a.Ws, a.H, a.feat, D, BF ? 2 : 4, a.pdl == 2 ? 2 : (a.pdl == 3 ? 1 : 0));
     }
     return;
   }
@@ -511,7 +524,8 @@ __device__ __forceinline__ void attn_bwd_body(const SAttnBwdP& a, float* sm, con
       hd.count = 5;
       if (a.l2_frac > 0.f) { ring.policy = pipe::l2_policy_evict_last(a.l2_frac); ring.hinted = true; }
       if (a.pdl == 1) pdl_wait();
-      produce(ring, k, row0, row1, L, RD, RH, 1, hd, a.feat, D, a.Ws, H, BF ? 2 : 4, a.pdl == 2);     // feat pieces, then Ws pieces
+      hd.dyn = 1u << 1;                                                // only d gctx comes from the preceding kernel
+      produce(ring, k, row0, row1, L, RD, RH, 1, hd, a.feat, D, a.Ws, H, BF ? 2 : 4, a.pdl == 2 ? 2 : (a.pdl == 3 ? 1 : 0));     // feat pieces, then Ws pieces
     }
     return;
   }
