@@ -47,7 +47,7 @@ struct AttnWs {
   float *MASK, *Hd;
   float *logits, *row_loss, *scal;   // scal: [0]=n_valid [1]=ce_sum [2]=reg
   float *dHout, *dh_next, *dc, *dgctx, *R, *dwv_part, *dWs, *dEmbIn, *dh0, *dc0, *dm;
-  float *cs_scratch, *reg_scratch;
+  float *cs_scratch, *cs_scratch2, *reg_scratch;
   uint8_t* arena; size_t arena_bytes;   // bf16 hi/lo operand copies of the big GEMMs (training layout only)
   uint16_t* loop_bf16; unsigned* loop_bar;   // persistent time loop: bf16 operand copies of h / gctx / weight slices; grid barrier
   float4* ce_stats; float* row_lse;          // fused vocabulary CE: per-row partial statistics, log-sum-exp
@@ -109,6 +109,7 @@ AttnWs attn_layout(const alexcap_dims* d, void* base, bool with_logits) {
   int64_t maxn = Vp;
   if (W5 > maxn) maxn = W5;
   w.cs_scratch = a.take<float>(64 * maxn);
+  w.cs_scratch2 = a.take<float>(64 * Vp);        // column-sum scratch of the deferred dW_o / db_o work (runs on a side stream)
   w.reg_scratch = a.take<float>(256);
   w.loop_bar = a.take<unsigned>(64);
   {
@@ -263,6 +264,39 @@ bool dws_overlap_enabled() {
   // persistent GEMM CTAs more than it hides -- so the fork is OFF unless ALEXCAP_DWS_OVERLAP=1
   static const bool on = [] { const char* v = getenv("ALEXCAP_DWS_OVERLAP"); return v && v[0] == '1'; }();
   return on;
+}
+
+// Second fork (its own stream and events): dW_o / db_o of the vocabulary projection underneath the reverse-time loop.
+SideStream& side_stream2() {
+  static thread_local SideStream ss;
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess) { ss.ok = false; return ss; }
+  if (ss.dev != dev) {
+    ss.ok = cudaStreamCreateWithFlags(&ss.s, cudaStreamNonBlocking) == cudaSuccess &&
+            cudaEventCreateWithFlags(&ss.fork, cudaEventDisableTiming) == cudaSuccess &&
+            cudaEventCreateWithFlags(&ss.join, cudaEventDisableTiming) == cudaSuccess;
+    ss.dev = dev;
+  }
+  return ss;
+}
+struct CtaCapScope {
+  int saved;
+  explicit CtaCapScope(int cap) : saved(gemm_cta_cap()) { gemm_cta_cap() = cap; }
+  ~CtaCapScope() { gemm_cta_cap() = saved; }
+};
+// SMs the reverse-time loop leaves idle: its attention kernel runs one image per CTA (B CTAs) and its per-step GEMMs are
+// sized for <= 128 CTAs, so with B <= #SMs - 16 a persistent GEMM capped to the remaining SMs runs beside the whole loop
+// without taking a slot from it.  0 = no room (or ALEXCAP_DWO_DEFER=0).
+int dwo_defer_ctas(int B) {
+  static const bool off = [] { const char* v = getenv("ALEXCAP_DWO_DEFER"); return v && v[0] == '0'; }();
+  int nsm = 0, dev = 0;
+  if (off || cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
+    return 0;
+  const int busy = B > 128 ? B : 128;
+  const int spare = (nsm - busy) & ~1;                 // (an even count: CTA pairs)
+  static const int want = [] { const char* v = getenv("ALEXCAP_DWO_CAP"); return v ? atoi(v) & ~1 : 0; }();   // (tuning)
+  if (spare < 16) return 0;
+  return (want >= 2 && want < spare) ? want : spare;
 }
 
 // ------------------------------------------------------------------------------------------ attention backward core
@@ -454,8 +488,9 @@ static int attn_train_phases(const alexcap_dims* d, const alexcap_attn_params* P
   AttnWs w = attn_layout(d, nullptr, true);
   if (int rc = check_attn_args(d, P, feat, workspace, workspace_bytes, w.bytes)) return rc;
   if (!gt || !G || !loss_out) return fail(ALEXCAP_E_BADARG, "NULL gt / grads / loss_out");
-  if (phase != 1 && phase != 2 && phase != 3 && phase != 4 && phase != 8 && phase != 16 && phase != 32)
-    return fail(ALEXCAP_E_BADARG, "phase must be 1, 2, 3 (= 1|2), 4 or 8 (the halves of 2), 16 or 32 (the halves of 1)");
+  if (phase != 1 && phase != 2 && phase != 3 && phase != 4 && phase != 8 && phase != 16 && phase != 32 && phase != 64 && phase != 128)
+    return fail(ALEXCAP_E_BADARG, "phase must be 1, 2, 3 (= 1|2), 4 or 8 (the halves of 2), 16 or 32 (the halves of 1), or 128 + 64 "
+                                  "(32 with dW_o / db_o split off)");
   w = attn_layout(d, workspace, true);
   // phases 2 / 4 / 8 / 32 continue the step an earlier phase started (same arguments and workspace): feat, W_W, dgates ... stay
   // split -- but only what the EARLIER phases made: a repeated phase 4 (say) must not find the copies of its previous run.
@@ -468,8 +503,8 @@ static int attn_train_phases(const alexcap_dims* d, const alexcap_attn_params* P
   if (!fresh && (step_arena.base != w.arena || step_arena.bytes != w.arena_bytes))
     return fail(ALEXCAP_E_BADARG, "phase 2/4/8/32 on a workspace whose step was not started by phase 1/16 with the same dims");
   ArenaScope arena_scope(w.arena, w.arena_bytes, &step_arena, fresh);
-  if (!fresh && step_arena.base) {
-    size_t mark = (phase == 8) ? ss.mark_after_4 : (phase == 32) ? ss.mark_after_16 : ss.mark_after_1;
+  if (!fresh && step_arena.base && phase != 64) {      // (64 runs BESIDE phase 4 and only reads copies phase 128 made)
+    size_t mark = (phase == 8) ? ss.mark_after_4 : (phase == 32 || phase == 128) ? ss.mark_after_16 : ss.mark_after_1;
     if (mark > step_arena.used) mark = step_arena.used;
     split_arena_release(&step_arena, mark);
   }
@@ -477,19 +512,44 @@ static int attn_train_phases(const alexcap_dims* d, const alexcap_attn_params* P
   const int B = d->B, D = d->D, H = d->H, Vp = d->Vp, S = d->S, L = d->L, SB = S * B;
   const int64_t DH = D + H;
   const bool reg = d->reg_weight != 0.f;
+  bool deferred_dwo = false;
   if ((phase & 1) || phase == 16) {
     if (int rc = attn_fwd_core(d, P, feat, gt, drop_mask, w, st)) return rc;
     ss.mark_after_16 = ss.mark_after_1 = ss.mark_after_4 = step_arena.used;
   }
-  if ((phase & 1) || phase == 32) {
-    const float* hout = w.Hd ? w.Hd : w.XH + (int64_t)B * DH + D;
-    const int64_t hld = w.Hd ? H : DH;
+  const float* hout = w.Hd ? w.Hd : w.XH + (int64_t)B * DH + D;
+  const int64_t hld = w.Hd ? H : DH;
+  if (phase == 64) {
+    // dW_o / db_o split off phase 128: on the caller's stream (a data-parallel caller runs it on its side stream, followed by
+    // the all-reduce of deep_output.*, while phase 4 runs on the main stream), capped to the SMs the reverse loop leaves idle
+    // (the same pure predicate phase 128 evaluates: when it is false, 128 computed the two gradients itself)
+    const int spare = (w.ce_stats && attn_engine() == 1) ? dwo_defer_ctas(B) : 0;
+    if (spare <= 0) return 0;
+    CtaCapScope cap(spare);
+    return vocab_ce_dwo(st, SB, Vp, H, hout, hld, w.ldV, w.ce_stats, G->deep_w, G->deep_b, w.cs_scratch2);
+  }
+  if ((phase & 1) || phase == 32 || phase == 128) {
     // vocabulary projection (AttentionLanguageModule.py:79) + CustomCrossEntropyLoss + vocab backward, in L2-sized row chunks
     API_CK(count_valid(st, w.tgt_tm, SB, d->ignore_index, w.scal));
     if (w.ce_stats) {
+      // Whole step in one call: dW_o and db_o, which nothing else in the step reads, are taken off the critical path -- they
+      // run on a side stream, capped to the SMs the reverse-time loop leaves idle, underneath that loop (joined at the end).
+      SideStream& s2 = side_stream2();
+      const int spare = ((phase == 3 || phase == 128) && attn_engine() == 1) ? dwo_defer_ctas(B) : 0;
+      deferred_dwo = spare > 0 && (s2.ok || phase == 128);        // (phase 128: phase 64, on the caller's stream, does them)
       if (int rc = vocab_ce_fused(st, SB, Vp, H, hout, hld, P->deep_w, P->deep_b, w.tgt_tm, w.ldV, w.ce_stats, w.row_lse,
                                   d->label_smoothing, d->ignore_index, ce_denominator ? ce_denominator : w.scal, w.row_loss,
-                                  G->deep_w, G->deep_b, w.dHout, w.cs_scratch)) return rc;
+                                  G->deep_w, G->deep_b, w.dHout, w.cs_scratch, deferred_dwo)) return rc;
+      if (deferred_dwo && phase == 128) deferred_dwo = false;      // nothing to fork or join inside this call
+      if (deferred_dwo) {
+        API_CK(cudaEventRecord(s2.fork, st));
+        API_CK(cudaStreamWaitEvent(s2.s, s2.fork, 0));
+        {
+          CtaCapScope cap(spare);
+          if (int rc = vocab_ce_dwo(s2.s, SB, Vp, H, hout, hld, w.ldV, w.ce_stats, G->deep_w, G->deep_b, w.cs_scratch2)) return rc;
+        }
+        API_CK(cudaEventRecord(s2.join, s2.s));
+      }
     } else if (int rc = vocab_ce_chunked(st, SB, Vp, H, hout, hld, P->deep_w, P->deep_b, w.tgt_tm, w.ldV, w.logits, d->label_smoothing,
                                          d->ignore_index, ce_denominator ? ce_denominator : w.scal, w.row_loss, G->deep_w, G->deep_b,
                                          w.dHout, w.cs_scratch)) return rc;
@@ -502,6 +562,7 @@ static int attn_train_phases(const alexcap_dims* d, const alexcap_attn_params* P
   }
   int rc = 0;
   if (phase & 2) rc = attn_bwd_core(d, P, feat, nullptr, reg ? w.R : nullptr, G, dfeat, w, st, 3);
+  if (deferred_dwo) API_CK(cudaStreamWaitEvent(st, side_stream2().join, 0));     // join: dW_o / db_o are complete on `st`
   else if (phase == 4 || phase == 8) rc = attn_bwd_core(d, P, feat, nullptr, reg ? w.R : nullptr, G, dfeat, w, st, phase == 4 ? 1 : 2);
   if (phase == 4) ss.mark_after_4 = step_arena.used;
   return rc;

@@ -144,7 +144,8 @@ inline bool vocab_ce_fused_ok(int SB, int Vp, int H) {
 }
 inline int vocab_ce_fused(cudaStream_t st, int SB, int Vp, int H, const float* hout, int64_t hld, const float* Wo, const float* bo,
                           const int32_t* tgt_tm, int64_t ldV, float4* stats, float* row_lse, float eps, int ignore_index,
-                          const float* denom, float* row_loss, float* dWo, float* dbo, float* dHout, float* cs_scratch) {
+                          const float* denom, float* row_loss, float* dWo, float* dbo, float* dHout, float* cs_scratch,
+                          bool defer_dwo = false) {
   SplitArena* arena = split_arena();
   if (!arena) return fail(ALEXCAP_E_BADARG, "vocab_ce_fused: no operand arena");
   const int nprod = gemm_engine() == 3 ? 3 : 1;
@@ -159,9 +160,28 @@ inline int vocab_ce_fused(cudaStream_t st, int SB, int Vp, int H, const float* h
   API_CK(gemm_ps_ce(st, true, SB, Vp, H, hout, hld, Wo, H, bo, tgt_tm, eps, ignore_index, denom, stats, row_lse, row_loss,
                     dl_hi, dl_lo, dl_ld, nprod, arena));
   // dW_o = dlogits^T h ; db_o = colsum(dlogits) ; dH = dlogits W_o      (all three read the copies)
-  API_CK(gemm_f32(st, true, false, Vp, H, SB, 1.f, key, ldV, hout, hld, dWo, H, nullptr, nullptr, false, ACT_NONE));
-  API_CK(col_sum_bf16(st, dl_hi, dl_lo, SB, Vp, dl_ld, dbo, false, cs_scratch));
+  // (defer_dwo: the reverse-time loop only needs dH; the caller runs vocab_ce_dwo() on a side stream underneath that loop)
+  if (!defer_dwo) {
+    API_CK(gemm_f32(st, true, false, Vp, H, SB, 1.f, key, ldV, hout, hld, dWo, H, nullptr, nullptr, false, ACT_NONE));
+    API_CK(col_sum_bf16(st, dl_hi, dl_lo, SB, Vp, dl_ld, dbo, false, cs_scratch));
+  }
   API_CK(gemm_f32(st, false, false, SB, H, Vp, 1.f, key, ldV, Wo, H, dHout, H, nullptr, nullptr, false, ACT_NONE));
+  return 0;
+}
+// The two vocabulary gradients that nothing downstream in the step reads: dW_o = dlogits^T h, db_o = colsum(dlogits), from the
+// operand copies vocab_ce_fused() left in the arena (same key).  `cs_scratch` must not be shared with work on another stream.
+inline int vocab_ce_dwo(cudaStream_t st, int SB, int Vp, int H, const float* hout, int64_t hld, int64_t ldV, const float4* stats,
+                        float* dWo, float* dbo, float* cs_scratch) {
+  SplitArena* arena = split_arena();
+  const float* key = reinterpret_cast<const float*>(stats);
+  uint16_t *dl_hi = nullptr, *dl_lo = nullptr;
+  int64_t dl_ld = 0;
+  if (!split_arena_find(arena, key, &dl_hi, &dl_lo, &dl_ld))
+    return fail(ALEXCAP_E_WORKSPACE, "vocab_ce_dwo: the d logits copies are not in the operand arena");
+  // (the HBM-streaming column sum first: it then runs beside the loss finalisation, not beside the loop's attention kernels --
+  //  measured 1.873 vs 1.902 ms for the other order)
+  API_CK(col_sum_bf16(st, dl_hi, dl_lo, SB, Vp, dl_ld, dbo, false, cs_scratch));
+  API_CK(gemm_f32(st, true, false, Vp, H, SB, 1.f, key, ldV, hout, hld, dWo, H, nullptr, nullptr, false, ACT_NONE));
   return 0;
 }
 

@@ -816,6 +816,17 @@ bool split_arena_reserve(SplitArena* a, const float* key, int rows, int cols, in
   return true;
 }
 
+// The copies a producer registered under `key` (split_arena_reserve) earlier in the step; false if there are none.
+bool split_arena_find(const SplitArena* a, const float* key, uint16_t** hi, uint16_t** lo, int64_t* ldo_out) {
+  if (!a) return false;
+  for (int i = a->n - 1; i >= 0; --i)
+    if (a->e[i].src == key && a->e[i].produced) {
+      *hi = a->e[i].hi; *lo = a->e[i].lo; *ldo_out = a->e[i].ldo;
+      return true;
+    }
+  return false;
+}
+
 // bf16 (hi) copy of X out of the arena -- made now if no GEMM has split X yet.  Used to stream Ws / feat as bf16 rows through
 // the attention kernels in ALEXCAP_BF16 mode.
 cudaError_t split_arena_get_hi(cudaStream_t st, SplitArena* a, const float* X, int rows, int cols, int64_t ld, const uint16_t** hi,
@@ -857,6 +868,7 @@ cudaError_t gemm_ps_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, 
 
   int nsm = 148;
   { int dev = 0; if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev); }
+  if (gemm_cta_cap() > 0 && gemm_cta_cap() < nsm) nsm = gemm_cta_cap();
   // ---- CTA-pair 256 x 256 tiles (cta_group::2) when the output is large enough to give every SM pair work
   if (pair_wanted(M, N, K, nprod)) {
     const int ncl = nsm / 2;
@@ -1023,6 +1035,7 @@ cudaError_t gemm_ps_ce(cudaStream_t st, bool want_grad, int M, int N, int K, con
   if (!ok) return cudaErrorInvalidValue;
   int nsm = 148;
   { int dev = 0; if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev); }
+  if (gemm_cta_cap() > 0 && gemm_cta_cap() < nsm) nsm = gemm_cta_cap();
   const int grid = p.n_items < nsm ? p.n_items : nsm;
   cudaError_t e;
   if (BN == 256 && pair_wanted(M, N, K, nprod)) {

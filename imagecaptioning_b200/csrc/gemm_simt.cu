@@ -209,6 +209,10 @@ static cudaError_t launch_cfg(cudaStream_t st, bool ta, bool tb, const GemmP& p)
   return cudaGetLastError();
 }
 
+int& gemm_cta_cap() {
+  static thread_local int cap = 0;
+  return cap;
+}
 bool& gemm_b_is_weight() {
   static thread_local bool on = false;
   return on;

@@ -49,6 +49,7 @@ cudaError_t split_arena_get_hi(cudaStream_t st, SplitArena* a, const float* X, i
                                int64_t* ldo);
 bool split_arena_reserve(SplitArena* a, const float* key, int rows, int cols, int64_t ld, bool with_lo, uint16_t** hi,
                          uint16_t** lo, int64_t* ldo_out);
+bool split_arena_find(const SplitArena* a, const float* key, uint16_t** hi, uint16_t** lo, int64_t* ldo_out);
 cudaError_t gemm_ps_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, float alpha,
                         const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
                         const float* bias, const float* bias2, bool accumulate, int act, int force_splits, int nprod,
@@ -68,6 +69,9 @@ void gemm_engine_set_default(int engine); // process-wide default, picked up by 
 // Hint for the calls made while it is true: the B operand holds weights that were final before the PREVIOUS kernel of the
 // stream started, so the kernel may fetch B tiles ahead of its programmatic-dependent-launch wait (api.cu: WeightBScope).
 bool& gemm_b_is_weight();
+// > 0: the pre-split engine's persistent kernels launched while it is set use at most this many CTAs (SMs), whatever the
+// device has -- for a GEMM forked onto a side stream next to kernels that need the other SMs (api.cu: CtaCapScope).
+int& gemm_cta_cap();
 
 // ---- attention (attention.cu)
 cudaError_t attn_step_fwd(cudaStream_t st, int B, int L, int D, int H, const float* Ws, const float* feat,

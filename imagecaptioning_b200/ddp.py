@@ -104,12 +104,19 @@ class GradAllReducer:
             self._reduce(step._slot.n_valid)
         run(phase=16)
         main.wait_stream(self.side)
-        for gi, (phase, g) in enumerate(((32, groups[0]), (4, groups[1]))):
-            run(phase=phase)
-            self.side.wait_stream(main)
-            with torch.cuda.stream(self.side):
-                if g.numel():
-                    self._reduce(g, gi)
+        # vocabulary projection + loss + dH on the main stream (phase 128); d deep_output.* (phase 64: restricted to the SMs
+        # the reverse loop leaves idle) and its all-reduce follow on the side stream, underneath phase 4
+        run(phase=128)
+        self.side.wait_stream(main)
+        with torch.cuda.stream(self.side):
+            run(phase=64)
+            if groups[0].numel():
+                self._reduce(groups[0], 0)
+        run(phase=4)
+        self.side.wait_stream(main)
+        with torch.cuda.stream(self.side):
+            if groups[1].numel():
+                self._reduce(groups[1], 1)
         run(phase=8)
         if groups[2].numel():
             self._reduce(groups[2], 2)

@@ -165,7 +165,7 @@ class DecoderTrainStep:
             F_.attn_train_fused(d, self._params, self._feat, self._gt, self._grads, self._ws, dfeat=self.dfeat,
                                 loss_out=self._loss, alphas_out=self._alphas, drop_mask=mask,
                                 ce_denominator=self.ce_denominator, phase=phase)
-        elif phase in (2, 4, 8, 32):
+        elif phase in (2, 4, 8, 32, 64, 128):
             return                               # plain LSTM: one call does the whole step (phase 1 / 16)
         else:
             P = self.llm._struct(self._params)
@@ -174,7 +174,7 @@ class DecoderTrainStep:
                                 drop_mask=mask, ce_denominator=self.ce_denominator)
 
     # phases whose saved state a warm-up run of `phase` consumes (gates -> dgates in place, accumulations): re-run after it
-    _PREREQ = {2: (1,), 4: (1,), 8: (1, 4), 32: (16,)}
+    _PREREQ = {2: (1,), 4: (1,), 8: (1, 4), 32: (16,), 128: (16,), 64: ()}
 
     def run_resident(self, phase=3):
         """One step on the inputs already staged in the static device buffers (bench: inputs resident in HBM).

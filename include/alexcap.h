@@ -139,7 +139,13 @@ ALEXCAP_API int alexcap_attn_train_fused(const alexcap_dims* dims, const alexcap
  * (all remaining gradients), so that the second-largest gradient group can be exchanged while phase 8 runs.
  * Phase 1 may itself be run as phase 16 (targets + the teacher-forced forward recurrence) followed by phase 32 (vocabulary
  * projection, loss, vocabulary backward, regulariser): `ce_denominator` is only read by phase 32, so a data-parallel caller
- * can all-reduce N_valid (alexcap_count_valid_targets) on a side stream while phase 16 runs. */
+ * can all-reduce N_valid (alexcap_count_valid_targets) on a side stream while phase 16 runs.
+ * Phase 32 may itself be run as phase 128 (everything of 32 except d deep_output.weight / .bias, which nothing later in the step
+ * reads) and phase 64 (those two gradients, restricted to the SMs the reverse-time loop leaves idle): 64 may be enqueued on a
+ * SECOND stream, ordered after 128, concurrently with phase 4 on the first -- a data-parallel caller runs 64 and the all-reduce of
+ * deep_output.* on its side stream underneath the reverse loop.  Where the split does not apply (exact-fp32 engines, a batch that
+ * fills the GPU) 128 does all of 32 and 64 does nothing.  The one-call forms (phase 3, alexcap_attn_train_fused) fork the
+ * same work onto a library-owned stream and join it before returning. */
 ALEXCAP_API int alexcap_attn_train_phase(const alexcap_dims* dims, const alexcap_attn_params* params,
                              const float* feat, const int32_t* gt,
                              const alexcap_attn_params* grads, float* dfeat,

@@ -116,6 +116,44 @@ def test_phases_16_32_4_8_interleaved_on_two_workspaces_equal_fused():
         assert rel_err(st._flat_grads, g0) < 1e-6 and rel_err(st.dfeat, df0) < 1e-6
 
 
+@pytest.mark.parametrize('two_streams', [False, True])
+def test_phase_128_plus_64_equals_phase_32(two_streams):
+    """Phase 32 split into 128 (everything but d deep_output.*) + 64 (those two gradients on the idle SMs), 64 either in
+    line or on a second stream beside phase 4 as GradAllReducer.step_overlapped runs it: same loss and gradients as the
+    fused step."""
+    from imagecaptioning_b200.model import DecoderTrainStep
+    cfg = dict(B=40, L=49, D=256, H=192, E=96, V=2100, T=9)       # large enough for the fused-CE / pre-split GEMM path
+    p = random_attn_params(cfg, seed=8)
+    feat, gt = synth_inputs(cfg['B'], cfg['L'], cfg['D'], cfg['V'], cfg['T'], seed=5)
+    dec = build_decoder(cfg, p)
+    dec.train()
+    st = DecoderTrainStep(dec, need_dfeat=True)
+    st.stage(feat.to(DEV), gt.to(DEV))
+    st.run_resident(3)
+    torch.cuda.synchronize()
+    g0, l0, df0 = st._flat_grads.clone(), st._loss.clone(), st.dfeat.clone()
+    st._flat_grads.zero_()
+    st.run_resident(16)
+    st.run_resident(128)
+    if two_streams:
+        side, main = torch.cuda.Stream(), torch.cuda.current_stream()
+        side.wait_stream(main)
+        with torch.cuda.stream(side):
+            st.run_resident(64)
+        st.run_resident(4)
+        st.run_resident(8)
+        main.wait_stream(side)
+    else:
+        st.run_resident(64)
+        st.run_resident(4)
+        st.run_resident(8)
+    torch.cuda.synchronize()
+    assert rel_err(st._loss, l0) < 1e-6
+    assert rel_err(st._flat_grads, g0) < 1e-6 and rel_err(st.dfeat, df0) < 1e-6
+    # the deep_output gradients really were produced (the buffer was zeroed before the phased run)
+    assert float(st.grad_groups()[0].abs().max()) > 0
+
+
 def test_count_valid_targets_and_fractional_denominator():
     from imagecaptioning_b200 import functional as F_
     from imagecaptioning_b200.model import DecoderTrainStep
