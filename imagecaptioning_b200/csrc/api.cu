@@ -129,6 +129,16 @@ AttnWs attn_layout(const alexcap_dims* d, void* base, bool with_logits) {
 // ALEXCAP_BF16 storage of the attention streams (BASELINE.json configs[2] / [4]): the per-step attention kernels read Ws and
 // feat 2 * S times per training step; in bf16 mode they read bf16 copies (half the bytes per launch).  feat's copy is the one
 // the hoisted Ws GEMM made of its A operand; Ws gets one split pass per training step.  NULL pointers = stream fp32.
+// bf16 configurations (engine 2) whose per-step GEMMs run on the pre-split engine (M = B >= 256): the kernels that PRODUCE the
+// per-step GEMM operands -- attention (gctx, dq, dbpre) and the LSTM pointwise kernels (h, d gates) -- also write them as
+// bf16 into a mirror of XH / DGQ in the operand arena, so none of the 4 split passes per time step is needed (they sat on
+// the serial chain: 8.6 % of the cfg3 step) and the post-loop dW GEMMs find their operands ready as well.
+// ALEXCAP_BF16_MIRROR=0 disables (A/B timing).
+static bool bf16_mirror_ok(int B, int D, int H) {
+  static const bool off = [] { const char* v = getenv("ALEXCAP_BF16_MIRROR"); return v && v[0] == '0'; }();
+  return !off && gemm_engine() == 2 && split_arena() && attn_engine() == 1 && attn_stream_supported(D, H) && !(D & 7) && !(H & 7) &&
+         gemm_ps_wanted(B, H + D, H) && gemm_ps_wanted(B, 4 * H, D + H);
+}
 struct AttnRows { const float* Ws; const float* feat; bool bf16; };
 // The streaming attention kernels take the hoisted Ws = W(features) in exponential form (ACT_EXP2C, common.cuh): one MUFU op
 // per score element instead of two in the forward, backward and dWs kernels.  Engine 0 (direct-load kernels) keeps raw Ws.
@@ -206,6 +216,11 @@ int attn_fwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
     // node in front of every GEMM (which would also cut the programmatic-dependent-launch chain of the time loop)
     API_CK(cudaMemsetAsync(w.QB, 0, sizeof(float) * (size_t)S * B * HD, st));
     const AttnRows rows = attn_rows(d, feat, w, st);
+    uint16_t *xhb = nullptr, *xhb_lo = nullptr;
+    int64_t xld = 0;
+    const bool mirror = !cell_fused && (rows.bf16 || ws_exp) && bf16_mirror_ok(B, D, H) &&
+                        split_arena_reserve_mirror(split_arena(), w.XH, (S + 1) * B, (int)DH, DH, false, &xhb, &xhb_lo, &xld);
+    if (mirror) API_CK(split_arena_fill_view(st, split_arena(), w.XH + D, B, H, DH));     // h_0 (written by the init GEMM)
     for (int t = 0; t < S; ++t) {                                            // AttentionLanguageModule.py:72
       float* xh = w.XH + (int64_t)t * B * DH;
       float* qb = w.QB + (int64_t)t * B * HD;
@@ -216,7 +231,7 @@ int attn_fwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
       if (rows.bf16 || ws_exp)
         API_CK(attn_step_fwd_stream(st, B, L, D, H, rows.Ws, rows.feat, qb, HD, qb + H, HD, P->att_v_w, w.ALPHA + (int64_t)t * L,
                                     (int64_t)S * L, w.CTX + (int64_t)t * B * D, w.BETA + (int64_t)t * B * D, xh, DH, 1, rows.bf16,
-                                    ws_exp, true));
+                                    ws_exp, true, mirror ? xhb + (int64_t)t * B * xld : nullptr, xld));
       else
         API_CK(attn_step_fwd(st, B, L, D, H, w.Ws, feat, qb, HD, qb + H, HD, P->att_v_w, w.ALPHA + (int64_t)t * L,
                              (int64_t)S * L, w.CTX + (int64_t)t * B * D, w.BETA + (int64_t)t * B * D, xh, DH));
@@ -228,7 +243,7 @@ int attn_fwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
         API_CK(gemm_tc_lstm_f32(st, B, H + D, H, la, w.Wub, H, qb + (int64_t)B * HD, HD, w.bub, gemm_engine() == 2 ? 1 : 2));
       } else {
         API_CK(lstm_pointwise_fwd(st, B, H, gp, GL, c_t, c_t + (int64_t)B * H, h_next, DH, nullptr, 0,
-                                  cell_fused ? g : nullptr, W5));
+                                  cell_fused ? g : nullptr, W5, mirror ? xhb + (int64_t)(t + 1) * B * xld + D : nullptr, xld));
       }
     }
   }
@@ -327,6 +342,10 @@ int attn_bwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
 
   const AttnRows rows = attn_rows(d, feat, w, st);      // (arena hits: the copies were made by the forward phase)
   const bool ws_exp = attn_ws_exp(D, H);                // (the same decision the forward phase took for the Ws GEMM)
+  uint16_t *gb = nullptr, *gb_lo = nullptr;
+  int64_t gld = 0;
+  const bool mirror = (rows.bf16 || ws_exp) && bf16_mirror_ok(B, D, H) &&
+                      split_arena_reserve_mirror(split_arena(), w.DGQ, S * B, (int)W5, W5, false, &gb, &gb_lo, &gld);
   for (int t = S - 1; t >= 0; --t) {
     float* dgc = w.dgctx + (int64_t)t * B * D;
     float* dhn = w.dh_next + (int64_t)t * B * H;                  // dh_{t-1}, consumed by reverse step t-1
@@ -334,7 +353,8 @@ int attn_bwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
     const float* qb = w.QB + (int64_t)t * B * HD;
     API_CK(lstm_pointwise_bwd(st, B, H, g, W5, w.Call + (int64_t)(t + 1) * B * H, w.Call + (int64_t)t * B * H,
                               w.dHout + (int64_t)t * B * H, H, w.MASK ? w.MASK + (int64_t)t * B * H : nullptr,
-                              (t == S - 1) ? nullptr : dhn + (int64_t)B * H, H, w.dc));
+                              (t == S - 1) ? nullptr : dhn + (int64_t)B * H, H, w.dc,
+                              mirror ? gb + (int64_t)t * B * gld : nullptr, gld));
     // d gctx = dgates W_ih[:, E:]
     { WeightBScope wb; API_CK(gemm_f32(st, false, false, B, D, 4 * H, 1.f, g, W5, P->lstm_w_ih + E, E + D, dgc, D, nullptr, nullptr,
                     true, ACT_NONE)); }
@@ -343,7 +363,9 @@ int attn_bwd_core(const alexcap_dims* d, const alexcap_attn_params* P, const flo
                                   w.CTX + (int64_t)t * B * D, w.BETA + (int64_t)t * B * D, dgc, D,
                                   dalphas ? dalphas + (int64_t)t * L : nullptr, (int64_t)S * L, reg_r,
                                   g + 4 * H, W5, g + 5 * H, W5, w.DE + (int64_t)t * L, (int64_t)S * L, w.dwv_part,
-                                  need_dfeat ? dfeat : nullptr, rows.bf16, ws_exp, true));
+                                  need_dfeat ? dfeat : nullptr, rows.bf16, ws_exp, true,
+                                  mirror ? gb + (int64_t)t * B * gld + 4 * H : nullptr,
+                                  mirror ? gb + (int64_t)t * B * gld + 5 * H : nullptr, gld));
     else
       API_CK(attn_step_bwd(st, B, L, D, H, w.Ws, feat, qb, HD, P->att_v_w, w.ALPHA + (int64_t)t * L, (int64_t)S * L,
                            w.CTX + (int64_t)t * B * D, w.BETA + (int64_t)t * B * D, dgc, D,

@@ -240,7 +240,7 @@ static size_t fwd_fixed_smem(int D, int seg_pad, int maxseg) {
 cudaError_t attn_step_fwd_stream(cudaStream_t st, int B, int L, int D, int H, const float* Ws, const float* feat,
                                  const float* q, int64_t q_ld, const float* bpre, int64_t bpre_ld, const float* wv,
                                  float* alpha, int64_t alpha_ld, float* ctx, float* beta, float* gctx, int64_t gctx_ld,
-                                 int rows_per_image, bool rows_bf16, bool ws_exp, bool static_ready) {
+                                 int rows_per_image, bool rows_bf16, bool ws_exp, bool static_ready, uint16_t* gctx_b16, int64_t gb_ld) {
   if (!attn_stream_supported(D, H) || (q_ld & 3) || (bpre_ld & 3) || (gctx_ld & 3)) return cudaErrorInvalidValue;
   if (rows_bf16 && ((D & 7) || (H & 7))) return cudaErrorInvalidValue;      // 16-byte bulk copies of bf16 rows
   if (B <= 0 || L <= 0) return cudaSuccess;
@@ -259,6 +259,10 @@ cudaError_t attn_step_fwd_stream(cudaStream_t st, int B, int L, int D, int H, co
   a.ws_exp = ws_exp ? 1 : 0;
   a.pdl = !static_ready ? 1 : (prefetch_before_wait() ? 2 : (header_split() ? 3 : 1));
   a.prof = prof_ptr();
+  if (gctx_b16) {
+    if ((gb_ld & 3) || (reinterpret_cast<uintptr_t>(gctx_b16) & 7)) return cudaErrorInvalidValue;
+    a.gctx_hi = gctx_b16; a.gctx_lo = nullptr; a.gb_ld = gb_ld;
+  }
   const size_t smem = (size_t)g.NST * g.stage_floats * 4 + fwd_fixed_smem(D, seg_pad, g.maxseg);
   const int nj = ceil_div(H, 128);
 #define LAUNCH_FWD_K(NJ, FULL, BF, EW)                                                      \
@@ -297,7 +301,8 @@ cudaError_t attn_step_bwd_stream(cudaStream_t st, int B, int L, int D, int H, co
                                  const float* ctx, const float* beta, const float* dgctx, int64_t dgctx_ld,
                                  const float* dalpha_ext, int64_t ext_ld, const float* reg_r,
                                  float* dq, int64_t dq_ld, float* dbpre, int64_t dbpre_ld, float* de, int64_t de_ld,
-                                 float* dwv_part, float* dfeat, bool rows_bf16, bool ws_exp, bool static_ready) {
+                                 float* dwv_part, float* dfeat, bool rows_bf16, bool ws_exp, bool static_ready,
+                                 uint16_t* dq_b16, uint16_t* dbpre_b16, int64_t db_ld) {
   if (!attn_stream_supported(D, H) || (q_ld & 3) || (dgctx_ld & 3) || (dq_ld & 3) || (dbpre_ld & 3))
     return cudaErrorInvalidValue;
   if (rows_bf16 && ((D & 7) || (H & 7))) return cudaErrorInvalidValue;
@@ -319,6 +324,11 @@ cudaError_t attn_step_bwd_stream(cudaStream_t st, int B, int L, int D, int H, co
   a.ws_exp = ws_exp ? 1 : 0;
   a.pdl = !static_ready ? 1 : (prefetch_before_wait() ? 2 : (header_split() ? 3 : 1));
   a.prof = prof_ptr() ? prof_ptr() + 8 : nullptr;
+  if (dq_b16 || dbpre_b16) {
+    if (!dq_b16 || !dbpre_b16 || (db_ld & 3) || (reinterpret_cast<uintptr_t>(dq_b16) & 7) || (reinterpret_cast<uintptr_t>(dbpre_b16) & 7))
+      return cudaErrorInvalidValue;
+    a.dq_b16 = dq_b16; a.dbpre_b16 = dbpre_b16; a.db_ld = db_ld;
+  }
 #define LAUNCH_BWD_K(AW, BF, EW)                                                            \
   do {                                                                                      \
     ACK(set_smem(attn_bwd_stream_kernel<AW, BF, EW>, smem));                                \

@@ -46,6 +46,14 @@ __device__ __forceinline__ void split_bf16x4(const float4& v, uint2& hi, uint2& 
   asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(lo.y) : "f"(r3), "f"(r2));
 }
 
+// fp32 x4 -> bf16 (round to nearest), packed pairs: what ps::split_bf16_kernel would write as the `hi` copy
+__device__ __forceinline__ uint2 to_bf16x4(const float4& v) {
+  uint2 o;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(o.x) : "f"(v.y), "f"(v.x));
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(o.y) : "f"(v.w), "f"(v.z));
+  return o;
+}
+
 // The ring protocol, shared by producer and consumers.  A cursor (stage index, use parity) walks the pieces in
 // order; it is advanced incrementally (no integer division per piece).
 struct Cursor {
@@ -382,7 +390,7 @@ __device__ __forceinline__ void attn_fwd_body(const SAttnFwdP& a, float* sm, con
               uint2 h2, l2;
               split_bf16x4(gc, h2, l2);
               reinterpret_cast<uint2*>(a.gctx_hi + (int64_t)b * a.gb_ld)[c2] = h2;
-              reinterpret_cast<uint2*>(a.gctx_lo + (int64_t)b * a.gb_ld)[c2] = l2;
+              if (a.gctx_lo) reinterpret_cast<uint2*>(a.gctx_lo + (int64_t)b * a.gb_ld)[c2] = l2;
             }
           } else {
             pctx[c2] = t;
@@ -455,8 +463,14 @@ __device__ __forceinline__ void attn_fwd_body(const SAttnFwdP& a, float* sm, con
         be.x = sigmoid_f(bp.x); be.y = sigmoid_f(bp.y); be.z = sigmoid_f(bp.z); be.w = sigmoid_f(bp.w);
         reinterpret_cast<float4*>(a.ctx + (int64_t)b * D)[c2] = o[ci];
         reinterpret_cast<float4*>(a.beta + (int64_t)b * D)[c2] = be;
-        reinterpret_cast<float4*>(a.gctx + (int64_t)b * a.gctx_ld)[c2] =
-            make_float4(be.x * o[ci].x, be.y * o[ci].y, be.z * o[ci].z, be.w * o[ci].w);
+        const float4 gc = make_float4(be.x * o[ci].x, be.y * o[ci].y, be.z * o[ci].z, be.w * o[ci].w);
+        reinterpret_cast<float4*>(a.gctx + (int64_t)b * a.gctx_ld)[c2] = gc;
+        if (a.gctx_hi) {
+          uint2 h2, l2;
+          split_bf16x4(gc, h2, l2);
+          reinterpret_cast<uint2*>(a.gctx_hi + (int64_t)b * a.gb_ld)[c2] = h2;
+          if (a.gctx_lo) reinterpret_cast<uint2*>(a.gctx_lo + (int64_t)b * a.gb_ld)[c2] = l2;
+        }
       }
     }
     if (tid == 0) a.counters[b] = 0;              // ready for the next launch
@@ -483,6 +497,7 @@ struct SAttnBwdP {
   int B, L, D, H, rp, RH, RD, NST, stage_floats, maxseg, seg_pad, rp_pad, slot_floats;
   float l2_frac;
   int bf16 = 0;       // Ws / feat point at bf16 rows (same shapes): selects the BF instantiation
+  uint16_t* dq_b16 = nullptr; uint16_t* dbpre_b16 = nullptr; int64_t db_ld = 0;   // optional bf16 mirrors of dq / dbpre
   int ws_exp = 0;     // Ws holds EXP2C(W(features)) (see r_of): selects the EW instantiation
   int pdl = 0;        // as SAttnFwdP::pdl (2: feat pieces are prefetched before the producer's griddepcontrol.wait)
   unsigned long long* prof = nullptr;
@@ -581,6 +596,7 @@ __device__ __forceinline__ void attn_bwd_body(const SAttnBwdP& a, float* sm, con
           db.x = dg.x * cx.x * be.x * (1.f - be.x); db.y = dg.y * cx.y * be.y * (1.f - be.y);
           db.z = dg.z * cx.z * be.z * (1.f - be.z); db.w = dg.w * cx.w * be.w * (1.f - be.w);
           reinterpret_cast<float4*>(a.dbpre + (int64_t)b * a.dbpre_ld)[c] = db;
+          if (a.dbpre_b16) reinterpret_cast<uint2*>(a.dbpre_b16 + (int64_t)b * a.db_ld)[c] = to_bf16x4(db);
         }
       }
     }
@@ -737,7 +753,9 @@ __device__ __forceinline__ void attn_bwd_body(const SAttnBwdP& a, float* sm, con
         }
       if (whole) {                                        // ref == dot: dq = w_v X1, dw_v += Y1
         const float4 v = __ldg(reinterpret_cast<const float4*>(a.wv) + f);
-        reinterpret_cast<float4*>(a.dq + (int64_t)b * a.dq_ld)[f] = make_float4(v.x * x1.x, v.y * x1.y, v.z * x1.z, v.w * x1.w);
+        const float4 dqv = make_float4(v.x * x1.x, v.y * x1.y, v.z * x1.z, v.w * x1.w);
+        reinterpret_cast<float4*>(a.dq + (int64_t)b * a.dq_ld)[f] = dqv;
+        if (a.dq_b16) reinterpret_cast<uint2*>(a.dq_b16 + (int64_t)b * a.db_ld)[f] = to_bf16x4(dqv);
         float4* out = reinterpret_cast<float4*>(a.dwv_part + (int64_t)b * H) + f;
         float4 o = *out;
         f4_add(o, y1);
@@ -793,7 +811,9 @@ __device__ __forceinline__ void attn_bwd_body(const SAttnBwdP& a, float* sm, con
         f4_add(t1, __ldcg(sl4 + 2 * H4 + tid)); f4_fma(t1, -ds, __ldcg(sl4 + 3 * H4 + tid));
       }
       const float4 v = __ldg(reinterpret_cast<const float4*>(a.wv) + tid);
-      reinterpret_cast<float4*>(a.dq + (int64_t)b * a.dq_ld)[tid] = make_float4(v.x * s1.x, v.y * s1.y, v.z * s1.z, v.w * s1.w);
+      const float4 dqv = make_float4(v.x * s1.x, v.y * s1.y, v.z * s1.z, v.w * s1.w);
+      reinterpret_cast<float4*>(a.dq + (int64_t)b * a.dq_ld)[tid] = dqv;
+      if (a.dq_b16) reinterpret_cast<uint2*>(a.dq_b16 + (int64_t)b * a.db_ld)[tid] = to_bf16x4(dqv);
       float4* out = reinterpret_cast<float4*>(a.dwv_part + (int64_t)b * H) + tid;
       float4 o = *out;
       f4_add(o, t1);

@@ -57,8 +57,8 @@ struct Params {
 // ------------------------------------------------------------------------------------------------ split pass
 // X [rows, cols] fp32 (row pitch ldx) -> hi (and lo) [rows, ldo] bf16, ldo = cols rounded up to 8; pad columns are zero.
 __global__ void __launch_bounds__(256) split_bf16_kernel(const float* __restrict__ X, int64_t ldx, int rows, int cols,
-                                                         uint16_t* __restrict__ hi, uint16_t* __restrict__ lo, int64_t ldo) {
-  const int groups = (int)(ldo >> 3);
+                                                         uint16_t* __restrict__ hi, uint16_t* __restrict__ lo, int64_t ldo,
+                                                         int groups) {      // groups: 8-column groups written per row (ldo / 8, or less for a sub-view)
   const int64_t total = (int64_t)rows * groups;
   const bool vec = ((ldx & 3) == 0) && ((reinterpret_cast<uintptr_t>(X) & 15) == 0);
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -753,6 +753,21 @@ static bool pair_wanted(int M, int N, int K, int nprod) {
 struct Split { uint16_t* hi; uint16_t* lo; int64_t ld; };
 
 // hi/lo bf16 copy of the fp32 matrix X [rows, cols] (pitch ld) out of the arena: cached per source for the arena's lifetime
+// X [rows, cols] (pitch ld) as a sub-block of a mirrored matrix: same pitch, inside its extents, column offset % 8 == 0
+static bool find_view(const SplitArena* a, const float* X, int rows, int cols, int64_t ld, bool with_lo, Split* out) {
+  for (int i = 0; i < a->n; ++i) {
+    const SplitArena::Entry& e = a->e[i];
+    if (!e.mirror || e.ld != ld || X < e.src || (with_lo && !e.lo)) continue;
+    const int64_t off = X - e.src, r0 = off / ld, c0 = off % ld;
+    if (r0 + rows > e.rows || c0 + cols > e.cols || (c0 & 7)) continue;
+    out->hi = e.hi + r0 * e.ldo + c0;
+    out->lo = e.lo ? e.lo + r0 * e.ldo + c0 : nullptr;
+    out->ld = e.ldo;
+    return true;
+  }
+  return false;
+}
+
 static cudaError_t get_split(cudaStream_t st, SplitArena* a, const float* X, int rows, int cols, int64_t ld, bool with_lo,
                              Split* out) {
   for (int i = 0; i < a->n; ++i) {
@@ -762,12 +777,13 @@ static cudaError_t get_split(cudaStream_t st, SplitArena* a, const float* X, int
       return cudaSuccess;
     }
   }
+  if (find_view(a, X, rows, cols, ld, with_lo, out)) return cudaSuccess;      // a sub-block of a producer-written mirror
   const int64_t ldo = ((int64_t)cols + 7) & ~int64_t(7);
   const size_t one = (((size_t)rows * ldo * 2) + 1023) & ~size_t(1023);
   const size_t need = one * (with_lo ? 2 : 1);
   if (!a->base || a->used + need > a->bytes || a->n >= SplitArena::MAX_ENTRIES) return cudaErrorMemoryAllocation;
   SplitArena::Entry& e = a->e[a->n];
-  e.src = X; e.rows = rows; e.cols = cols; e.ld = ld; e.ldo = ldo; e.produced = false;
+  e.src = X; e.rows = rows; e.cols = cols; e.ld = ld; e.ldo = ldo; e.produced = false; e.mirror = false;
   e.hi = reinterpret_cast<uint16_t*>(a->base + a->used);
   e.lo = with_lo ? reinterpret_cast<uint16_t*>(a->base + a->used + one) : nullptr;
   a->used += need;
@@ -778,7 +794,7 @@ static cudaError_t get_split(cudaStream_t st, SplitArena* a, const float* X, int
   if (blocks > 148 * 16) blocks = 148 * 16;
   if (blocks < 1) blocks = 1;
   ALEXCAP_NOTE_LAUNCH();
-  split_bf16_kernel<<<blocks, 256, 0, st>>>(X, ld, rows, cols, e.hi, e.lo, ldo);
+  split_bf16_kernel<<<blocks, 256, 0, st>>>(X, ld, rows, cols, e.hi, e.lo, ldo, (int)(ldo >> 3));
   ACK(cudaGetLastError());
   out->hi = e.hi; out->lo = e.lo; out->ld = ldo;
   return cudaSuccess;
@@ -806,7 +822,7 @@ bool split_arena_reserve(SplitArena* a, const float* key, int rows, int cols, in
   const size_t need = one * (with_lo ? 2 : 1);
   if (a->used + need > a->bytes) return false;
   SplitArena::Entry& e = a->e[a->n];
-  e.src = key; e.rows = rows; e.cols = cols; e.ld = ld; e.ldo = ldo; e.produced = true;
+  e.src = key; e.rows = rows; e.cols = cols; e.ld = ld; e.ldo = ldo; e.produced = true; e.mirror = false;
   e.hi = reinterpret_cast<uint16_t*>(a->base + a->used);
   e.lo = with_lo ? reinterpret_cast<uint16_t*>(a->base + a->used + one) : nullptr;
   a->used += need;
@@ -814,6 +830,26 @@ bool split_arena_reserve(SplitArena* a, const float* key, int rows, int cols, in
   a->n++;
   *hi = e.hi; *lo = e.lo; *ldo_out = ldo;
   return true;
+}
+
+bool split_arena_reserve_mirror(SplitArena* a, const float* src, int rows, int cols, int64_t ld, bool with_lo, uint16_t** hi,
+                                uint16_t** lo, int64_t* ldo_out) {
+  if (!split_arena_reserve(a, src, rows, cols, ld, with_lo, hi, lo, ldo_out)) return false;
+  a->e[a->n - 1].mirror = true;
+  return true;
+}
+
+cudaError_t split_arena_fill_view(cudaStream_t st, SplitArena* a, const float* X, int rows, int cols, int64_t ld) {
+  ps::Split sp;
+  if (!a || !ps::find_view(a, X, rows, cols, ld, false, &sp)) return cudaErrorInvalidValue;
+  if (cols & 7) return cudaErrorInvalidValue;           // (the split kernel zero-pads to 8 columns: must not spill into the neighbours)
+  const int64_t total = (int64_t)rows * (cols >> 3);
+  int blocks = (int)((total + 255) / 256);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  if (blocks < 1) blocks = 1;
+  ALEXCAP_NOTE_LAUNCH();
+  ps::split_bf16_kernel<<<blocks, 256, 0, st>>>(X, ld, rows, cols, sp.hi, sp.lo, sp.ld, cols >> 3);
+  return cudaGetLastError();
 }
 
 // The copies a producer registered under `key` (split_arena_reserve) earlier in the step; false if there are none.
@@ -842,7 +878,7 @@ cudaError_t split_arena_get_hi(cudaStream_t st, SplitArena* a, const float* X, i
 bool split_arena_is_produced(const SplitArena* a, const float* p) {
   if (!a) return false;
   for (int i = 0; i < a->n; ++i)
-    if (a->e[i].src == p && a->e[i].produced) return true;
+    if (a->e[i].src == p && a->e[i].produced && !a->e[i].mirror) return true;      // (a mirror has its fp32 matrix)
   return false;
 }
 

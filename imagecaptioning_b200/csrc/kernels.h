@@ -36,7 +36,9 @@ cudaError_t gemm_tc_lstm_f32(cudaStream_t st, int M, int N, int H, const LstmA& 
 // Returns cudaErrorMemoryAllocation when the arena cannot hold the copies (the caller falls back to gemm_tc_f32).
 struct SplitArena {
   static constexpr int MAX_ENTRIES = 256;
-  struct Entry { const float* src; int rows, cols; int64_t ld, ldo; uint16_t* hi; uint16_t* lo; size_t end; bool produced; };
+  struct Entry { const float* src; int rows, cols; int64_t ld, ldo; uint16_t* hi; uint16_t* lo; size_t end; bool produced; bool mirror; };
+  // produced: the bf16 copies are written by the matrix's producer kernel, not by a split pass.  mirror: ... beside the fp32
+  // matrix, which exists as well (a GEMM operand that is a row / column sub-block of `src` uses the matching sub-view).
   uint8_t* base = nullptr; size_t bytes = 0, used = 0;
   Entry e[MAX_ENTRIES]; int n = 0;
 };
@@ -50,6 +52,14 @@ cudaError_t split_arena_get_hi(cudaStream_t st, SplitArena* a, const float* X, i
 bool split_arena_reserve(SplitArena* a, const float* key, int rows, int cols, int64_t ld, bool with_lo, uint16_t** hi,
                          uint16_t** lo, int64_t* ldo_out);
 bool split_arena_find(const SplitArena* a, const float* key, uint16_t** hi, uint16_t** lo, int64_t* ldo_out);
+// bf16 (+ lo) MIRROR of the fp32 matrix `src` [rows, cols] (pitch ld): the kernels that write `src` write the same values into
+// the mirror (row pitch *ldo_out elements), so that no split pass is needed when `src` -- or any sub-block of it with a column
+// offset that is a multiple of 8 -- is a GEMM operand later in the step.  The caller must make sure EVERY element a GEMM will
+// read has been written by a producer (or by split_arena_fill_view).
+bool split_arena_reserve_mirror(SplitArena* a, const float* src, int rows, int cols, int64_t ld, bool with_lo, uint16_t** hi,
+                                uint16_t** lo, int64_t* ldo_out);
+// split pass over the sub-block X [rows, cols] (pitch ld) of a mirrored matrix into the matching part of its mirror
+cudaError_t split_arena_fill_view(cudaStream_t st, SplitArena* a, const float* X, int rows, int cols, int64_t ld);
 cudaError_t gemm_ps_f32(cudaStream_t st, bool ta, bool tb, int M, int N, int K, float alpha,
                         const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
                         const float* bias, const float* bias2, bool accumulate, int act, int force_splits, int nprod,
@@ -91,7 +101,8 @@ int& attn_engine();
 cudaError_t attn_step_fwd_stream(cudaStream_t st, int B, int L, int D, int H, const float* Ws, const float* feat,
                                  const float* q, int64_t q_ld, const float* bpre, int64_t bpre_ld, const float* wv,
                                  float* alpha, int64_t alpha_ld, float* ctx, float* beta, float* gctx, int64_t gctx_ld,
-                                 int rows_per_image, bool rows_bf16 = false, bool ws_exp = false, bool static_ready = false);
+                                 int rows_per_image, bool rows_bf16 = false, bool ws_exp = false, bool static_ready = false,
+                                 uint16_t* gctx_b16 = nullptr, int64_t gb_ld = 0);   // gctx_b16: bf16 mirror of gctx
 // static_ready: Ws / feat were complete before the kernel that precedes this launch in the stream started (true inside the
 // time loops): the producer may fetch row pieces before griddepcontrol.wait; only q / bpre (dgctx) wait for the predecessor
 // ws_exp: Ws holds EXP2C(W(features)) (GEMM activation ACT_EXP2C; common.cuh) -- one MUFU op per score element instead of two
@@ -101,7 +112,8 @@ cudaError_t attn_step_bwd_stream(cudaStream_t st, int B, int L, int D, int H, co
                                  const float* ctx, const float* beta, const float* dgctx, int64_t dgctx_ld,
                                  const float* dalpha_ext, int64_t ext_ld, const float* reg_r,
                                  float* dq, int64_t dq_ld, float* dbpre, int64_t dbpre_ld, float* de, int64_t de_ld,
-                                 float* dwv_part, float* dfeat, bool rows_bf16 = false, bool ws_exp = false, bool static_ready = false);
+                                 float* dwv_part, float* dfeat, bool rows_bf16 = false, bool ws_exp = false, bool static_ready = false,
+                                 uint16_t* dq_b16 = nullptr, uint16_t* dbpre_b16 = nullptr, int64_t db_ld = 0);   // bf16 mirrors of dq / dbpre
 // dWs[b,l,h] = wv[h] * sum_t de[b,t,l] * (1 - tanh^2(Ws[b,l,h] + q[t,b,h]));  q: [S][B] rows of stride q_ld,
 // de: [B][S][L].
 cudaError_t attn_dws(cudaStream_t st, int B, int L, int H, int S, const float* Ws, const float* q, int64_t q_ld,
@@ -130,12 +142,13 @@ int time_loop_profile_read(unsigned long long* host_out, int max_entries);
 // h written to h_out (row stride h_ld) and optionally h_out2 (row stride h2_ld).
 cudaError_t lstm_pointwise_fwd(cudaStream_t st, int B, int H, float* gates, int64_t g_ld, const float* c_prev,
                                float* c_out, float* h_out, int64_t h_ld, float* h_out2, int64_t h2_ld, float* acts_out = nullptr,
-                               int64_t acts_ld = 0);   // acts_out: write the gate activations there instead of over `gates`
+                               int64_t acts_ld = 0, uint16_t* h_b16 = nullptr, int64_t hb_ld = 0);
+// acts_out: write the gate activations there instead of over `gates`; h_b16: bf16 mirror of h_out (row pitch hb_ld elements)
 // gates hold activations (i,f,g,o) -> overwritten with d(pre-activations).  dh = dh_a + dh_b (either may be NULL;
 // dh_a scaled by mask_a if given).  dc_io [B,H]: in = dc from step t+1, out = dc for step t-1.
 cudaError_t lstm_pointwise_bwd(cudaStream_t st, int B, int H, float* gates, int64_t g_ld, const float* c_t,
                                const float* c_prev, const float* dh_a, int64_t dha_ld, const float* mask_a,
-                               const float* dh_b, int64_t dhb_ld, float* dc_io);
+                               const float* dh_b, int64_t dhb_ld, float* dc_io, uint16_t* g_b16 = nullptr, int64_t gb_ld = 0);
 
 // ---- loss (ce_loss.cu)
 cudaError_t count_valid(cudaStream_t st, const int32_t* tgt, int N, int ignore_index, float* n_valid_out);

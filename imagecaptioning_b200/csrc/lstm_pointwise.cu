@@ -3,6 +3,8 @@
 // The gate pre-activations come from the GEMMs; these kernels are elementwise and negligible in bytes -- but they sit on the
 // serial chain of every time step, so sigmoid / tanh are the two-MUFU forms of common.cuh (~2e-7 absolute error) rather than
 // libm's expf / tanhf / IEEE division (4 cells per thread of those are ~450 dependent instructions).
+#include <cuda_bf16.h>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -12,7 +14,8 @@ __global__ void __launch_bounds__(256) lstm_fwd_kernel(int B, int H, float* __re
                                                        const float* __restrict__ c_prev, float* __restrict__ c_out,
                                                        float* __restrict__ h_out, int64_t h_ld,
                                                        float* __restrict__ h_out2, int64_t h2_ld,
-                                                       float* __restrict__ acts_out, int64_t acts_ld) {
+                                                       float* __restrict__ acts_out, int64_t acts_ld,
+                                                       uint16_t* __restrict__ h_b16, int64_t hb_ld) {
   const int H4 = H >> 2;
   const int64_t n = (int64_t)B * H4;
   pdl_trigger();
@@ -33,18 +36,24 @@ __global__ void __launch_bounds__(256) lstm_fwd_kernel(int B, int H, float* __re
     reinterpret_cast<float4*>(c_out + (int64_t)b * H)[c] = cn;
     reinterpret_cast<float4*>(h_out + (int64_t)b * h_ld)[c] = hn;
     if (h_out2) reinterpret_cast<float4*>(h_out2 + (int64_t)b * h2_ld)[c] = hn;
+    if (h_b16) {                 // bf16 mirror of h (operand copy of the next GEMMs: no split pass)
+      uint2 o;
+      asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(o.x) : "f"(hn.y), "f"(hn.x));
+      asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(o.y) : "f"(hn.w), "f"(hn.z));
+      reinterpret_cast<uint2*>(h_b16 + (int64_t)b * hb_ld)[c] = o;
+    }
   }
 }
 
 cudaError_t lstm_pointwise_fwd(cudaStream_t st, int B, int H, float* gates, int64_t g_ld, const float* c_prev,
                                float* c_out, float* h_out, int64_t h_ld, float* h_out2, int64_t h2_ld, float* acts_out,
-                               int64_t acts_ld) {
+                               int64_t acts_ld, uint16_t* h_b16, int64_t hb_ld) {
   if ((H & 3) || (g_ld & 3) || (h_ld & 3) || (h_out2 && (h2_ld & 3)) || (acts_out && (acts_ld & 3))) return cudaErrorInvalidValue;
   const int64_t n = (int64_t)B * (H / 4);
   const int blocks = (int)((n + 255) / 256);
   ALEXCAP_NOTE_LAUNCH();
   return launch_pdl(lstm_fwd_kernel, dim3(blocks), dim3(256), 0, st, B, H, gates, g_ld, c_prev, c_out, h_out, h_ld, h_out2, h2_ld,
-                    acts_out, acts_ld);
+                    acts_out, acts_ld, h_b16, hb_ld);
 }
 
 __global__ void __launch_bounds__(256) lstm_bwd_kernel(int B, int H, float* __restrict__ gates, int64_t g_ld,
@@ -52,7 +61,7 @@ __global__ void __launch_bounds__(256) lstm_bwd_kernel(int B, int H, float* __re
                                                        const float* __restrict__ dh_a, int64_t dha_ld,
                                                        const float* __restrict__ mask_a,
                                                        const float* __restrict__ dh_b, int64_t dhb_ld,
-                                                       float* __restrict__ dc_io) {
+                                                       float* __restrict__ dc_io, uint16_t* __restrict__ g_b16, int64_t gb_ld) {
   const int64_t n = (int64_t)B * H;
   pdl_trigger();
   pdl_wait();
@@ -75,16 +84,22 @@ __global__ void __launch_bounds__(256) lstm_bwd_kernel(int B, int H, float* __re
     const float d_g = dc * gi * (1.f - gg * gg);
     dc_io[(int64_t)b * H + h] = dc * gf;
     g[h] = d_i; g[H + h] = d_f; g[2 * H + h] = d_g; g[3 * H + h] = d_o;
+    if (g_b16) {                 // bf16 mirror of d gates
+      uint16_t* gb = g_b16 + (int64_t)b * gb_ld;
+      gb[h] = __bfloat16_as_ushort(__float2bfloat16_rn(d_i)); gb[H + h] = __bfloat16_as_ushort(__float2bfloat16_rn(d_f));
+      gb[2 * H + h] = __bfloat16_as_ushort(__float2bfloat16_rn(d_g)); gb[3 * H + h] = __bfloat16_as_ushort(__float2bfloat16_rn(d_o));
+    }
   }
 }
 
 cudaError_t lstm_pointwise_bwd(cudaStream_t st, int B, int H, float* gates, int64_t g_ld, const float* c_t,
                                const float* c_prev, const float* dh_a, int64_t dha_ld, const float* mask_a,
-                               const float* dh_b, int64_t dhb_ld, float* dc_io) {
+                               const float* dh_b, int64_t dhb_ld, float* dc_io, uint16_t* g_b16, int64_t gb_ld) {
   const int64_t n = (int64_t)B * H;
   const int blocks = (int)((n + 255) / 256);
   ALEXCAP_NOTE_LAUNCH();
-  return launch_pdl(lstm_bwd_kernel, dim3(blocks), dim3(256), 0, st, B, H, gates, g_ld, c_t, c_prev, dh_a, dha_ld, mask_a, dh_b, dhb_ld, dc_io);
+  return launch_pdl(lstm_bwd_kernel, dim3(blocks), dim3(256), 0, st, B, H, gates, g_ld, c_t, c_prev, dh_a, dha_ld, mask_a, dh_b, dhb_ld, dc_io,
+                    g_b16, gb_ld);
 }
 
 }  // namespace alexcap

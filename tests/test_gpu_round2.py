@@ -344,3 +344,26 @@ def test_lstm_cell_fused_into_next_query_gemm_vs_oracle():
         assert a['loss_rel'] < TOL and a['grad_rel'] < TOL and a['dfeat_rel'] < TOL, a
         if not a['graph']:
             assert a['launches'] == b['launches'] - (a['S'] - 1), (a, b)       # one launch fewer per step but the last
+
+
+def test_producer_written_bf16_operand_mirrors_equal_split_passes(tmp_path):
+    """bf16 mode, per-step GEMMs on the pre-split engine: the attention and LSTM pointwise kernels write their outputs as bf16
+    into mirrors of XH / DGQ as well, and the GEMMs read sub-views of those instead of running a split pass per operand per
+    time step.  Same roundings, so the step equals the split-pass step to bf16-mode run-to-run noise, with 4 launches fewer per
+    time step (ALEXCAP_BF16_MIRROR is read once per process: subprocesses)."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    res = {}
+    for tag, val in (('on', '1'), ('off', '0')):
+        out = str(tmp_path / f'mirror_{tag}.pt')
+        r = subprocess.run([sys.executable, os.path.join(root, 'tests', 'mirror_worker.py'), out],
+                           env=dict(os.environ, ALEXCAP_BF16_MIRROR=val), capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+        res[tag] = torch.load(out)
+    on, off = res['on'], res['off']
+    # (bf16 mode: a 1e-7 accumulation-order difference in an fp32 intermediate can flip the bf16 rounding of the operand made
+    #  from it, so two runs of the SAME code agree to ~1e-3, not to fp32 round-off)
+    assert abs(on['loss'] - off['loss']) < 1e-4 * abs(off['loss'])
+    assert rel_err(on['flat'], off['flat']) < 1e-3 and rel_err(on['dfeat'], off['dfeat']) < 2e-3
+    assert on['launches'] <= off['launches'] - 4 * on['S'], (on['launches'], off['launches'])
