@@ -664,7 +664,7 @@ __device__ __forceinline__ void attn_bwd_body(const SAttnBwdP& a, float* sm, con
       part = fmaf(al_s[i], dv, part); asum += al_s[i];
     }
     part = pipe::group_sum(part, scratch, SA_CWARPS, 1);
-    asum = pipe::group_sum(asum, scratch, SA_CWARPS, 1);
+    if (!whole) asum = pipe::group_sum(asum, scratch, SA_CWARPS, 1);     // (uniform per segment; a whole image has sum alpha = 1)
     const float ref = whole ? part : (asum > 0.f ? part / asum : 0.f);    // whole image: ref == dot (sum alpha = 1)
     if (!whole && tid == 0) { slot[0] = part; slot[1] = ref; }
     if (whole)                                            // de = alpha (dalpha - dot)                            (:20)
@@ -741,15 +741,16 @@ __device__ __forceinline__ void attn_bwd_body(const SAttnBwdP& a, float* sm, con
     }
     SA_STAMP(5);
     // reduce over the consumer groups and the row sub-groups inside each
-    red[tid] = x1; red[SA_CTHREADS + tid] = x2; red[2 * SA_CTHREADS + tid] = y1; red[3 * SA_CTHREADS + tid] = y2;
+    red[tid] = x1; red[2 * SA_CTHREADS + tid] = y1;
+    if (!ALLWHOLE) { red[SA_CTHREADS + tid] = x2; red[3 * SA_CTHREADS + tid] = y2; }
     pipe::named_sync(1, SA_CTHREADS);
     if (grp == 0 && g == 0 && f < H4) {
       x1 = x2 = y1 = y2 = f4_zero();
       for (int gi = 0; gi < SA_NG; ++gi)
         for (int gg = 0; gg < G; ++gg) {
           const int o = gi * SA_GTHREADS + gg * H4 + f;
-          f4_add(x1, red[o]); f4_add(x2, red[SA_CTHREADS + o]);
-          f4_add(y1, red[2 * SA_CTHREADS + o]); f4_add(y2, red[3 * SA_CTHREADS + o]);
+          f4_add(x1, red[o]); f4_add(y1, red[2 * SA_CTHREADS + o]);
+          if (!ALLWHOLE) { f4_add(x2, red[SA_CTHREADS + o]); f4_add(y2, red[3 * SA_CTHREADS + o]); }
         }
       if (whole) {                                        // ref == dot: dq = w_v X1, dw_v += Y1
         const float4 v = __ldg(reinterpret_cast<const float4*>(a.wv) + f);
