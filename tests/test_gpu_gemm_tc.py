@@ -155,3 +155,27 @@ def test_gemm_presplit_epilogues_and_long_k(F_):
     out = F_.gemm(A.to(DEV), B.to(DEV), engine=300)
     e3, e1 = rel_err(out, ref), rel_err(F_.gemm(A.to(DEV), B.to(DEV), engine=400), ref)
     assert e3 < 1e-5 and e1 > 100 * e3, (e3, e1)     # hi + lo keeps ~17 significand bits per operand
+
+
+@pytest.mark.parametrize('engine', [0, 1, 200, 300])
+@pytest.mark.parametrize('M,N,K', [(300, 260, 128), (2176, 515, 96)])
+def test_gemm_exp2c_activation_all_engines(F_, engine, M, N, K):
+    """act = 3 (ACT_EXP2C, common.cuh): C = 2^(clamp(2 log2(e) (A B^T + bias), +-60)) = e^(2x) -- the form the hoisted
+    W(features) GEMM stores for the streaming attention kernels -- on the CUDA-core, 3xTF32, bf16x3 and pre-split engines,
+    aligned (vector epilogue) and odd N (scalar epilogue), including the clamp."""
+    g = torch.Generator().manual_seed(M + N + engine)
+    A = torch.randn(M, K, generator=g) / K ** 0.5 * 3
+    B = torch.randn(N, K, generator=g)
+    bias = torch.randn(N, generator=g)
+    A[0] *= 40                                                       # a row whose pre-activations leave the clamp range
+    z = 2.8853900817779268 * (A.double() @ B.double().T + bias.double())
+    ref = torch.exp2(z.clamp(-60, 60))
+    out = F_.gemm(A.to(DEV), B.to(DEV), transa=False, transb=True, bias=bias.to(DEV), act=3, engine=engine).double().cpu()
+    torch.cuda.synchronize()
+    # rows 1..: element-wise relative (e^(2x) spans many decades; d e^(2x) / e^(2x) = 2 dx, the error of the pre-activation doubled)
+    rel = ((out[1:] - ref[1:]).abs() / ref[1:]).max()
+    assert float(rel) < (2e-3 if engine else 2e-4), float(rel)
+    # row 0: far outside the clamp range -> exactly 2^+-60 wherever the pre-activation is clearly beyond it
+    far = z[0].abs() > 70
+    assert int(far.sum()) > N // 2
+    assert torch.equal(out[0][far], ref[0][far])
