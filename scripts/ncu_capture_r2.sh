@@ -17,3 +17,4 @@ run pair 'gemm_ps2_kernel' 4 2                                     # the CTA-pai
 run ce_stats 'gemm_ps2?_kernel<.*\(int\)1>' 2 1                    # EPI 1: vocabulary projection + online-softmax partials
 run ce_grad 'gemm_ps2?_kernel<.*\(int\)2>' 2 1                     # EPI 2: recompute + d logits (bf16 hi/lo copies only)
 run loop 'attn_loop_fwd_kernel' 2 1 ALEXCAP_TIME_LOOP=1            # the persistent forward time loop (opt-in)
+run gemm_step 'gemm_tc_kernel' 20 3                                # three per-step split-K GEMMs of the time loops (query, gates, ...)
